@@ -1,0 +1,140 @@
+/* b200vr -- thin C ABI of the B200-native volume-rendering device for Open Volume Renderer (OVR).
+ *
+ * This is the drop-in boundary beneath OVR's C++ plugin interface: `DeviceB200 : ovr::MainRenderer`
+ * (open-volume-renderer_b200/device/device_b200.cpp, loaded by create_renderer("b200") through
+ * ovr/renderer.cpp:42-61 + ovr/common/dylink/ObjectFactory.h:35-85) translates each MainRenderer call into the
+ * entry points below; the Python host mirror (open-volume-renderer_b200/renderer.py) binds the same ABI with
+ * ctypes. Plain pointers and sizes only; every call returns 0 on success or a negative B200VR_E* code, with a
+ * message available from b200vr_last_error(). Calls on one handle must be serialised by the caller
+ * (same rule as MainRenderer's worker-thread methods, ovr/renderer.h:112-116). There is no CPU fallback: every
+ * entry point that computes runs hand-written sm_100a CUDA kernels and fails if no CUDA device is present.
+ *
+ * Citations (file:line) are relative to the reference tree.
+ */
+#ifndef B200VR_H
+#define B200VR_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200VR_ABI_VERSION 1
+
+enum {
+  B200VR_OK = 0,
+  B200VR_EINVAL = -1,  /* bad argument / call order (maps to std::runtime_error in DeviceB200) */
+  B200VR_ECUDA = -2,   /* CUDA runtime error, text in b200vr_last_error */
+  B200VR_ENODEV = -3,  /* no usable CUDA device: the product path never falls back to the CPU */
+  B200VR_ESTATE = -4   /* render before volume / transfer function / framebuffer size are set */
+};
+
+/* scalar types a volume can arrive in: ovr::ValueType, ovr/scene.h:32-53 */
+enum {
+  B200VR_TYPE_UINT8 = 0, B200VR_TYPE_INT8, B200VR_TYPE_UINT16, B200VR_TYPE_INT16,
+  B200VR_TYPE_UINT32, B200VR_TYPE_INT32, B200VR_TYPE_FLOAT, B200VR_TYPE_DOUBLE
+};
+
+enum { B200VR_MODE_RAYMARCH = 0, B200VR_MODE_PATHTRACE = 1 };        /* set_path_tracing, ovr/renderer.h:187 */
+enum { B200VR_SHADING_NONE = 0, B200VR_SHADING_REF = 1 };            /* REF = gradient + shadow rays of the reference */
+enum { B200VR_SAMPLER_TEX3D = 0, B200VR_SAMPLER_MANUAL = 1 };        /* hardware filtered 3-D texture | 8-tap ld.global */
+
+typedef struct b200vr b200vr_t;
+
+/* replaces LaunchParams' per-frame switches (ovr/devices/optix7/params.h:55-99) and
+ * StructuredRegularVolume::set_sampling_rate (volume.cpp:156-179) */
+typedef struct b200vr_params {
+  float sampling_rate;      /* step = 1 / sampling_rate (world units) */
+  float base;               /* opacity-correction base; <= 0 keeps the default 1 */
+  int32_t spp;              /* set_sample_per_pixel */
+  int32_t mode;             /* B200VR_MODE_* */
+  int32_t shading;          /* B200VR_SHADING_* */
+  int32_t sampler;          /* B200VR_SAMPLER_* */
+  int32_t skip_empty;       /* 1 = macrocell empty-space skipping (bit-exact), 0 = visit every sample */
+  int32_t accumulate;       /* set_frame_accumulation */
+  int32_t max_num_scatters; /* 24, params.h:86 */
+  int32_t premultiplied;    /* 1 = store (C, A) before the final divide (sort-last partial images) */
+  float light_pos[3];       /* fixed directional light, params.h:79 */
+  float light_ambient;      /* params.h:80 */
+} b200vr_params;
+
+typedef struct b200vr_stats {
+  float ms;                  /* CUDA-event time of the render kernel(s) of the last b200vr_render */
+  uint64_t primary_samples;  /* TF-classified primary-march fetches executed */
+  uint64_t shadow_samples;   /* shadow-march fetches executed */
+  uint64_t gradient_fetches; /* extra trilinear fetches for gradients */
+  uint64_t delta_samples;    /* delta-tracking tentative collisions */
+  uint64_t rays;
+  int32_t frame_index;       /* value the launch saw (device_impl.cpp:241) */
+  int32_t kernel_launches;   /* kernels launched by this render call */
+} b200vr_stats;
+
+/* lifetime: replaces DeviceOptix7::Impl::init's context creation, device_impl.cpp:70-100,344-387 */
+int b200vr_abi_version(void);
+int b200vr_create(b200vr_t** out, int cuda_device);
+void b200vr_destroy(b200vr_t* h);
+const char* b200vr_last_error(const b200vr_t* h); /* h may be NULL: error of the last failed create */
+void b200vr_default_params(b200vr_params* p);
+
+/* volume: replaces StructuredRegularVolume::load_from_array3d_scalar (volume.cpp:181-257) =
+ * CreateArray3DScalarOptix7 (array.cpp:287-351: min/max, u16/i16/f64 -> f32 conversion, 3-D array + texture)
+ * + SpacePartiton_SingleMC::allocate/compute_value_range (accel/sp_singlemc.cu:99-120).
+ * voxels: x fastest, nx*ny*nz elements of `type`; host pointer, or device pointer when on_device != 0.
+ * obj_to_world: 3x4 row-major = translate(grid_origin) * scale(grid_spacing * dims) (device_impl.cpp:288-296). */
+int b200vr_set_volume(b200vr_t* h, const void* voxels, int type, int nx, int ny, int nz,
+                      const float obj_to_world[12], int on_device);
+/* synthetic volume noise(seed) generated on the device; the brick [org, org+dims) of the infinite
+ * lattice field is produced, so sort-last ranks can each create their own brick of a larger volume */
+int b200vr_set_volume_noise(b200vr_t* h, uint32_t seed, const int32_t org[3], int nx, int ny, int nz,
+                            const float obj_to_world[12]);
+int b200vr_get_value_range(b200vr_t* h, float* lo, float* hi); /* original_value_range, volume.cpp:187-189 */
+int b200vr_get_macrocells(b200vr_t* h, int32_t mc_dims[3], float* ranges_or_null, float* majorants_or_null);
+int b200vr_download_volume(b200vr_t* h, float* host_voxels); /* fp32 copy of the resident volume (tests) */
+
+/* replaces StructuredRegularVolume::set_transfer_function(vector<float> c, vector<float> o, vec2f r)
+ * (volume.cpp:104-129, fed by MainRenderer::set_scene, ovr/renderer.h:299-341): colors = 3*n_colors floats RGB,
+ * alphas = 2*n_alphas floats (position, alpha) pairs of which only alpha is read, [range_lo, range_hi] = TF value
+ * range (ignored when range_hi < range_lo, like set_value_range, volume.cpp:131-145). Rebuilds the majorants
+ * (accel/sp_singlemc.cu:122-137). */
+int b200vr_set_transfer_function(b200vr_t* h, const float* colors, int n_colors, const float* alphas, int n_alphas,
+                                 float range_lo, float range_hi);
+
+/* camera: replaces the camera block of Impl::commit (device_impl.cpp:125-144). set_camera_lookat performs that
+ * derivation itself from ovr::Camera {from, at, up, perspective.fovy} and the current framebuffer size. */
+int b200vr_set_camera(b200vr_t* h, const float position[3], const float direction[3], const float horizontal[3],
+                      const float vertical[3]);
+int b200vr_set_camera_lookat(b200vr_t* h, const float from[3], const float at[3], const float up[3], float fovy);
+int b200vr_get_camera(b200vr_t* h, float position[3], float direction[3], float horizontal[3], float vertical[3]);
+
+int b200vr_set_params(b200vr_t* h, const b200vr_params* p);
+int b200vr_get_params(b200vr_t* h, b200vr_params* p);
+int b200vr_resize(b200vr_t* h, int width, int height);   /* framebuffer.resize, device_impl.cpp:116-122 */
+int b200vr_reset_accumulation(b200vr_t* h);               /* framebuffer_reset, device_impl.cpp:225-233 */
+
+/* sort-last: clip rays against a sub-box of the object-space unit cube (one brick), default [0,1]^3 */
+int b200vr_set_clip_box(b200vr_t* h, const float lo[3], const float hi[3]);
+/* sort-first: render only the image tiles owned by `rank` of `nranks` (64x32-pixel tiles, round robin) */
+int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks);
+
+/* replaces Impl::render (device_impl.cpp:199-269): one synchronous frame; stats may be NULL */
+int b200vr_render(b200vr_t* h, b200vr_stats* stats);
+/* replaces Impl::mapframe / swap (device_impl.cpp:102-111,271-281): device pointers of the current buffer
+ * (rgba: W*H float4, grad: W*H float3, row 0 = bottom), valid until the next render/resize on this handle */
+int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev);
+int b200vr_swap(b200vr_t* h);
+int b200vr_download(b200vr_t* h, float* rgba_host, float* grad_host_or_null);
+
+/* sort-first exchange helpers: pack the tiles owned by (rank, nranks) of the current frame into a dense slice /
+ * scatter a slice received from `rank` back into this handle's frame. Slices are device pointers. */
+int64_t b200vr_tile_slice_floats(b200vr_t* h, int rank, int nranks);
+int b200vr_pack_tiles(b200vr_t* h, float* slice_dev);
+int b200vr_unpack_tiles(b200vr_t* h, const float* slice_dev, int rank, int nranks);
+/* sort-last exchange: out = front OVER back on premultiplied float4 pixels (device pointers; `back` may be a peer
+ * GPU's buffer mapped over NVLink); finalize divides colour by alpha (alpha_blend, shaders_common.h:329-337) */
+int b200vr_composite_over(b200vr_t* h, const float* front_dev, const float* back_dev, float* out_dev,
+                          int64_t n_pixels);
+int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64_t n_pixels);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VR_H */

@@ -1,0 +1,80 @@
+// Per-launch constant block of the B200 volume kernels. Plays the role of the reference's LaunchParams +
+// DeviceStructuredRegularVolume + DeviceSpacePartiton_SingleMC (ovr/devices/optix7/params.h:55-99, volume.h:40-62,
+// accel/spatial_partition.h:23-52) but is passed by value as a __grid_constant__ kernel argument: no SBT, no
+// params upload, no pointer chase per sample.
+#pragma once
+#include "device_math.cuh"
+
+namespace b200vr {
+
+constexpr int MC_SIZE = 16;        // macrocell edge in voxels (accel/spatial_partition.h:24)
+constexpr int WARP_TILE_W = 8;     // pixels per warp tile: 8 x 4
+constexpr int WARP_TILE_H = 4;
+constexpr int SUPER_TILE_W = 64;   // sort-first ownership granule: 64 x 32 pixels = 8 x 8 warp tiles
+constexpr int SUPER_TILE_H = 32;
+constexpr int WARP_TILES_PER_SUPER = (SUPER_TILE_W / WARP_TILE_W) * (SUPER_TILE_H / WARP_TILE_H);
+constexpr int RENDER_THREADS = 128;
+
+struct Counters {
+  unsigned long long primary_samples, shadow_samples, gradient_fetches, delta_samples, rays;
+};
+
+struct LaunchParams {
+  // ---- volume ----
+  cudaTextureObject_t tex;  // fp32 3-D array, linear filter, clamp, normalised coords (array.cpp:300-306)
+  const float* lin;         // linear fp32 copy, x fastest (manual sampler, macrocell build)
+  int nx, ny, nz;
+  f3 rdim;                  // 1 / dims
+  aff3 otw, wto;
+  f3 clip_lo, clip_hi;      // object-space clip box (unit cube unless sort-last)
+  // ---- transfer function (global copies; staged into shared memory by every CTA) ----
+  const float4* tf_color;
+  const float* tf_alpha;
+  int n_color, n_alpha;
+  float tf_lower, tf_upper, tf_scale;
+  // ---- macrocells ----
+  const float* majorants;
+  i3 mc;
+  f3 cells_per_unit;        // dims / 16: object-space position -> macrocell coordinate
+  f3 spac_rcp;              // 1 / (16 / dims) computed like sp_singlemc.cu:99-111 (delta tracking DDA)
+  // ---- sampling ----
+  float step, base;
+  // ---- camera (device form, device_impl.cpp:125-136) ----
+  f3 cam_pos, cam_dir, cam_hor, cam_ver;
+  lin3 wtc;                 // get_xfm_world_to_camera (shaders_common.h:276-289)
+  f3 light_dir;             // normalize(light_directional_pos), params.h:79
+  float light_ambient;
+  int max_num_scatters;
+  // ---- frame ----
+  float4* rgba;
+  float* grad;              // 3 floats per pixel (vec3f)
+  float4* accum;
+  int width, height;
+  float rw, rh;             // 1 / size (size_rcp)
+  int frame_index;
+  int spp;
+  int accumulate;
+  int premultiplied;
+  // ---- tiles ----
+  int super_w, super_h;     // image size in super tiles
+  int rank, nranks;         // sort-first ownership: super tile s belongs to rank s % nranks
+  int n_warp_tiles;         // warp tiles this launch has to render
+  unsigned int* tile_counter;
+  Counters* counters;
+};
+
+// k-th warp tile owned by (rank, nranks) -> pixel origin
+__host__ __device__ __forceinline__ void warp_tile_origin(int k, int rank, int nranks, int super_w, int& px, int& py)
+{
+  const int m = k / WARP_TILES_PER_SUPER, r = k % WARP_TILES_PER_SUPER;
+  const int s = rank + m * nranks;
+  const int sx = s % super_w, sy = s / super_w;
+  px = sx * SUPER_TILE_W + (r % (SUPER_TILE_W / WARP_TILE_W)) * WARP_TILE_W;
+  py = sy * SUPER_TILE_H + (r / (SUPER_TILE_W / WARP_TILE_W)) * WARP_TILE_H;
+}
+__host__ __device__ __forceinline__ int owned_super_tiles(int rank, int nranks, int n_super)
+{
+  return rank < n_super ? (n_super - rank + nranks - 1) / nranks : 0;
+}
+
+} // namespace b200vr

@@ -1,0 +1,136 @@
+// Scalar-field sampling and transfer-function classification for the B200 volume kernels.
+//   * SAMPLER_TEX3D : the 3-D texture unit (same filter settings as the reference, array.cpp:300-306)
+//   * SAMPLER_MANUAL: 8-tap ld.global.nc fetch from the linear fp32 copy with the texture unit's 1.8 fixed-point
+//                     weights reproduced in software (CUDA Programming Guide, "Linear Filtering")
+//   * the 1-D transfer function is staged in shared memory once per CTA and interpolated in software with the same
+//     fixed-point weights the reference's hardware tex1D applies (shaders_common.h:311-319,356-367).
+#pragma once
+#include "launch_params.cuh"
+
+namespace b200vr {
+
+enum { SAMPLER_TEX3D = 0, SAMPLER_MANUAL = 1 };
+
+// one filter tap: xB = N*x - 0.5 (un-fused, as the texture unit), i = floor(xB), alpha quantised to 8 fractional bits
+__device__ __forceinline__ void filter_tap(float x, int n, int& i0, int& i1, float& w)
+{
+  const float xb = __fsub_rn(__fmul_rn(x, (float)n), 0.5f);
+  const float fl = floorf(xb);
+  w = floorf(__fmaf_rn(__fsub_rn(xb, fl), 256.f, 0.5f)) * (1.f / 256.f);
+  const int i = (int)fl;
+  i0 = min(max(i, 0), n - 1);
+  i1 = min(max(i + 1, 0), n - 1);
+}
+__device__ __forceinline__ float lerp_q(float a, float b, float w)
+{
+  return __fadd_rn(__fmul_rn(__fsub_rn(1.f, w), a), __fmul_rn(w, b));
+}
+
+template<int SAMPLER>
+__device__ __forceinline__ float sample_volume(const LaunchParams& P, f3 p)
+{
+  // sample_volume_object_space (shaders_common.h:186-193): clamp to the unit cube, then fetch
+  p.x = clampf(p.x, 0.f, 1.f);
+  p.y = clampf(p.y, 0.f, 1.f);
+  p.z = clampf(p.z, 0.f, 1.f);
+  if (SAMPLER == SAMPLER_TEX3D) {
+    return tex3D<float>(P.tex, p.x, p.y, p.z);
+  }
+  else {
+    int x0, x1, y0, y1, z0, z1;
+    float wx, wy, wz;
+    filter_tap(p.x, P.nx, x0, x1, wx);
+    filter_tap(p.y, P.ny, y0, y1, wy);
+    filter_tap(p.z, P.nz, z0, z1, wz);
+    const size_t sy = (size_t)P.nx, sz = (size_t)P.nx * (size_t)P.ny;
+    const float* __restrict__ v = P.lin;
+    const size_t r00 = y0 * sy + z0 * sz, r10 = y1 * sy + z0 * sz, r01 = y0 * sy + z1 * sz, r11 = y1 * sy + z1 * sz;
+    const float a0 = __ldg(v + r00 + x0), a1 = __ldg(v + r00 + x1);
+    const float b0 = __ldg(v + r10 + x0), b1 = __ldg(v + r10 + x1);
+    const float c0 = __ldg(v + r01 + x0), c1 = __ldg(v + r01 + x1);
+    const float d0 = __ldg(v + r11 + x0), d1 = __ldg(v + r11 + x1);
+    const float c00 = lerp_q(a0, a1, wx), c10 = lerp_q(b0, b1, wx);
+    const float c01 = lerp_q(c0, c1, wx), c11 = lerp_q(d0, d1, wx);
+    return lerp_q(lerp_q(c00, c10, wy), lerp_q(c01, c11, wy), wz);
+  }
+}
+
+// transfer function tables in shared memory
+struct TfShared {
+  const float4* color;
+  const float* alpha;
+};
+
+__device__ __forceinline__ TfShared stage_transfer_function(const LaunchParams& P, unsigned char* smem)
+{
+  float4* c = reinterpret_cast<float4*>(smem);
+  float* a = reinterpret_cast<float*>(smem + sizeof(float4) * (size_t)P.n_color);
+  for (int i = threadIdx.x; i < P.n_color; i += blockDim.x) c[i] = P.tf_color[i];
+  for (int i = threadIdx.x; i < P.n_alpha; i += blockDim.x) a[i] = P.tf_alpha[i];
+  __syncthreads();
+  TfShared t;
+  t.color = c;
+  t.alpha = a;
+  return t;
+}
+__host__ __device__ __forceinline__ size_t tf_shared_bytes(int n_color, int n_alpha)
+{
+  return sizeof(float4) * (size_t)n_color + sizeof(float) * (size_t)n_alpha;
+}
+
+// array1d_nodal coordinate: u = fmaf(v, N-1, 0.5) * __frcp_rn(N), v clamped to [0,1]
+__device__ __forceinline__ float nodal_coord(float v, int n)
+{
+  v = clampf(v, 0.f, 1.f);
+  return __fmul_rn(__fmaf_rn(v, (float)(n - 1), 0.5f), __frcp_rn((float)n));
+}
+__device__ __forceinline__ float tf_normalise(const LaunchParams& P, float sample)
+{
+  return __fmul_rn(__fsub_rn(clampf(sample, P.tf_lower, P.tf_upper), P.tf_lower), P.tf_scale);
+}
+__device__ __forceinline__ float classify_alpha(const LaunchParams& P, const TfShared& tf, float sample)
+{
+  int i0, i1;
+  float w;
+  filter_tap(nodal_coord(tf_normalise(P, sample), P.n_alpha), P.n_alpha, i0, i1, w);
+  return lerp_q(tf.alpha[i0], tf.alpha[i1], w);
+}
+__device__ __forceinline__ f3 classify_color(const LaunchParams& P, const TfShared& tf, float sample)
+{
+  int i0, i1;
+  float w;
+  filter_tap(nodal_coord(tf_normalise(P, sample), P.n_color), P.n_color, i0, i1, w);
+  const float4 a = tf.color[i0], b = tf.color[i1];
+  return mk3(lerp_q(a.x, b.x, w), lerp_q(a.y, b.y, w), lerp_q(a.z, b.z, w));
+}
+
+// opacity correction (shaders_raymarching.cu:73-77,118-122)
+__device__ __forceinline__ float correct_alpha(float a, float base, float dt)
+{
+  const float adj = base * dt;
+  if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));
+  return a;
+}
+
+// macrocell lookup at an object-space position; returns the linear cell index and the integer cell
+__device__ __forceinline__ int cell_of(const LaunchParams& P, f3 p, i3& c)
+{
+  c.x = min((int)(clampf(p.x, 0.f, 1.f) * (float)P.nx) / MC_SIZE, P.mc.x - 1);
+  c.y = min((int)(clampf(p.y, 0.f, 1.f) * (float)P.ny) / MC_SIZE, P.mc.y - 1);
+  c.z = min((int)(clampf(p.z, 0.f, 1.f) * (float)P.nz) / MC_SIZE, P.mc.z - 1);
+  return c.x + P.mc.x * (c.y + P.mc.y * c.z);
+}
+
+// parametric exit of macrocell c along the object-space ray (oo, od); cells are [16c, 16c+16) voxels
+__device__ __forceinline__ float cell_exit_t(const LaunchParams& P, i3 c, f3 oo, f3 od_rcp, f3 od)
+{
+  const float bx = (float)((c.x + (od.x > 0.f ? 1 : 0)) * MC_SIZE) * P.rdim.x;
+  const float by = (float)((c.y + (od.y > 0.f ? 1 : 0)) * MC_SIZE) * P.rdim.y;
+  const float bz = (float)((c.z + (od.z > 0.f ? 1 : 0)) * MC_SIZE) * P.rdim.z;
+  const float tx = od.x != 0.f ? (bx - oo.x) * od_rcp.x : FLT_MAX;
+  const float ty = od.y != 0.f ? (by - oo.y) * od_rcp.y : FLT_MAX;
+  const float tz = od.z != 0.f ? (bz - oo.z) * od_rcp.z : FLT_MAX;
+  return fminf(fminf(tx, ty), tz);
+}
+
+} // namespace b200vr

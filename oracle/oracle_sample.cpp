@@ -1,0 +1,221 @@
+// TEST INFRASTRUCTURE ONLY -- CPU oracle: texture-unit model, transfer function, clipping, macrocells, noise.
+// See ovr_oracle.h for the reference files this restates.
+#include "oracle_internal.h"
+
+#include <cstring>
+
+namespace ovr_oracle {
+
+// Linear filtering with normalised coordinates and clamp addressing (reference texture settings:
+// ovr/devices/optix7/array.cpp:300-306, ovr/common/cuda/cuda_buffer.h:248-287). Per the CUDA Programming
+// Guide ("Texture Fetching", linear filtering): xB = N*x - 0.5, i = floor(xB), alpha = frac(xB) held in
+// 1.8 fixed point; taps i and i+1 are clamped to [0, N-1]. Voxel k is therefore centred at (k+0.5)/N.
+static inline void tap(float p, int n, int mode, int& i0, int& i1, float& w)
+{
+  const float xb = p * float(n) - 0.5f;
+  const float fl = std::floor(xb);
+  w = quant_weight(xb - fl, mode);
+  const int i = int(fl);
+  i0 = std::min(std::max(i, 0), n - 1);
+  i1 = std::min(std::max(i + 1, 0), n - 1);
+}
+
+static inline float lerpf(float a, float b, float w) { return (1.f - w) * a + w * b; }
+
+float tex3d(const VolumeTex& t, float px, float py, float pz)
+{
+  int x0, x1, y0, y1, z0, z1;
+  float wx, wy, wz;
+  tap(px, t.nx, t.mode, x0, x1, wx);
+  tap(py, t.ny, t.mode, y0, y1, wy);
+  tap(pz, t.nz, t.mode, z0, z1, wz);
+  const size_t sy = size_t(t.nx), sz = size_t(t.nx) * size_t(t.ny);
+  const float* v = t.v;
+  const float c00 = lerpf(v[x0 + y0 * sy + z0 * sz], v[x1 + y0 * sy + z0 * sz], wx);
+  const float c10 = lerpf(v[x0 + y1 * sy + z0 * sz], v[x1 + y1 * sy + z0 * sz], wx);
+  const float c01 = lerpf(v[x0 + y0 * sy + z1 * sz], v[x1 + y0 * sy + z1 * sz], wx);
+  const float c11 = lerpf(v[x0 + y1 * sy + z1 * sz], v[x1 + y1 * sy + z1 * sz], wx);
+  return lerpf(lerpf(c00, c10, wy), lerpf(c01, c11, wy), wz);
+}
+
+float tex1d_scalar(const float* tab, int n, float u, int mode)
+{
+  int i0, i1;
+  float w;
+  tap(u, n, mode, i0, i1, w);
+  return lerpf(tab[i0], tab[i1], w);
+}
+
+void tex1d_float4(const float* tab, int n, float u, int mode, float out[4])
+{
+  int i0, i1;
+  float w;
+  tap(u, n, mode, i0, i1, w);
+  for (int c = 0; c < 4; c++) out[c] = lerpf(tab[4 * i0 + c], tab[4 * i1 + c], w);
+}
+
+// array1d_nodal: v clamped to [0,1]; u = fmaf(v, N-1, 0.5) * __frcp_rn(N)   (shaders_common.h:311-319)
+static inline float nodal_coord(float v, int n)
+{
+  v = cclamp(v, 0.f, 1.f);
+  return std::fmaf(v, float(n - 1), 0.5f) * (1.f / float(n));
+}
+
+RGBA sample_tf(const ovr_oracle_scene& s, float sample)
+{
+  // shaders_common.h:356-367; scale = 1/(upper-lower) from volume.cpp:131-145
+  const float scale = 1.f / (s.tf_upper - s.tf_lower);
+  const float v = (cclamp(sample, s.tf_lower, s.tf_upper) - s.tf_lower) * scale;
+  float c[4];
+  tex1d_float4(s.tf_color, s.n_color, nodal_coord(v, s.n_color), s.filter_mode, c);
+  RGBA r;
+  r.r = c[0];
+  r.g = c[1];
+  r.b = c[2];
+  r.a = tex1d_scalar(s.tf_alpha, s.n_alpha, nodal_coord(v, s.n_alpha), s.filter_mode);
+  return r;
+}
+
+bool intersect_box(float& _t0, float& _t1, vec3 org, vec3 dir, vec3 lower, vec3 upper)
+{
+  // __frcp_rn(x) is the correctly rounded reciprocal == 1.f/x in IEEE fp32
+  const bool sx = std::fabs(dir.x) < float_small, sy = std::fabs(dir.y) < float_small,
+             sz = std::fabs(dir.z) < float_small;
+  const vec3 rcp = v3(1.f / dir.x, 1.f / dir.y, 1.f / dir.z);
+  const vec3 t_lo = v3(sx ? float_large : (lower.x - org.x) * rcp.x, sy ? float_large : (lower.y - org.y) * rcp.y,
+                       sz ? float_large : (lower.z - org.z) * rcp.z);
+  const vec3 t_hi = v3(sx ? -float_large : (upper.x - org.x) * rcp.x, sy ? -float_large : (upper.y - org.y) * rcp.y,
+                       sz ? -float_large : (upper.z - org.z) * rcp.z);
+  const float near_ = cmax(cmax(cmin(t_lo.x, t_hi.x), cmin(t_lo.y, t_hi.y)), cmin(t_lo.z, t_hi.z));
+  const float far_ = cmin(cmin(cmax(t_lo.x, t_hi.x), cmax(t_lo.y, t_hi.y)), cmax(t_lo.z, t_hi.z));
+  const float t0 = cmax(_t0, near_);
+  const float t1 = cmin(_t1, far_);
+  _t0 = t0;
+  _t1 = t1;
+  return t1 > t0;
+}
+
+void parallel_rows(int y0, int y1, int stride_y, int num_threads, const std::function<void(int)>& row_fn)
+{
+  if (stride_y < 1) stride_y = 1;
+  const int n_rows = (y1 - y0 + stride_y - 1) / stride_y;
+  if (n_rows <= 0) return;
+  if (num_threads <= 0) num_threads = ovr_oracle_hardware_threads();
+  num_threads = std::min(num_threads, n_rows);
+  std::atomic<int> next{ 0 };
+  auto worker = [&]() {
+    for (;;) {
+      const int r = next.fetch_add(1);
+      if (r >= n_rows) break;
+      row_fn(y0 + r * stride_y);
+    }
+  };
+  if (num_threads == 1) {
+    worker();
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int i = 0; i < num_threads; i++) pool.emplace_back(worker);
+  for (auto& t : pool) t.join();
+}
+
+} // namespace ovr_oracle
+
+using namespace ovr_oracle;
+
+extern "C" int ovr_oracle_hardware_threads(void)
+{
+  const unsigned n = std::thread::hardware_concurrency();
+  return n ? int(n) : 1;
+}
+
+extern "C" void ovr_oracle_default_scene(ovr_oracle_scene* s)
+{
+  std::memset(s, 0, sizeof(*s));
+  const float id[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
+  std::memcpy(s->obj_to_world, id, sizeof(id));
+  s->step = 1.f;
+  s->base = 1.f;
+  s->spp = 1;
+  s->frame_index = 1;
+  s->shading = OVR_ORACLE_SHADING_REF;
+  s->max_num_scatters = 24;
+  s->light_pos[0] = -907.108f; // params.h:79
+  s->light_pos[1] = 2205.875f;
+  s->light_pos[2] = -400.0267f;
+  s->light_ambient = 1.f;
+  for (int i = 0; i < 3; i++) s->clip_hi[i] = 1.f;
+}
+
+extern "C" void ovr_oracle_camera(const float from[3], const float at[3], const float up[3], float fovy, int width,
+                                  int height, float position[3], float direction[3], float horizontal[3],
+                                  float vertical[3])
+{
+  // device_impl.cpp:125-136 ("the factor 2.f ... to match ospray"); tan evaluated in double like the host code
+  const float t = 2.f * float(std::tan(double(fovy * 0.5f * float(M_PI) / 180.f)));
+  const float aspect = float(width) / float(height);
+  const vec3 f = v3(from[0], from[1], from[2]), a = v3(at[0], at[1], at[2]), u = v3(up[0], up[1], up[2]);
+  const vec3 d = normalize(a - f);
+  const vec3 h = (t * aspect) * normalize(cross(d, u));
+  const vec3 v = cross(h, d) / aspect;
+  position[0] = f.x, position[1] = f.y, position[2] = f.z;
+  direction[0] = d.x, direction[1] = d.y, direction[2] = d.z;
+  horizontal[0] = h.x, horizontal[1] = h.y, horizontal[2] = h.z;
+  vertical[0] = v.x, vertical[1] = v.y, vertical[2] = v.z;
+}
+
+extern "C" int ovr_oracle_clip(const float org[3], const float dir[3], const float lo[3], const float hi[3],
+                               float* t0, float* t1)
+{
+  float a = 0.f, b = float_large;
+  const bool hit = intersect_box(a, b, v3(org[0], org[1], org[2]), v3(dir[0], dir[1], dir[2]),
+                                 v3(lo[0], lo[1], lo[2]), v3(hi[0], hi[1], hi[2]));
+  *t0 = a;
+  *t1 = b;
+  return hit ? 1 : 0;
+}
+
+extern "C" void ovr_oracle_sample_volume(const float* voxels, const int32_t dims[3], int filter_mode,
+                                         const float* pts, int64_t n, float* out)
+{
+  VolumeTex t{ voxels, dims[0], dims[1], dims[2], filter_mode };
+  for (int64_t i = 0; i < n; i++) out[i] = sample_volume(t, v3(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]));
+}
+
+extern "C" void ovr_oracle_sample_tf(const ovr_oracle_scene* s, const float* values, int64_t n, float* rgba)
+{
+  for (int64_t i = 0; i < n; i++) {
+    const RGBA c = sample_tf(*s, values[i]);
+    rgba[4 * i + 0] = c.r, rgba[4 * i + 1] = c.g, rgba[4 * i + 2] = c.b, rgba[4 * i + 3] = c.a;
+  }
+}
+
+extern "C" void ovr_oracle_tea(uint32_t v0, uint32_t v1, int n_draws, float* out_pairs, uint32_t* out_state)
+{
+  TEA rng(v0, v1);
+  for (int i = 0; i < n_draws; i++) {
+    rng.draw(out_pairs[2 * i], out_pairs[2 * i + 1]);
+    if (out_state) out_state[2 * i] = rng.v0, out_state[2 * i + 1] = rng.v1;
+  }
+}
+
+extern "C" int ovr_oracle_dda(const float org[3], const float dir[3], float tmin, float tmax, const int32_t grid[3],
+                              int max_cells, int32_t* cells, float* t0t1)
+{
+  // same traversal as dda::dda3 (accel/dda.h:150-297) expressed through the resumable iterator
+  DDAIter it;
+  const vec3 o = v3(org[0], org[1], org[2]), d = v3(dir[0], dir[1], dir[2]);
+  const vec3i_t g = { grid[0], grid[1], grid[2] };
+  it.init(o, d, tmin, tmax, g);
+  int n = 0;
+  while (it.next(o, d, tmin, tmax, g, [&](const vec3i_t& c, float t0, float t1) {
+    if (n < max_cells) {
+      cells[3 * n] = c.x, cells[3 * n + 1] = c.y, cells[3 * n + 2] = c.z;
+      t0t1[2 * n] = t0, t0t1[2 * n + 1] = t1;
+    }
+    n++;
+    return true;
+  })) {
+  }
+  return n;
+}

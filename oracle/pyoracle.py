@@ -1,0 +1,224 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes binding of the CPU oracle (oracle/liboracle.so).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / ``--impl reference`` legs may import this.
+The product path (open-volume-renderer_b200/) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+SHADING_NONE, SHADING_REF = 0, 1
+FILTER_FIXED8_RN, FILTER_FIXED8_TRUNC, FILTER_FP32 = 0, 1, 2
+MC_REFERENCE, MC_CONSERVATIVE = 0, 1
+
+_f3 = C.c_float * 3
+_i3 = C.c_int32 * 3
+
+
+class Scene(C.Structure):
+    _fields_ = [
+        ("dims", _i3), ("voxels", C.c_void_p), ("obj_to_world", C.c_float * 12),
+        ("tf_color", C.c_void_p), ("n_color", C.c_int32), ("tf_alpha", C.c_void_p), ("n_alpha", C.c_int32),
+        ("tf_lower", C.c_float), ("tf_upper", C.c_float), ("step", C.c_float), ("base", C.c_float),
+        ("cam_position", _f3), ("cam_direction", _f3), ("cam_horizontal", _f3), ("cam_vertical", _f3),
+        ("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("frame_index", C.c_int32),
+        ("shading", C.c_int32), ("skip_empty", C.c_int32), ("filter_mode", C.c_int32),
+        ("max_num_scatters", C.c_int32), ("light_pos", _f3), ("light_ambient", C.c_float),
+        ("clip_lo", _f3), ("clip_hi", _f3), ("mc_majorants", C.c_void_p), ("mc_dims", _i3),
+    ]
+
+
+class Counters(C.Structure):
+    _fields_ = [("primary_samples", C.c_uint64), ("shadow_samples", C.c_uint64), ("gradient_fetches", C.c_uint64),
+                ("delta_samples", C.c_uint64), ("rays", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+def build(force=False):
+    """Compile liboracle.so (and oracle/_ref when /root/reference is present)."""
+    so = os.path.join(_HERE, "liboracle.so")
+    if force or not os.path.exists(so):
+        subprocess.run(["make", "-C", _HERE, "liboracle.so"], check=True, capture_output=True)
+    if os.path.isdir("/root/reference/ovr") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "libovr_ref_kat.so"))):
+        subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        L = C.CDLL(so)
+        L.ovr_oracle_hardware_threads.restype = C.c_int
+        L.ovr_oracle_dda.restype = C.c_int
+        L.ovr_oracle_clip.restype = C.c_int
+        _LIB = L
+    return _LIB
+
+
+def ref_kat_lib():
+    """The reference's own dda.h / RandomTEA / gdt compiled on the host (exists only where /root/reference does)."""
+    so = os.path.join(_HERE, "_ref", "libovr_ref_kat.so")
+    if not os.path.exists(so):
+        return None
+    L = C.CDLL(so)
+    L.ref_dda3.restype = C.c_int
+    L.ref_dda_iter.restype = C.c_int
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def hardware_threads():
+    return int(lib().ovr_oracle_hardware_threads())
+
+
+def camera(frm, at, up, fovy, width, height):
+    out = [np.zeros(3, np.float32) for _ in range(4)]
+    lib().ovr_oracle_camera(_f3(*frm), _f3(*at), _f3(*up), C.c_float(fovy), width, height, *[_fp(o) for o in out])
+    return dict(position=out[0], direction=out[1], horizontal=out[2], vertical=out[3])
+
+
+def noise(n, seed=1337, org=(0, 0, 0), bdims=None, threads=0):
+    bdims = tuple(bdims) if bdims is not None else (n, n, n)
+    out = np.empty((bdims[2], bdims[1], bdims[0]), np.float32)
+    lib().ovr_oracle_noise(n, C.c_uint32(seed), _i3(*org), _i3(*bdims), _fp(out), threads)
+    return out
+
+
+def macrocell_dims(dims):
+    mc = _i3()
+    lib().ovr_oracle_macrocell_dims(_i3(*dims), mc)
+    return tuple(mc)
+
+
+def build_ranges(vol, mode=MC_CONSERVATIVE):
+    """vol: float32 [nz, ny, nx]; returns ranges [mz, my, mx, 2]."""
+    vol = np.ascontiguousarray(vol, np.float32)
+    dims = (vol.shape[2], vol.shape[1], vol.shape[0])
+    mc = macrocell_dims(dims)
+    r = np.empty((mc[2], mc[1], mc[0], 2), np.float32)
+    lib().ovr_oracle_build_ranges(_fp(vol), _i3(*dims), mode, _fp(r))
+    return r
+
+
+def build_majorants(ranges, tf_alpha, win_lo, win_hi):
+    ranges = np.ascontiguousarray(ranges, np.float32)
+    tf_alpha = np.ascontiguousarray(tf_alpha, np.float32)
+    m = np.empty(ranges.shape[:-1], np.float32)
+    lib().ovr_oracle_build_majorants(_fp(ranges), C.c_int64(m.size), _fp(tf_alpha), len(tf_alpha),
+                                     C.c_float(win_lo), C.c_float(win_hi), _fp(m))
+    return m
+
+
+def tea(v0, v1, n):
+    out = np.empty((n, 2), np.float32)
+    st = np.empty((n, 2), np.uint32)
+    lib().ovr_oracle_tea(C.c_uint32(v0), C.c_uint32(v1), n, _fp(out), st.ctypes.data_as(C.c_void_p))
+    return out, st
+
+
+def dda(org, dr, tmin, tmax, grid, max_cells=4096):
+    cells = np.empty((max_cells, 3), np.int32)
+    tt = np.empty((max_cells, 2), np.float32)
+    n = lib().ovr_oracle_dda(_f3(*org), _f3(*dr), C.c_float(tmin), C.c_float(tmax), _i3(*grid), max_cells,
+                             cells.ctypes.data_as(C.c_void_p), _fp(tt))
+    return cells[:n].copy(), tt[:n].copy()
+
+
+def clip(org, dr, lo=(0, 0, 0), hi=(1, 1, 1)):
+    t0, t1 = C.c_float(), C.c_float()
+    hit = lib().ovr_oracle_clip(_f3(*org), _f3(*dr), _f3(*lo), _f3(*hi), C.byref(t0), C.byref(t1))
+    return bool(hit), t0.value, t1.value
+
+
+def sample_volume(vol, pts, filter_mode=FILTER_FIXED8_RN):
+    vol = np.ascontiguousarray(vol, np.float32)
+    pts = np.ascontiguousarray(pts, np.float32)
+    out = np.empty(len(pts), np.float32)
+    dims = (vol.shape[2], vol.shape[1], vol.shape[0])
+    lib().ovr_oracle_sample_volume(_fp(vol), _i3(*dims), filter_mode, _fp(pts), C.c_int64(len(pts)), _fp(out))
+    return out
+
+
+class OracleScene:
+    """Owns the numpy buffers behind an ovr_oracle_scene. `desc` is a scenes.SceneDesc-like object with
+    attributes: volume [nz,ny,nx] f32, obj_to_world (12,), tf_color [Nc,4], tf_alpha [Na], tf_range (lo,hi),
+    step, base, cam (dict from camera()), width, height, spp, shading."""
+
+    def __init__(self, desc, skip_empty=False, filter_mode=FILTER_FIXED8_RN, mc_mode=MC_CONSERVATIVE,
+                 build_macrocells=True):
+        self.vol = np.ascontiguousarray(desc.volume, np.float32)
+        self.tf_color = np.ascontiguousarray(desc.tf_color, np.float32).reshape(-1, 4)
+        self.tf_alpha = np.ascontiguousarray(desc.tf_alpha, np.float32)
+        s = Scene()
+        lib().ovr_oracle_default_scene(C.byref(s))
+        nz, ny, nx = self.vol.shape
+        s.dims = _i3(nx, ny, nz)
+        s.voxels = _p(self.vol)
+        s.obj_to_world = (C.c_float * 12)(*[float(x) for x in desc.obj_to_world])
+        s.tf_color, s.n_color = _p(self.tf_color), len(self.tf_color)
+        s.tf_alpha, s.n_alpha = _p(self.tf_alpha), len(self.tf_alpha)
+        s.tf_lower, s.tf_upper = float(desc.tf_range[0]), float(desc.tf_range[1])
+        s.step, s.base = float(desc.step), float(desc.base)
+        cam = desc.cam
+        s.cam_position, s.cam_direction = _f3(*cam["position"]), _f3(*cam["direction"])
+        s.cam_horizontal, s.cam_vertical = _f3(*cam["horizontal"]), _f3(*cam["vertical"])
+        s.width, s.height, s.spp = int(desc.width), int(desc.height), int(desc.spp)
+        s.shading = int(desc.shading)
+        s.skip_empty = int(bool(skip_empty))
+        s.filter_mode = int(filter_mode)
+        clip = getattr(desc, "clip", None)
+        if clip is not None:
+            s.clip_lo, s.clip_hi = _f3(*clip[0]), _f3(*clip[1])
+        self.s = s
+        self.ranges = self.majorants = None
+        if build_macrocells:
+            self.ranges = build_ranges(self.vol, mc_mode)
+            self.majorants = build_majorants(self.ranges, self.tf_alpha, s.tf_lower, s.tf_upper)
+            s.mc_majorants = _p(self.majorants)
+            s.mc_dims = _i3(*macrocell_dims((nx, ny, nz)))
+
+    def render_march(self, rect=None, stride=(1, 1), premultiplied=False, threads=0, frame_index=1):
+        s = self.s
+        s.frame_index = frame_index
+        W, H = s.width, s.height
+        x0, y0, x1, y1 = rect if rect is not None else (0, 0, W, H)
+        rgba = np.zeros((H, W, 4), np.float32)
+        grad = np.zeros((H, W, 3), np.float32)
+        cnt = Counters()
+        lib().ovr_oracle_render_march(C.byref(s), x0, y0, x1, y1, stride[0], stride[1], _fp(rgba), _fp(grad),
+                                      int(premultiplied), C.byref(cnt), threads)
+        return rgba, grad, cnt.as_dict()
+
+    def render_path(self, rect=None, stride=(1, 1), threads=0, frame_index=1):
+        s = self.s
+        s.frame_index = frame_index
+        W, H = s.width, s.height
+        x0, y0, x1, y1 = rect if rect is not None else (0, 0, W, H)
+        rgba = np.zeros((H, W, 4), np.float32)
+        cnt = Counters()
+        lib().ovr_oracle_render_path(C.byref(s), x0, y0, x1, y1, stride[0], stride[1], _fp(rgba), C.byref(cnt),
+                                     threads)
+        return rgba, cnt.as_dict()
+
+    def sample_tf(self, values):
+        values = np.ascontiguousarray(values, np.float32)
+        out = np.empty((len(values), 4), np.float32)
+        lib().ovr_oracle_sample_tf(C.byref(self.s), _fp(values), C.c_int64(len(values)), _fp(out))
+        return out

@@ -1,0 +1,84 @@
+// TEST INFRASTRUCTURE ONLY -- known-answer shim around the REFERENCE's own headers, compiled as host code.
+// Nothing here is a copy: the reference headers are #included where they lie under /root/reference
+// (see oracle/Makefile, target `ref`); the output goes to oracle/_ref/ (git-ignored).
+//   ovr/devices/optix7/accel/dda.h          dda::DDAIter, dda::dda3
+//   ovr/common/random/random.h              random::RandomTEA
+//   extern/gdt/gdt/math/{vec,mat}.h         normalize, xfmPoint/Vector/Normal, affine inverse
+// tests/golden/make_golden.py drives it to produce the fixtures that pin the oracle.
+#include <cuda_runtime.h> // float2 / make_float2 for random.h (host-side CUDA headers only)
+#include <dda.h>
+namespace ovr { namespace random {
+#include <random_tea_extract.h> // struct RandomTEA, cut from ovr/common/random/random.h:146-188 at build time
+} }
+
+#include <cstdint>
+
+using namespace ovr;
+using namespace gdt;
+
+extern "C" void ref_tea(uint32_t v0, uint32_t v1, int n_draws, float* out_pairs)
+{
+  ovr::random::RandomTEA rng(v0, v1);
+  for (int i = 0; i < n_draws; i++) {
+    const float2 f = rng.get_floats();
+    out_pairs[2 * i] = f.x;
+    out_pairs[2 * i + 1] = f.y;
+  }
+}
+
+extern "C" int ref_dda3(const float org[3], const float dir[3], float tmin, float tmax, const int32_t grid[3],
+                        int max_cells, int32_t* cells, float* t0t1)
+{
+  int n = 0;
+  dda::dda3(vec3f(org[0], org[1], org[2]), vec3f(dir[0], dir[1], dir[2]), tmin, tmax,
+            vec3i(grid[0], grid[1], grid[2]), false, [&](const vec3i& c, float t0, float t1) {
+              if (n < max_cells) {
+                cells[3 * n] = c.x, cells[3 * n + 1] = c.y, cells[3 * n + 2] = c.z;
+                t0t1[2 * n] = t0, t0t1[2 * n + 1] = t1;
+              }
+              n++;
+              return true;
+            });
+  return n;
+}
+
+extern "C" int ref_dda_iter(const float org[3], const float dir[3], float tmin, float tmax, const int32_t grid[3],
+                            int max_cells, int32_t* cells, float* t0t1)
+{
+  dda::DDAIter it;
+  const vec3f o(org[0], org[1], org[2]), d(dir[0], dir[1], dir[2]);
+  const vec3i g(grid[0], grid[1], grid[2]);
+  it.init(o, d, tmin, tmax, g);
+  int n = 0;
+  while (it.next(o, d, tmin, tmax, g, false, [&](const vec3i& c, float t0, float t1) {
+    if (n < max_cells) {
+      cells[3 * n] = c.x, cells[3 * n + 1] = c.y, cells[3 * n + 2] = c.z;
+      t0t1[2 * n] = t0, t0t1[2 * n + 1] = t1;
+    }
+    n++;
+    return true;
+  })) {
+  }
+  return n;
+}
+
+// gdt transforms: m = 3x4 row-major; out[0..2] = xfmPoint, [3..5] = xfmVector, [6..8] = xfmNormal,
+// [9..11] = normalize(v), [12..23] = inverse(m) as 3x4 row-major
+extern "C" void ref_xfm(const float m[12], const float v[3], float* out)
+{
+  affine3f a;
+  a.l.vx = vec3f(m[0], m[4], m[8]);
+  a.l.vy = vec3f(m[1], m[5], m[9]);
+  a.l.vz = vec3f(m[2], m[6], m[10]);
+  a.p = vec3f(m[3], m[7], m[11]);
+  const vec3f x(v[0], v[1], v[2]);
+  const vec3f p = xfmPoint(a, x), w = xfmVector(a, x), n = xfmNormal(a, x), u = normalize(x);
+  out[0] = p.x, out[1] = p.y, out[2] = p.z;
+  out[3] = w.x, out[4] = w.y, out[5] = w.z;
+  out[6] = n.x, out[7] = n.y, out[8] = n.z;
+  out[9] = u.x, out[10] = u.y, out[11] = u.z;
+  const affine3f inv = rcp(a);
+  out[12] = inv.l.vx.x, out[13] = inv.l.vy.x, out[14] = inv.l.vz.x, out[15] = inv.p.x;
+  out[16] = inv.l.vx.y, out[17] = inv.l.vy.y, out[18] = inv.l.vz.y, out[19] = inv.p.y;
+  out[20] = inv.l.vx.z, out[21] = inv.l.vy.z, out[22] = inv.l.vz.z, out[23] = inv.p.z;
+}
