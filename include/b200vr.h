@@ -74,6 +74,8 @@ int b200vr_create(b200vr_t** out, int cuda_device);
 void b200vr_destroy(b200vr_t* h);
 const char* b200vr_last_error(const b200vr_t* h); /* h may be NULL: error of the last failed create */
 void b200vr_default_params(b200vr_params* p);
+/* launch on a caller-owned cudaStream_t (framebuffer_stream, device_impl.cpp:102-111); NULL restores the private stream */
+int b200vr_set_stream(b200vr_t* h, void* cuda_stream);
 
 /* volume: replaces StructuredRegularVolume::load_from_array3d_scalar (volume.cpp:181-257) =
  * CreateArray3DScalarOptix7 (array.cpp:287-351: min/max, u16/i16/f64 -> f32 conversion, 3-D array + texture)
@@ -89,6 +91,17 @@ int b200vr_set_volume_noise(b200vr_t* h, uint32_t seed, const int32_t org[3], in
 int b200vr_get_value_range(b200vr_t* h, float* lo, float* hi); /* original_value_range, volume.cpp:187-189 */
 int b200vr_get_macrocells(b200vr_t* h, int32_t mc_dims[3], float* ranges_or_null, float* majorants_or_null);
 int b200vr_download_volume(b200vr_t* h, float* host_voxels); /* fp32 copy of the resident volume (tests) */
+/* known-answer probe: sample the resident volume at n object-space points (host arrays, 3 floats each) with the given
+ * B200VR_SAMPLER_* and classify through the transfer function exactly as the render kernels do
+ * (sample_volume_object_space + sample_transfer_function, shaders_common.h:186-193,356-367).
+ * values_out: n floats; rgba_out: 4n floats or NULL. */
+int b200vr_probe(b200vr_t* h, const float* points, int64_t n, int sampler, float* values_out, float* rgba_out);
+
+/* fetch-rate micro-benchmark on the resident volume (roofline denominator P_fetch): n_warps bundles of 8x4
+ * parallel rays march `iters` unit steps along dir (voxels/step) inside a footprint^3-voxel cube; reports the CUDA-event
+ * time and the number of trilinear fetches issued. */
+int b200vr_bench_fetch(b200vr_t* h, int sampler, int footprint, int iters, const float dir[3], int ctas_per_sm,
+                       float* ms_out, uint64_t* fetches_out);
 
 /* replaces StructuredRegularVolume::set_transfer_function(vector<float> c, vector<float> o, vec2f r)
  * (volume.cpp:104-129, fed by MainRenderer::set_scene, ovr/renderer.h:299-341): colors = 3*n_colors floats RGB,

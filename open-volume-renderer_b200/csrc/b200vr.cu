@@ -1,0 +1,829 @@
+// b200vr -- host side of the thin C ABI declared in include/b200vr.h. Owns all device state of one renderer
+// (volume array + texture, linear copy, macrocells, TF tables, double-buffered frame) and launches the sm_100a
+// kernels in build.cuh / raymarch.cuh / pathtrace.cuh. No CPU compute path exists: without a CUDA device
+// b200vr_create fails with B200VR_ENODEV.
+#include "../../include/b200vr.h"
+
+#include "build.cuh"
+#include "pathtrace.cuh"
+#include "raymarch.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace b200k;
+
+namespace {
+thread_local std::string g_create_error;
+}
+
+struct b200vr {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string error;
+
+  // volume
+  int nx = 0, ny = 0, nz = 0;
+  float* lin = nullptr;
+  cudaArray_t array = nullptr;
+  cudaTextureObject_t tex = 0;
+  aff3 otw, wto;
+  float data_lo = 0.f, data_hi = 0.f; // original_value_range (volume.cpp:187-189)
+  bool has_volume = false;
+  int vol_type = B200VR_TYPE_FLOAT; // texture element type as the reference would hold it (array.cpp:322-351)
+  // macrocells
+  i3 mc = { 0, 0, 0 };
+  float2* ranges = nullptr;
+  float* majorants = nullptr;
+  int* minmax = nullptr;
+  // transfer function
+  float4* tf_color = nullptr;
+  float* tf_alpha = nullptr;
+  int n_color = 0, n_alpha = 0;
+  float tf_lower = 0.f, tf_upper = 1.f; // lookup window volume.lower/upper (volume.cpp:131-145)
+  bool has_tf = false;
+  // camera
+  f3 cam_pos, cam_dir, cam_hor, cam_ver;
+  bool has_camera = false;
+  bool lookat_valid = false;
+  float la_from[3], la_at[3], la_up[3], la_fovy = 45.f;
+  // params
+  b200vr_params prm;
+  f3 clip_lo = { 0.f, 0.f, 0.f }, clip_hi = { 1.f, 1.f, 1.f };
+  int rank = 0, nranks = 1;
+  // frame: double buffer {rgba, grad} + accumulation (optix7_common.h:256-414, device_impl.cpp:204-241)
+  int width = 0, height = 0;
+  float4* rgba[2] = { nullptr, nullptr };
+  float* grad[2] = { nullptr, nullptr };
+  float4* accum = nullptr;
+  int current = 0;
+  int frame_index = 0;
+  bool reset = true;
+  unsigned int* tile_counter = nullptr;
+  Counters* counters = nullptr;
+};
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      h->error = std::string(#call) + ": " + cudaGetErrorString(e_);                               \
+      return B200VR_ECUDA;                                                                         \
+    }                                                                                              \
+  } while (0)
+
+static int fail(b200vr_t* h, int code, const char* msg)
+{
+  h->error = msg;
+  return code;
+}
+
+static int grid_for(size_t n, int threads, int sm_count)
+{
+  const size_t want = (n + threads - 1) / threads;
+  const size_t cap = (size_t)sm_count * 16;
+  return (int)std::max<size_t>(1, std::min(want, cap));
+}
+
+extern "C" int b200vr_abi_version(void) { return B200VR_ABI_VERSION; }
+
+extern "C" void b200vr_default_params(b200vr_params* p)
+{
+  std::memset(p, 0, sizeof(*p));
+  p->sampling_rate = 1.f;
+  p->base = 1.f;
+  p->spp = 1;
+  p->mode = B200VR_MODE_RAYMARCH;
+  p->shading = B200VR_SHADING_REF;
+  p->sampler = B200VR_SAMPLER_TEX3D;
+  p->skip_empty = 1;
+  p->accumulate = 0;
+  p->max_num_scatters = 24;
+  p->premultiplied = 0;
+  p->light_pos[0] = -907.108f; // params.h:79
+  p->light_pos[1] = 2205.875f;
+  p->light_pos[2] = -400.0267f;
+  p->light_ambient = 1.f;
+}
+
+extern "C" const char* b200vr_last_error(const b200vr_t* h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int b200vr_create(b200vr_t** out, int cuda_device)
+{
+  if (!out) return B200VR_EINVAL;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    g_create_error = std::string("no CUDA device available (") + cudaGetErrorString(e) + "); b200vr has no CPU fallback";
+    return B200VR_ENODEV;
+  }
+  if (cuda_device < 0 || cuda_device >= n) {
+    g_create_error = "cuda_device out of range";
+    return B200VR_EINVAL;
+  }
+  b200vr_t* h = new b200vr();
+  h->device = cuda_device;
+  b200vr_default_params(&h->prm);
+  auto bail = [&](cudaError_t err, const char* what) {
+    g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+    delete h;
+    return B200VR_ECUDA;
+  };
+  if ((e = cudaSetDevice(cuda_device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, cuda_device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+  h->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  h->stream = h->own_stream;
+  if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaEventCreate(&h->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaMalloc(&h->tile_counter, sizeof(unsigned int))) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = cudaMalloc(&h->counters, sizeof(Counters))) != cudaSuccess) return bail(e, "cudaMalloc");
+  if ((e = cudaMalloc(&h->minmax, 2 * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc");
+  *out = h;
+  return B200VR_OK;
+}
+
+static void free_volume(b200vr_t* h)
+{
+  if (h->tex) cudaDestroyTextureObject(h->tex);
+  if (h->array) cudaFreeArray(h->array);
+  cudaFree(h->lin);
+  cudaFree(h->ranges);
+  cudaFree(h->majorants);
+  h->tex = 0;
+  h->array = nullptr;
+  h->lin = nullptr;
+  h->ranges = nullptr;
+  h->majorants = nullptr;
+  h->has_volume = false;
+}
+static void free_frame(b200vr_t* h)
+{
+  for (int i = 0; i < 2; i++) {
+    cudaFree(h->rgba[i]);
+    cudaFree(h->grad[i]);
+    h->rgba[i] = nullptr;
+    h->grad[i] = nullptr;
+  }
+  cudaFree(h->accum);
+  h->accum = nullptr;
+}
+
+extern "C" void b200vr_destroy(b200vr_t* h)
+{
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  free_volume(h);
+  free_frame(h);
+  cudaFree(h->tf_color);
+  cudaFree(h->tf_alpha);
+  cudaFree(h->tile_counter);
+  cudaFree(h->counters);
+  cudaFree(h->minmax);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// volume
+// ---------------------------------------------------------------------------------------------------------------------
+
+static int rebuild_majorants(b200vr_t* h);
+
+// h->lin holds nx*ny*nz fp32 voxels: build the 3-D array + texture (array.cpp:287-309, cuda_buffer.h:248-331) and the
+// macrocell ranges / global range (sp_singlemc.cu:99-120, array.cpp:27-66)
+static int finish_volume(b200vr_t* h, const float obj_to_world[12])
+{
+  const cudaChannelFormatDesc desc = cudaCreateChannelDesc<float>();
+  const cudaExtent ext = make_cudaExtent((size_t)h->nx, (size_t)h->ny, (size_t)h->nz);
+  CK(cudaMalloc3DArray(&h->array, &desc, ext));
+  cudaMemcpy3DParms cp;
+  std::memset(&cp, 0, sizeof(cp));
+  cp.srcPtr = make_cudaPitchedPtr(h->lin, (size_t)h->nx * sizeof(float), (size_t)h->nx, (size_t)h->ny);
+  cp.dstArray = h->array;
+  cp.extent = ext;
+  cp.kind = cudaMemcpyDeviceToDevice;
+  CK(cudaMemcpy3DAsync(&cp, h->stream));
+  cudaResourceDesc rd;
+  std::memset(&rd, 0, sizeof(rd));
+  rd.resType = cudaResourceTypeArray;
+  rd.res.array.array = h->array;
+  cudaTextureDesc td;
+  std::memset(&td, 0, sizeof(td));
+  td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+  td.filterMode = cudaFilterModeLinear;
+  td.readMode = cudaReadModeElementType;
+  td.normalizedCoords = 1;
+  CK(cudaCreateTextureObject(&h->tex, &rd, &td, nullptr));
+
+  h->otw = from_3x4(obj_to_world);
+  h->wto = inverse(h->otw);
+
+  h->mc.x = (h->nx + MC_SIZE - 1) / MC_SIZE;
+  h->mc.y = (h->ny + MC_SIZE - 1) / MC_SIZE;
+  h->mc.z = (h->nz + MC_SIZE - 1) / MC_SIZE;
+  const size_t n_cells = (size_t)h->mc.x * h->mc.y * h->mc.z;
+  CK(cudaMalloc(&h->ranges, n_cells * sizeof(float2)));
+  CK(cudaMalloc(&h->majorants, n_cells * sizeof(float)));
+  CK(cudaMemsetAsync(h->majorants, 0, n_cells * sizeof(float), h->stream));
+  const int init[2] = { 0x7fffffff, (int)0x80000000 };
+  CK(cudaMemcpyAsync(h->minmax, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
+  macrocell_range_kernel<<<(unsigned)n_cells, RANGE_THREADS, 0, h->stream>>>(h->lin, h->nx, h->ny, h->nz, h->mc.x, h->mc.y,
+                                                                              h->mc.z, h->ranges, h->minmax);
+  CK(cudaGetLastError());
+  int mm[2];
+  CK(cudaMemcpyAsync(mm, h->minmax, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->data_lo = ordered_to_float(mm[0]);
+  h->data_hi = ordered_to_float(mm[1]);
+  // load_from_array3d_scalar calls set_value_range(1,-1): lookup window = data range until a TF arrives
+  if (!h->has_tf) {
+    h->tf_lower = h->data_lo;
+    h->tf_upper = h->data_hi;
+  }
+  h->has_volume = true;
+  h->reset = true;
+  if (h->has_tf) return rebuild_majorants(h);
+  return B200VR_OK;
+}
+
+template<typename T>
+static int upload_typed(b200vr_t* h, const void* voxels, size_t n, int on_device)
+{
+  const T* src = (const T*)voxels;
+  T* staged = nullptr;
+  if (!on_device) {
+    CK(cudaMalloc(&staged, n * sizeof(T)));
+    CK(cudaMemcpyAsync(staged, voxels, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    src = staged;
+  }
+  convert_kernel<T><<<grid_for(n, 256, h->sm_count), 256, 0, h->stream>>>(h->lin, src, n);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  if (staged) CK(cudaFree(staged));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_volume(b200vr_t* h, const void* voxels, int type, int nx, int ny, int nz,
+                                 const float obj_to_world[12], int on_device)
+{
+  if (!h) return B200VR_EINVAL;
+  if (!voxels || !obj_to_world || nx <= 0 || ny <= 0 || nz <= 0) return fail(h, B200VR_EINVAL, "set_volume: bad argument");
+  CK(cudaSetDevice(h->device));
+  free_volume(h);
+  h->nx = nx, h->ny = ny, h->nz = nz;
+  const size_t n = (size_t)nx * ny * nz;
+  CK(cudaMalloc(&h->lin, n * sizeof(float)));
+  int rc = B200VR_OK;
+  // 16-bit integers and doubles are converted to plain floats by the reference; 8/32-bit integers stay normalised
+  h->vol_type = (type == B200VR_TYPE_UINT16 || type == B200VR_TYPE_INT16 || type == B200VR_TYPE_DOUBLE) ? B200VR_TYPE_FLOAT : type;
+  switch (type) {
+  case B200VR_TYPE_FLOAT:
+    CK(cudaMemcpyAsync(h->lin, voxels, n * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                       h->stream));
+    break;
+  case B200VR_TYPE_UINT8: rc = upload_typed<uint8_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_INT8: rc = upload_typed<int8_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_UINT16: rc = upload_typed<uint16_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_INT16: rc = upload_typed<int16_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_UINT32: rc = upload_typed<uint32_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_INT32: rc = upload_typed<int32_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_DOUBLE: rc = upload_typed<double>(h, voxels, n, on_device); break;
+  default: return fail(h, B200VR_EINVAL, "set_volume: unknown value type"); // array.cpp:347
+  }
+  if (rc != B200VR_OK) return rc;
+  return finish_volume(h, obj_to_world);
+}
+
+extern "C" int b200vr_set_volume_noise(b200vr_t* h, uint32_t seed, const int32_t org[3], int nx, int ny, int nz,
+                                       const float obj_to_world[12])
+{
+  if (!h) return B200VR_EINVAL;
+  if (!org || !obj_to_world || nx <= 0 || ny <= 0 || nz <= 0) return fail(h, B200VR_EINVAL, "set_volume_noise: bad argument");
+  CK(cudaSetDevice(h->device));
+  free_volume(h);
+  h->nx = nx, h->ny = ny, h->nz = nz;
+  const size_t n = (size_t)nx * ny * nz;
+  CK(cudaMalloc(&h->lin, n * sizeof(float)));
+  h->vol_type = B200VR_TYPE_FLOAT;
+  noise_kernel<<<grid_for(n, 256, h->sm_count), 256, 0, h->stream>>>(h->lin, seed, org[0], org[1], org[2], nx, ny, nz);
+  CK(cudaGetLastError());
+  return finish_volume(h, obj_to_world);
+}
+
+extern "C" int b200vr_get_value_range(b200vr_t* h, float* lo, float* hi)
+{
+  if (!h || !lo || !hi) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "get_value_range: no volume");
+  *lo = h->data_lo;
+  *hi = h->data_hi;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_get_macrocells(b200vr_t* h, int32_t mc_dims[3], float* ranges, float* majorants)
+{
+  if (!h || !mc_dims) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "get_macrocells: no volume");
+  CK(cudaSetDevice(h->device));
+  mc_dims[0] = h->mc.x, mc_dims[1] = h->mc.y, mc_dims[2] = h->mc.z;
+  const size_t n_cells = (size_t)h->mc.x * h->mc.y * h->mc.z;
+  if (ranges) CK(cudaMemcpy(ranges, h->ranges, n_cells * sizeof(float2), cudaMemcpyDeviceToHost));
+  if (majorants) CK(cudaMemcpy(majorants, h->majorants, n_cells * sizeof(float), cudaMemcpyDeviceToHost));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_download_volume(b200vr_t* h, float* host_voxels)
+{
+  if (!h || !host_voxels) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "download_volume: no volume");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpy(host_voxels, h->lin, (size_t)h->nx * h->ny * h->nz * sizeof(float), cudaMemcpyDeviceToHost));
+  return B200VR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// transfer function, camera, parameters
+// ---------------------------------------------------------------------------------------------------------------------
+
+// integer_normalize(float, ValueType) (array.h:64-106): the TF range arrives in file units
+static float integer_normalize(float v, int type)
+{
+  switch (type) {
+  case B200VR_TYPE_UINT8: return (float)(uint8_t)v / 255.f;
+  case B200VR_TYPE_INT8: return std::max((float)(int8_t)v / 127.f, -1.f);
+  case B200VR_TYPE_UINT32: return (float)(uint32_t)v / 4294967295.f;
+  case B200VR_TYPE_INT32: return std::max((float)(int32_t)v / 2147483647.f, -1.f);
+  default: return v;
+  }
+}
+
+static int rebuild_majorants(b200vr_t* h)
+{
+  const int n_cells = h->mc.x * h->mc.y * h->mc.z;
+  const int threads = 256;
+  const int grid = std::max(1, std::min((n_cells + threads - 1) / threads, h->sm_count * 8));
+  majorant_kernel<<<grid, threads, (size_t)h->n_alpha * sizeof(float), h->stream>>>(h->ranges, n_cells, h->tf_alpha, h->n_alpha,
+                                                                                     h->tf_lower, h->tf_upper, h->majorants);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, int n_colors, const float* alphas, int n_alphas,
+                                            float range_lo, float range_hi)
+{
+  if (!h) return B200VR_EINVAL;
+  if (!colors || !alphas || n_colors <= 0 || n_alphas <= 0) return fail(h, B200VR_EINVAL, "set_transfer_function: empty table");
+  if (tf_shared_bytes(n_colors, n_alphas) > 200 * 1024) return fail(h, B200VR_EINVAL, "set_transfer_function: table exceeds shared memory");
+  CK(cudaSetDevice(h->device));
+  // volume.cpp:104-121: colours -> float4(r,g,b,1); alphas = every second float of the (position, alpha) pairs
+  std::vector<float4> c((size_t)n_colors);
+  for (int i = 0; i < n_colors; i++) c[i] = make_float4(colors[3 * i], colors[3 * i + 1], colors[3 * i + 2], 1.f);
+  std::vector<float> a((size_t)n_alphas);
+  for (int i = 0; i < n_alphas; i++) a[i] = alphas[2 * i + 1];
+  cudaFree(h->tf_color);
+  cudaFree(h->tf_alpha);
+  h->tf_color = nullptr;
+  h->tf_alpha = nullptr;
+  CK(cudaMalloc(&h->tf_color, c.size() * sizeof(float4)));
+  CK(cudaMalloc(&h->tf_alpha, a.size() * sizeof(float)));
+  CK(cudaMemcpy(h->tf_color, c.data(), c.size() * sizeof(float4), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h->tf_alpha, a.data(), a.size() * sizeof(float), cudaMemcpyHostToDevice));
+  h->n_color = n_colors;
+  h->n_alpha = n_alphas;
+  // set_value_range (volume.cpp:131-145): only a non-empty range replaces the lookup window
+  if (range_hi >= range_lo) {
+    h->tf_upper = integer_normalize(range_hi, h->vol_type);
+    h->tf_lower = integer_normalize(range_lo, h->vol_type);
+  }
+  h->has_tf = true;
+  h->reset = true;
+  if (h->has_volume) return rebuild_majorants(h);
+  return B200VR_OK;
+}
+
+static void derive_camera(b200vr_t* h)
+{
+  // device_impl.cpp:125-136; tan is evaluated in double on the host like the reference
+  const float t = 2.f * (float)std::tan((double)(h->la_fovy * 0.5f * (float)M_PI / 180.f));
+  const float aspect = (float)h->width / (float)h->height;
+  const f3 from = mk3(h->la_from[0], h->la_from[1], h->la_from[2]), at = mk3(h->la_at[0], h->la_at[1], h->la_at[2]);
+  const f3 up = mk3(h->la_up[0], h->la_up[1], h->la_up[2]);
+  h->cam_pos = from;
+  h->cam_dir = normalize3(at - from);
+  h->cam_hor = (t * aspect) * normalize3(cross3(h->cam_dir, up));
+  h->cam_ver = cross3(h->cam_hor, h->cam_dir) / aspect;
+  h->has_camera = true;
+}
+
+extern "C" int b200vr_set_camera(b200vr_t* h, const float position[3], const float direction[3], const float horizontal[3],
+                                 const float vertical[3])
+{
+  if (!h || !position || !direction || !horizontal || !vertical) return B200VR_EINVAL;
+  h->cam_pos = mk3(position[0], position[1], position[2]);
+  h->cam_dir = mk3(direction[0], direction[1], direction[2]);
+  h->cam_hor = mk3(horizontal[0], horizontal[1], horizontal[2]);
+  h->cam_ver = mk3(vertical[0], vertical[1], vertical[2]);
+  h->has_camera = true;
+  h->lookat_valid = false;
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_camera_lookat(b200vr_t* h, const float from[3], const float at[3], const float up[3], float fovy)
+{
+  if (!h || !from || !at || !up) return B200VR_EINVAL;
+  for (int i = 0; i < 3; i++) h->la_from[i] = from[i], h->la_at[i] = at[i], h->la_up[i] = up[i];
+  h->la_fovy = fovy;
+  h->lookat_valid = true;
+  if (h->width > 0 && h->height > 0) derive_camera(h);
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_get_camera(b200vr_t* h, float position[3], float direction[3], float horizontal[3], float vertical[3])
+{
+  if (!h) return B200VR_EINVAL;
+  if (!h->has_camera) return fail(h, B200VR_ESTATE, "get_camera: no camera");
+  const f3 v[4] = { h->cam_pos, h->cam_dir, h->cam_hor, h->cam_ver };
+  float* o[4] = { position, direction, horizontal, vertical };
+  for (int i = 0; i < 4; i++)
+    if (o[i]) o[i][0] = v[i].x, o[i][1] = v[i].y, o[i][2] = v[i].z;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_params(b200vr_t* h, const b200vr_params* p)
+{
+  if (!h || !p) return B200VR_EINVAL;
+  if (!(p->sampling_rate > 0.f)) return fail(h, B200VR_EINVAL, "set_params: sampling_rate must be positive");
+  if (p->spp < 1) return fail(h, B200VR_EINVAL, "set_params: spp must be >= 1");
+  if (p->mode != B200VR_MODE_RAYMARCH && p->mode != B200VR_MODE_PATHTRACE) return fail(h, B200VR_EINVAL, "set_params: bad mode");
+  if (p->shading != B200VR_SHADING_NONE && p->shading != B200VR_SHADING_REF) return fail(h, B200VR_EINVAL, "set_params: bad shading");
+  if (p->sampler != B200VR_SAMPLER_TEX3D && p->sampler != B200VR_SAMPLER_MANUAL) return fail(h, B200VR_EINVAL, "set_params: bad sampler");
+  const float base = p->base > 0.f ? p->base : h->prm.base; // set_sampling_rate(r, b): b <= 0 keeps base (volume.cpp:156-162)
+  h->prm = *p;
+  h->prm.base = base;
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_get_params(b200vr_t* h, b200vr_params* p)
+{
+  if (!h || !p) return B200VR_EINVAL;
+  *p = h->prm;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_resize(b200vr_t* h, int width, int height)
+{
+  if (!h) return B200VR_EINVAL;
+  if (width <= 0 || height <= 0) return fail(h, B200VR_EINVAL, "resize: size must be positive");
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  if (width != h->width || height != h->height) {
+    free_frame(h);
+    const size_t n = (size_t)width * height;
+    for (int i = 0; i < 2; i++) {
+      CK(cudaMalloc(&h->rgba[i], n * sizeof(float4)));
+      CK(cudaMalloc(&h->grad[i], n * 3 * sizeof(float)));
+      CK(cudaMemset(h->rgba[i], 0, n * sizeof(float4)));
+      CK(cudaMemset(h->grad[i], 0, n * 3 * sizeof(float)));
+    }
+    CK(cudaMalloc(&h->accum, n * sizeof(float4)));
+    CK(cudaMemset(h->accum, 0, n * sizeof(float4)));
+    h->width = width;
+    h->height = height;
+  }
+  if (h->lookat_valid) derive_camera(h); // "camera.update() || framebuffer_size_updated", device_impl.cpp:125
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_reset_accumulation(b200vr_t* h)
+{
+  if (!h) return B200VR_EINVAL;
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_clip_box(b200vr_t* h, const float lo[3], const float hi[3])
+{
+  if (!h || !lo || !hi) return B200VR_EINVAL;
+  for (int i = 0; i < 3; i++)
+    if (!(hi[i] > lo[i])) return fail(h, B200VR_EINVAL, "set_clip_box: empty box");
+  h->clip_lo = mk3(lo[0], lo[1], lo[2]);
+  h->clip_hi = mk3(hi[0], hi[1], hi[2]);
+  h->reset = true;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
+{
+  if (!h) return B200VR_EINVAL;
+  if (nranks < 1 || rank < 0 || rank >= nranks) return fail(h, B200VR_EINVAL, "set_tile_partition: bad rank");
+  h->rank = rank;
+  h->nranks = nranks;
+  h->reset = true;
+  return B200VR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// render
+// ---------------------------------------------------------------------------------------------------------------------
+
+typedef void (*render_kernel_t)(const LaunchParams);
+
+static render_kernel_t pick_kernel(const b200vr_params& p)
+{
+  if (p.mode == B200VR_MODE_PATHTRACE)
+    return p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
+  const int key = (p.shading == B200VR_SHADING_REF ? 4 : 0) | (p.sampler == B200VR_SAMPLER_MANUAL ? 2 : 0) | (p.skip_empty ? 1 : 0);
+  switch (key) {
+  case 0: return raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, false>;
+  case 1: return raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, true>;
+  case 2: return raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, false>;
+  case 3: return raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, true>;
+  case 4: return raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, false>;
+  case 5: return raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, true>;
+  case 6: return raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, false>;
+  default: return raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, true>;
+  }
+}
+
+static void fill_launch_params(b200vr_t* h, LaunchParams& P)
+{
+  std::memset(&P, 0, sizeof(P));
+  P.tex = h->tex;
+  P.lin = h->lin;
+  P.nx = h->nx, P.ny = h->ny, P.nz = h->nz;
+  P.rdim = mk3(1.f) / mk3((float)h->nx, (float)h->ny, (float)h->nz);
+  P.otw = h->otw;
+  P.wto = h->wto;
+  P.clip_lo = h->clip_lo;
+  P.clip_hi = h->clip_hi;
+  P.tf_color = h->tf_color;
+  P.tf_alpha = h->tf_alpha;
+  P.n_color = h->n_color, P.n_alpha = h->n_alpha;
+  P.tf_lower = h->tf_lower, P.tf_upper = h->tf_upper;
+  P.tf_scale = 1.f / (h->tf_upper - h->tf_lower); // volume.scale (volume.cpp:145)
+  P.majorants = h->majorants;
+  P.mc = h->mc;
+  P.cells_per_unit = mk3((float)h->nx, (float)h->ny, (float)h->nz) / (float)MC_SIZE;
+  {
+    const f3 spac = mk3((float)MC_SIZE) / mk3((float)h->nx, (float)h->ny, (float)h->nz); // sp_singlemc.cu:102-103
+    P.spac_rcp = mk3(1.f) / spac;
+  }
+  P.step = 1.f / h->prm.sampling_rate; // volume.cpp:172-179
+  P.base = h->prm.base;
+  P.cam_pos = h->cam_pos, P.cam_dir = h->cam_dir, P.cam_hor = h->cam_hor, P.cam_ver = h->cam_ver;
+  {
+    // get_xfm_world_to_camera (shaders_common.h:276-289); kernels want transpose(inverse(l)) for xfmNormal
+    const f3 x = normalize3(h->cam_hor), y = normalize3(h->cam_ver), z = -normalize3(h->cam_dir);
+    lin3 l;
+    l.vx = mk3(x.x, y.x, z.x);
+    l.vy = mk3(x.y, y.y, z.y);
+    l.vz = mk3(x.z, y.z, z.z);
+    P.wtc = transposed(inverse(l));
+  }
+  P.light_dir = normalize3(mk3(h->prm.light_pos[0], h->prm.light_pos[1], h->prm.light_pos[2]));
+  P.light_ambient = h->prm.light_ambient;
+  P.max_num_scatters = h->prm.max_num_scatters;
+  P.rgba = h->rgba[h->current];
+  P.grad = h->grad[h->current];
+  P.accum = h->accum;
+  P.width = h->width, P.height = h->height;
+  P.rw = 1.f / (float)h->width, P.rh = 1.f / (float)h->height;
+  P.frame_index = h->frame_index;
+  P.spp = h->prm.spp;
+  P.accumulate = h->prm.accumulate;
+  P.premultiplied = h->prm.premultiplied;
+  P.super_w = (h->width + SUPER_TILE_W - 1) / SUPER_TILE_W;
+  P.super_h = (h->height + SUPER_TILE_H - 1) / SUPER_TILE_H;
+  P.rank = h->rank, P.nranks = h->nranks;
+  P.n_warp_tiles = owned_super_tiles(h->rank, h->nranks, P.super_w * P.super_h) * WARP_TILES_PER_SUPER;
+  P.tile_counter = h->tile_counter;
+  P.counters = h->counters;
+}
+
+extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
+{
+  if (!h) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "render: no volume");
+  if (!h->has_tf) return fail(h, B200VR_ESTATE, "render: no transfer function");
+  if (!h->has_camera) return fail(h, B200VR_ESTATE, "render: no camera");
+  if (h->width <= 0 || h->height <= 0) return fail(h, B200VR_ESTATE, "render: framebuffer size not set");
+  CK(cudaSetDevice(h->device));
+  // accumulation bookkeeping (device_impl.cpp:225-241)
+  if (h->prm.accumulate && h->reset) h->frame_index = 0;
+  h->reset = false;
+  h->frame_index++;
+
+  LaunchParams P;
+  fill_launch_params(h, P);
+  const render_kernel_t kernel = pick_kernel(h->prm);
+  const size_t smem = tf_shared_bytes(h->n_color, h->n_alpha);
+  if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kernel, RENDER_THREADS, smem));
+  if (per_sm < 1) return fail(h, B200VR_ECUDA, "render: kernel does not fit on an SM");
+  const int warps_per_cta = RENDER_THREADS / 32;
+  const int want = (P.n_warp_tiles + warps_per_cta - 1) / warps_per_cta;
+  const int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
+  CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
+  CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
+  CK(cudaEventRecord(h->ev0, h->stream));
+  if (P.n_warp_tiles > 0) {
+    void* args[] = { (void*)&P };
+    CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3(RENDER_THREADS), args, smem, h->stream));
+  }
+  CK(cudaEventRecord(h->ev1, h->stream));
+  Counters c;
+  CK(cudaMemcpyAsync(&c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream)); // synchronous like DeviceOptix7::render (device.cpp:34-43)
+  if (stats) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    stats->ms = ms;
+    stats->primary_samples = c.primary_samples;
+    stats->shadow_samples = c.shadow_samples;
+    stats->gradient_fetches = c.gradient_fetches;
+    stats->delta_samples = c.delta_samples;
+    stats->rays = c.rays;
+    stats->frame_index = h->frame_index;
+    stats->kernel_launches = P.n_warp_tiles > 0 ? 1 : 0;
+  }
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev)
+{
+  if (!h) return B200VR_EINVAL;
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "map: framebuffer size not set");
+  if (rgba_dev) *rgba_dev = h->rgba[h->current];
+  if (grad_dev) *grad_dev = h->grad[h->current];
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_swap(b200vr_t* h)
+{
+  if (!h) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  h->current ^= 1;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_download(b200vr_t* h, float* rgba_host, float* grad_host)
+{
+  if (!h || !rgba_host) return B200VR_EINVAL;
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "download: framebuffer size not set");
+  CK(cudaSetDevice(h->device));
+  const size_t n = (size_t)h->width * h->height;
+  CK(cudaMemcpyAsync(rgba_host, h->rgba[h->current], n * sizeof(float4), cudaMemcpyDeviceToHost, h->stream));
+  if (grad_host) CK(cudaMemcpyAsync(grad_host, h->grad[h->current], n * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return B200VR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// multi-GPU exchange helpers
+// ---------------------------------------------------------------------------------------------------------------------
+
+extern "C" int64_t b200vr_tile_slice_floats(b200vr_t* h, int rank, int nranks)
+{
+  if (!h || h->width <= 0 || nranks < 1 || rank < 0 || rank >= nranks) return -1;
+  const int sw = (h->width + SUPER_TILE_W - 1) / SUPER_TILE_W, sh = (h->height + SUPER_TILE_H - 1) / SUPER_TILE_H;
+  return (int64_t)owned_super_tiles(rank, nranks, sw * sh) * SUPER_TILE_W * SUPER_TILE_H * 4;
+}
+
+static int tile_copy(b200vr_t* h, float* slice, int rank, int nranks, bool pack)
+{
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "tile copy: framebuffer size not set");
+  CK(cudaSetDevice(h->device));
+  const int sw = (h->width + SUPER_TILE_W - 1) / SUPER_TILE_W, sh = (h->height + SUPER_TILE_H - 1) / SUPER_TILE_H;
+  const int n_owned = owned_super_tiles(rank, nranks, sw * sh);
+  if (n_owned == 0) return B200VR_OK;
+  const size_t n = (size_t)n_owned * SUPER_TILE_W * SUPER_TILE_H;
+  const int grid = grid_for(n, 256, h->sm_count);
+  if (pack)
+    tile_copy_kernel<true><<<grid, 256, 0, h->stream>>>(h->rgba[h->current], (float4*)slice, h->width, h->height, sw, rank, nranks, n_owned);
+  else
+    tile_copy_kernel<false><<<grid, 256, 0, h->stream>>>(h->rgba[h->current], (float4*)slice, h->width, h->height, sw, rank, nranks, n_owned);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_pack_tiles(b200vr_t* h, float* slice_dev)
+{
+  if (!h || !slice_dev) return B200VR_EINVAL;
+  return tile_copy(h, slice_dev, h->rank, h->nranks, true);
+}
+
+extern "C" int b200vr_unpack_tiles(b200vr_t* h, const float* slice_dev, int rank, int nranks)
+{
+  if (!h || !slice_dev || nranks < 1 || rank < 0 || rank >= nranks) return B200VR_EINVAL;
+  return tile_copy(h, const_cast<float*>(slice_dev), rank, nranks, false);
+}
+
+extern "C" int b200vr_composite_over(b200vr_t* h, const float* front_dev, const float* back_dev, float* out_dev, int64_t n_pixels)
+{
+  if (!h || !front_dev || !back_dev || !out_dev || n_pixels < 0) return B200VR_EINVAL;
+  if (n_pixels == 0) return B200VR_OK;
+  CK(cudaSetDevice(h->device));
+  composite_over_kernel<<<grid_for((size_t)n_pixels, 256, h->sm_count), 256, 0, h->stream>>>(
+    (const float4*)front_dev, (const float4*)back_dev, (float4*)out_dev, (size_t)n_pixels);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64_t n_pixels)
+{
+  if (!h || !rgba_dev || n_pixels < 0) return B200VR_EINVAL;
+  if (n_pixels == 0) return B200VR_OK;
+  CK(cudaSetDevice(h->device));
+  finalize_premultiplied_kernel<<<grid_for((size_t)n_pixels, 256, h->sm_count), 256, 0, h->stream>>>((float4*)rgba_dev, (size_t)n_pixels);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_probe(b200vr_t* h, const float* points, int64_t n, int sampler, float* values_out, float* rgba_out)
+{
+  if (!h || !points || !values_out || n < 0) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "probe: no volume");
+  if (rgba_out && !h->has_tf) return fail(h, B200VR_ESTATE, "probe: no transfer function");
+  if (n == 0) return B200VR_OK;
+  CK(cudaSetDevice(h->device));
+  float *d_pts = nullptr, *d_val = nullptr;
+  float4* d_rgba = nullptr;
+  CK(cudaMalloc(&d_pts, (size_t)n * 3 * sizeof(float)));
+  CK(cudaMalloc(&d_val, (size_t)n * sizeof(float)));
+  if (rgba_out) CK(cudaMalloc(&d_rgba, (size_t)n * sizeof(float4)));
+  CK(cudaMemcpyAsync(d_pts, points, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+  LaunchParams P;
+  const bool cam = h->has_camera;
+  if (!cam) h->cam_pos = mk3(0.f), h->cam_dir = mk3(0.f, 0.f, 1.f), h->cam_hor = mk3(1.f, 0.f, 0.f), h->cam_ver = mk3(0.f, 1.f, 0.f);
+  fill_launch_params(h, P);
+  const size_t smem = rgba_out ? tf_shared_bytes(h->n_color, h->n_alpha) : 0;
+  if (!rgba_out) P.n_color = P.n_alpha = 0;
+  const void* k = sampler == B200VR_SAMPLER_MANUAL ? (const void*)probe_kernel<SAMPLER_MANUAL> : (const void*)probe_kernel<SAMPLER_TEX3D>;
+  if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long nn = n;
+  void* args[] = { (void*)&P, (void*)&d_pts, (void*)&nn, (void*)&d_val, (void*)&d_rgba };
+  CK(cudaLaunchKernel(k, dim3((unsigned)grid_for((size_t)n, 128, h->sm_count)), dim3(128), args, smem, h->stream));
+  CK(cudaMemcpyAsync(values_out, d_val, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  if (rgba_out) CK(cudaMemcpyAsync(rgba_out, d_rgba, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  cudaFree(d_pts);
+  cudaFree(d_val);
+  cudaFree(d_rgba);
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_bench_fetch(b200vr_t* h, int sampler, int footprint, int iters, const float dir[3], int ctas_per_sm,
+                                  float* ms_out, uint64_t* fetches_out)
+{
+  if (!h || !dir || !ms_out || !fetches_out || iters <= 0 || ctas_per_sm <= 0) return B200VR_EINVAL;
+  if (!h->has_volume) return fail(h, B200VR_ESTATE, "bench_fetch: no volume");
+  const int min_dim = std::min(h->nx, std::min(h->ny, h->nz));
+  if (footprint < 8 || footprint > min_dim) return fail(h, B200VR_EINVAL, "bench_fetch: footprint must be in [8, min(dims)]");
+  CK(cudaSetDevice(h->device));
+  LaunchParams P;
+  if (!h->has_camera) h->cam_pos = mk3(0.f), h->cam_dir = mk3(0.f, 0.f, 1.f), h->cam_hor = mk3(1.f, 0.f, 0.f), h->cam_ver = mk3(0.f, 1.f, 0.f);
+  fill_launch_params(h, P);
+  const void* k = sampler == B200VR_SAMPLER_MANUAL ? (const void*)fetch_bench_kernel<SAMPLER_MANUAL> : (const void*)fetch_bench_kernel<SAMPLER_TEX3D>;
+  float* sink = (float*)h->counters;
+  float dx = dir[0], dy = dir[1], dz = dir[2];
+  const int grid = h->sm_count * ctas_per_sm;
+  void* args[] = { (void*)&P, (void*)&footprint, (void*)&iters, (void*)&dx, (void*)&dy, (void*)&dz, (void*)&sink };
+  CK(cudaLaunchKernel(k, dim3((unsigned)grid), dim3(RENDER_THREADS), args, 0, h->stream)); // warm-up
+  CK(cudaEventRecord(h->ev0, h->stream));
+  CK(cudaLaunchKernel(k, dim3((unsigned)grid), dim3(RENDER_THREADS), args, 0, h->stream));
+  CK(cudaEventRecord(h->ev1, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaEventElapsedTime(ms_out, h->ev0, h->ev1));
+  *fetches_out = (uint64_t)grid * RENDER_THREADS * (uint64_t)iters;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_stream(b200vr_t* h, void* cuda_stream)
+{
+  if (!h) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+  return B200VR_OK;
+}

@@ -1,0 +1,198 @@
+// Set-up and exchange kernels of the B200 volume device (sm_100a): synthetic volume, type conversion, macrocell value
+// ranges + global range, majorants, sort-first tile pack/unpack, sort-last OVER compositing.
+// Reference counterparts: value_range_kernel / majorant_kernel (ovr/devices/optix7/accel/sp_singlemc.cu:10-97),
+// compute_scalar_range + convert_array1d (ovr/devices/optix7/array.cpp:27-90), alpha_blend (shaders_common.h:329-337).
+#pragma once
+#include "launch_params.cuh"
+
+namespace b200k {
+
+// ---- synthetic volume noise(seed): integer-exact fBm value noise -------------------------------------
+__device__ __forceinline__ uint32_t fmix32(uint32_t h)
+{
+  h ^= h >> 16;
+  h *= 0x85ebca6bu;
+  h ^= h >> 13;
+  h *= 0xc2b2ae35u;
+  h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ unsigned long long noise_lattice(uint32_t seed, uint32_t a, uint32_t b, uint32_t c, uint32_t o)
+{
+  return fmix32(seed ^ (a * 73856093u) ^ (b * 19349663u) ^ (c * 83492791u) ^ (o * 0x9E3779B9u)) >> 16;
+}
+__device__ __forceinline__ float noise_voxel(uint32_t seed, uint32_t x, uint32_t y, uint32_t z)
+{
+  unsigned long long sum = 0;
+#pragma unroll
+  for (uint32_t o = 0; o < 4; o++) {
+    const uint32_t sh = 6 - o, P = 1u << sh;
+    const uint32_t a = x >> sh, b = y >> sh, c = z >> sh;
+    const unsigned long long fx = x & (P - 1), fy = y & (P - 1), fz = z & (P - 1);
+    unsigned long long acc = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < 8; k++) {
+      const uint32_t dx = k & 1, dy = (k >> 1) & 1, dz = k >> 2;
+      const unsigned long long w = (dx ? fx : P - fx) * (dy ? fy : P - fy) * (dz ? fz : P - fz);
+      acc += w * noise_lattice(seed, a + dx, b + dy, c + dz, o);
+    }
+    sum += (unsigned long long)(8u >> o) * (acc << (3 * o));
+  }
+  return (float)((double)sum / (double)(15ull * 65536ull * 262144ull));
+}
+
+__global__ void noise_kernel(float* __restrict__ out, uint32_t seed, int ox, int oy, int oz, int nx, int ny, int nz)
+{
+  const size_t n = (size_t)nx * ny * nz;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % nx), y = (int)((i / nx) % ny), z = (int)(i / ((size_t)nx * ny));
+    out[i] = noise_voxel(seed, (uint32_t)(ox + x), (uint32_t)(oy + y), (uint32_t)(oz + z));
+  }
+}
+
+// ---- typed volume -> fp32 (array.cpp:68-108,300-306,335-346; array.h:64-106) ---------------------------------------
+// 8/32-bit integers are read by the reference through cudaReadModeNormalizedFloat (value / type-max, signed clamped at
+// -1); 16-bit integers and doubles are cast to float without normalisation.
+template<typename T> __device__ __forceinline__ float to_f32(T v) { return (float)v; }
+template<> __device__ __forceinline__ float to_f32<uint8_t>(uint8_t v) { return (float)v / 255.f; }
+template<> __device__ __forceinline__ float to_f32<int8_t>(int8_t v) { return fmaxf((float)v / 127.f, -1.f); }
+template<> __device__ __forceinline__ float to_f32<uint32_t>(uint32_t v) { return (float)v / 4294967295.f; }
+template<> __device__ __forceinline__ float to_f32<int32_t>(int32_t v) { return fmaxf((float)v / 2147483647.f, -1.f); }
+
+template<typename T>
+__global__ void convert_kernel(float* __restrict__ out, const T* __restrict__ in, size_t n)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = to_f32<T>(in[i]);
+}
+
+// ---- macrocell value ranges: one CTA per macrocell, lanes along x, warps over (y,z) rows --------------------------
+// Range over voxels 16c-2 .. 16c+17 (clamped): the tri-lerp footprint of every position in the cell plus slack
+// (the reference kernel, sp_singlemc.cu:36-42, misses the upper apron). Also reduces the global
+// [min,max] (compute_scalar_range, array.cpp:27-66) through ordered-int atomics.
+__device__ __forceinline__ int float_to_ordered(float f)
+{
+  const int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__host__ __device__ __forceinline__ float ordered_to_float(int i)
+{
+  const int j = i >= 0 ? i : i ^ 0x7fffffff;
+#ifdef __CUDA_ARCH__
+  return __int_as_float(j);
+#else
+  float f;
+  memcpy(&f, &j, sizeof(f));
+  return f;
+#endif
+}
+
+constexpr int MC_APRON = 2;
+constexpr int RANGE_THREADS = 256;
+
+__global__ void __launch_bounds__(RANGE_THREADS)
+macrocell_range_kernel(const float* __restrict__ vol, int nx, int ny, int nz, int mx, int my, int mz,
+                       float2* __restrict__ ranges, int* __restrict__ global_minmax)
+{
+  const int cell = blockIdx.x;
+  const int cx = cell % mx, cy = (cell / mx) % my, cz = cell / (mx * my);
+  const int bx = max(cx * MC_SIZE - MC_APRON, 0), ex = min(cx * MC_SIZE + MC_SIZE + MC_APRON, nx);
+  const int by = max(cy * MC_SIZE - MC_APRON, 0), ey = min(cy * MC_SIZE + MC_SIZE + MC_APRON, ny);
+  const int bz = max(cz * MC_SIZE - MC_APRON, 0), ez = min(cz * MC_SIZE + MC_SIZE + MC_APRON, nz);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RANGE_THREADS / 32;
+  const int rows_y = ey - by, rows = rows_y * (ez - bz);
+  float lo = INFINITY, hi = -INFINITY;
+  for (int r = warp; r < rows; r += nwarps) {
+    const int y = by + r % rows_y, z = bz + r / rows_y;
+    const float* row = vol + ((size_t)z * ny + y) * nx;
+    const int x = bx + lane;
+    if (x < ex) {
+      const float v = __ldg(row + x);
+      lo = fminf(lo, v);
+      hi = fmaxf(hi, v);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  __shared__ float s_lo[RANGE_THREADS / 32], s_hi[RANGE_THREADS / 32];
+  if (lane == 0) {
+    s_lo[warp] = lo;
+    s_hi[warp] = hi;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < nwarps; w++) {
+      lo = fminf(lo, s_lo[w]);
+      hi = fmaxf(hi, s_hi[w]);
+    }
+    ranges[cell] = make_float2(lo, hi);
+    atomicMin(global_minmax + 0, float_to_ordered(lo));
+    atomicMax(global_minmax + 1, float_to_ordered(hi));
+  }
+}
+
+// ---- majorants: max of the opacity table over the (+-1 entry padded) index range of the cell's value range ---------
+// majorant_kernel (sp_singlemc.cu:56-97) with its defects fixed: whole table staged by all threads
+// before the barrier, index clamped before the float->int conversion, lookup window used for normalisation.
+__global__ void majorant_kernel(const float2* __restrict__ ranges, int n_cells, const float* __restrict__ alphas, int n_alpha,
+                                float win_lo, float win_hi, float* __restrict__ majorants)
+{
+  extern __shared__ float s_alpha[];
+  for (int i = threadIdx.x; i < n_alpha; i += blockDim.x) s_alpha[i] = alphas[i];
+  __syncthreads();
+  const float rcp = 1.f / (win_hi - win_lo);
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cells; c += gridDim.x * blockDim.x) {
+    const float2 r = ranges[c];
+    const float lo = __fmul_rn(__fsub_rn(clampf(r.x, win_lo, win_hi), win_lo), rcp);
+    const float hi = __fmul_rn(__fsub_rn(clampf(r.y, win_lo, win_hi), win_lo), rcp);
+    float fl = floorf(__fmaf_rn(lo, (float)(n_alpha - 1), 0.5f)) - 1.f;
+    float fh = floorf(__fmaf_rn(hi, (float)(n_alpha - 1), 0.5f)) + 1.f;
+    fl = clampf(fl, 0.f, (float)(n_alpha - 1));
+    fh = clampf(fh, 0.f, (float)(n_alpha - 1));
+    float m = 0.f;
+    for (int k = (int)fl; k <= (int)fh; k++) m = fmaxf(m, s_alpha[k]);
+    majorants[c] = m;
+  }
+}
+
+// ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------
+// slice layout: [owned super tile m][y in 32][x in 64][rgba]; pixels outside the image are zero in the slice
+template<bool PACK>
+__global__ void tile_copy_kernel(float4* __restrict__ frame, float4* __restrict__ slice, int width, int height, int super_w,
+                                 int rank, int nranks, int n_owned)
+{
+  const size_t n = (size_t)n_owned * SUPER_TILE_W * SUPER_TILE_H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / (SUPER_TILE_W * SUPER_TILE_H)), r = (int)(i % (SUPER_TILE_W * SUPER_TILE_H));
+    const int s = rank + m * nranks;
+    const int x = (s % super_w) * SUPER_TILE_W + r % SUPER_TILE_W, y = (s / super_w) * SUPER_TILE_H + r / SUPER_TILE_W;
+    const bool inb = x < width && y < height;
+    if (PACK)
+      slice[i] = inb ? frame[(size_t)y * width + x] : make_float4(0.f, 0.f, 0.f, 0.f);
+    else if (inb)
+      frame[(size_t)y * width + x] = slice[i];
+  }
+}
+
+// ---- sort-last: front OVER back on premultiplied float4; `back` may live on a peer GPU (NVLink P2P ld.global) ------
+__global__ void composite_over_kernel(const float4* __restrict__ front, const float4* __restrict__ back, float4* __restrict__ out,
+                                      size_t n)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 f = front[i], b = back[i];
+    const float tr = 1.f - f.w;
+    out[i] = make_float4(f.x + tr * b.x, f.y + tr * b.y, f.z + tr * b.z, f.w + tr * b.w);
+  }
+}
+__global__ void finalize_premultiplied_kernel(float4* __restrict__ px, size_t n)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 p = px[i];
+    px[i] = p.w > 0.f ? make_float4(p.x / p.w, p.y / p.w, p.z / p.w, p.w) : make_float4(0.f, 0.f, 0.f, p.w);
+  }
+}
+
+} // namespace b200k

@@ -7,7 +7,7 @@
 #include <stdint.h>
 #include <float.h>
 
-namespace b200vr {
+namespace b200k {
 
 struct f3 { float x, y, z; };
 struct i3 { int x, y, z; };
@@ -35,7 +35,7 @@ __host__ __device__ __forceinline__ f3 clamp01(f3 v) { return mk3(clamp01(v.x), 
 struct lin3 { f3 vx, vy, vz; };          // columns
 struct aff3 { lin3 l; f3 p; };
 
-__host__ __device__ __forceinline__ f3 xfm_vector(const lin3& l, f3 v) { return v.x * l.vx + v.y * l.vy + v.z * l.vz; }
+__host__ __device__ __forceinline__ f3 xfm_vector(const lin3& l, f3 v) { return v.x * l.vx + (v.y * l.vy + v.z * l.vz); } // gdt madd order
 __host__ __device__ __forceinline__ f3 xfm_point(const aff3& m, f3 p)
 {
   return mk3(p.x) * m.l.vx + (mk3(p.y) * m.l.vy + (mk3(p.z) * m.l.vz + m.p));
@@ -66,10 +66,7 @@ __host__ __device__ __forceinline__ aff3 inverse(const aff3& m)
 {
   aff3 r;
   r.l = inverse(m.l);
-  aff3 t;
-  t.l = r.l;
-  t.p = mk3(0.f);
-  r.p = -xfm_point(t, m.p);
+  r.p = -((m.p.x * r.l.vx + m.p.y * r.l.vy) + m.p.z * r.l.vz); // rcp(AffineSpace): -(il * a.p)
   return r;
 }
 __host__ __device__ __forceinline__ aff3 from_3x4(const float* m)
@@ -118,4 +115,4 @@ __device__ __forceinline__ bool intersect_box(float& t0, float& t1, f3 org, f3 d
   return t1 > t0;
 }
 
-} // namespace b200vr
+} // namespace b200k

@@ -5,7 +5,7 @@
 #pragma once
 #include "device_math.cuh"
 
-namespace b200vr {
+namespace b200k {
 
 constexpr int MC_SIZE = 16;        // macrocell edge in voxels (accel/spatial_partition.h:24)
 constexpr int WARP_TILE_W = 8;     // pixels per warp tile: 8 x 4
@@ -77,4 +77,4 @@ __host__ __device__ __forceinline__ int owned_super_tiles(int rank, int nranks, 
   return rank < n_super ? (n_super - rank + nranks - 1) / nranks : 0;
 }
 
-} // namespace b200vr
+} // namespace b200k

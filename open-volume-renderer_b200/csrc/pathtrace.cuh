@@ -7,7 +7,7 @@
 #pragma once
 #include "sampling.cuh"
 
-namespace b200vr {
+namespace b200k {
 
 struct DdaIter {
   f3 t_next;
@@ -204,4 +204,4 @@ pathtrace_kernel(const __grid_constant__ LaunchParams P)
   }
 }
 
-} // namespace b200vr
+} // namespace b200k

@@ -10,7 +10,7 @@
 #pragma once
 #include "sampling.cuh"
 
-namespace b200vr {
+namespace b200k {
 
 enum { SHADING_NONE = 0, SHADING_REF = 1 };
 
@@ -55,6 +55,47 @@ __device__ __forceinline__ float shadow_march(const LaunchParams& P, const TfSha
     }
   }
   return alpha;
+}
+
+// known-answer probe: the kernels' own sampling + classification at arbitrary object-space points
+template<int SAMPLER>
+__global__ void probe_kernel(const __grid_constant__ LaunchParams P, const float* __restrict__ pts, long long n,
+                             float* __restrict__ values, float4* __restrict__ rgba)
+{
+  extern __shared__ __align__(16) unsigned char smem[];
+  const TfShared tf = stage_transfer_function(P, smem);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float s = sample_volume<SAMPLER>(P, mk3(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]));
+    values[i] = s;
+    if (rgba) {
+      const f3 c = classify_color(P, tf, s);
+      rgba[i] = make_float4(c.x, c.y, c.z, classify_alpha(P, tf, s));
+    }
+  }
+}
+
+// fetch-rate micro-benchmark (the P_fetch denominator of SURVEY 8d): every warp marches an 8x4 bundle of parallel rays,
+// one voxel apart, `iters` unit steps through a cubic footprint of the resident volume; nothing but the fetch and an add.
+template<int SAMPLER>
+__global__ void __launch_bounds__(RENDER_THREADS)
+fetch_bench_kernel(const __grid_constant__ LaunchParams P, int footprint, int iters, float dx, float dy, float dz, float* __restrict__ sink)
+{
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // bundle origin: hashed position inside the footprint, rays offset in the plane orthogonal-ish to the direction
+  unsigned int hsh = (unsigned)warp * 2654435761u;
+  const float fx = (float)(hsh % (unsigned)footprint), fy = (float)((hsh >> 8) % (unsigned)footprint), fz = (float)((hsh >> 16) % (unsigned)footprint);
+  float x = fx + (float)(lane & 7), y = fy + (float)(lane >> 3), z = fz;
+  const float fp = (float)footprint;
+  float acc = 0.f;
+  for (int i = 0; i < iters; i++) {
+    acc += sample_volume<SAMPLER>(P, mk3((x + 0.37f) * P.rdim.x, (y + 0.41f) * P.rdim.y, (z + 0.29f) * P.rdim.z));
+    x += dx; y += dy; z += dz;
+    if (x >= fp) x -= fp;
+    if (y >= fp) y -= fp;
+    if (z >= fp) z -= fp;
+  }
+  if (acc == 123.456f) sink[0] = acc; // keeps the loop alive
 }
 
 struct MarchResult { float alpha; f3 color, gradient; };
@@ -213,4 +254,4 @@ raymarch_kernel(const __grid_constant__ LaunchParams P)
   }
 }
 
-} // namespace b200vr
+} // namespace b200k

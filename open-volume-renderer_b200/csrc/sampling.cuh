@@ -7,7 +7,7 @@
 #pragma once
 #include "launch_params.cuh"
 
-namespace b200vr {
+namespace b200k {
 
 enum { SAMPLER_TEX3D = 0, SAMPLER_MANUAL = 1 };
 
@@ -133,4 +133,4 @@ __device__ __forceinline__ float cell_exit_t(const LaunchParams& P, i3 c, f3 oo,
   return fminf(fminf(tx, ty), tz);
 }
 
-} // namespace b200vr
+} // namespace b200k

@@ -47,8 +47,8 @@ struct affine3 { linear3 l; vec3 p; };
 
 static inline vec3 xfmVector(const linear3& l, vec3 v)
 {
-  // gdt: v.x*vx + v.y*vy + v.z*vz   (LinearSpace3 operator*)
-  return v.x * l.vx + v.y * l.vy + v.z * l.vz;
+  // gdt xfmVector (LinearSpace.h:320): madd(a.x, vx, madd(a.y, vy, a.z*vz))
+  return v.x * l.vx + (v.y * l.vy + v.z * l.vz);
 }
 static inline vec3 madd(vec3 a, vec3 b, vec3 c) { return a * b + c; }
 static inline vec3 xfmPoint(const affine3& m, vec3 p)
@@ -71,7 +71,7 @@ static inline affine3 inverse(const affine3& m)
   const linear3 inv = inverse(m.l);
   affine3 r;
   r.l = inv;
-  r.p = -xfmPoint(affine3{ inv, v3(0.f) }, m.p);
+  r.p = -((m.p.x * inv.vx + m.p.y * inv.vy) + m.p.z * inv.vz); // rcp(AffineSpace): -(il * a.p), LinearSpace operator*
   return r;
 }
 // 3x4 row-major (the OptiX instance layout, ovr/devices/optix7/volume.cpp:25-40) -> affine3

@@ -219,3 +219,19 @@ extern "C" int ovr_oracle_dda(const float org[3], const float dir[3], float tmin
   }
   return n;
 }
+
+// same layout as ref_xfm in ref_shim.cpp: xfmPoint, xfmVector, xfmNormal, normalize, inverse(3x4)
+extern "C" void ovr_oracle_xfm(const float m[12], const float v[3], float* out)
+{
+  const affine3 a = from_3x4(m);
+  const vec3 x = v3(v[0], v[1], v[2]);
+  const vec3 p = xfmPoint(a, x), w = xfmVector(a.l, x), n = xfmNormal(a.l, x), u = normalize(x);
+  out[0] = p.x, out[1] = p.y, out[2] = p.z;
+  out[3] = w.x, out[4] = w.y, out[5] = w.z;
+  out[6] = n.x, out[7] = n.y, out[8] = n.z;
+  out[9] = u.x, out[10] = u.y, out[11] = u.z;
+  const affine3 inv = inverse(a);
+  out[12] = inv.l.vx.x, out[13] = inv.l.vy.x, out[14] = inv.l.vz.x, out[15] = inv.p.x;
+  out[16] = inv.l.vx.y, out[17] = inv.l.vy.y, out[18] = inv.l.vz.y, out[19] = inv.p.y;
+  out[20] = inv.l.vx.z, out[21] = inv.l.vy.z, out[22] = inv.l.vz.z, out[23] = inv.p.z;
+}

@@ -103,6 +103,7 @@ void ovr_oracle_sample_tf(const ovr_oracle_scene* s, const float* values, int64_
 /* synthetic procedural volume of SURVEY 8(d): brick [org, org+bdims) of noise(N, seed) */
 void ovr_oracle_noise(int32_t n, uint32_t seed, const int32_t org[3], const int32_t bdims[3], float* out,
                       int num_threads);
+void ovr_oracle_xfm(const float m[12], const float v[3], float* out24); /* gdt transforms, layout of ref_xfm */
 int ovr_oracle_hardware_threads(void);
 
 #ifdef __cplusplus

@@ -156,6 +156,14 @@ def sample_volume(vol, pts, filter_mode=FILTER_FIXED8_RN):
     return out
 
 
+def xfm(m, v):
+    m = np.ascontiguousarray(m, np.float32)
+    v = np.ascontiguousarray(v, np.float32)
+    out = np.empty(24, np.float32)
+    lib().ovr_oracle_xfm(_fp(m), _fp(v), _fp(out))
+    return out
+
+
 class OracleScene:
     """Owns the numpy buffers behind an ovr_oracle_scene. `desc` is a scenes.SceneDesc-like object with
     attributes: volume [nz,ny,nx] f32, obj_to_world (12,), tf_color [Nc,4], tf_alpha [Na], tf_range (lo,hi),

@@ -1,0 +1,118 @@
+"""Generates the committed fixtures under tests/golden/ from the REFERENCE itself (run in the authoring container only,
+where /root/reference exists):
+
+  ref_kat.npz       outputs of the reference's own dda.h (dda3 + DDAIter), RandomTEA and gdt transforms compiled on the
+                    host by oracle/Makefile (target `ref`, oracle/ref_shim.cpp)
+  scene_vorts1.npz  the bundled scene data/configs/scene_vorts1.json (BASELINE config C1): camera, sample distance,
+                    scalar mapping range, 1024-entry alpha array, colour controls
+
+Usage: python tests/golden/make_golden.py
+"""
+import base64
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle import pyoracle  # noqa: E402
+
+REF = "/root/reference"
+
+
+def f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+def i3(v):
+    return (C.c_int32 * 3)(*[int(x) for x in v])
+
+
+def main():
+    pyoracle.build()
+    L = pyoracle.ref_kat_lib()
+    assert L is not None, "oracle/_ref/libovr_ref_kat.so missing (needs /root/reference)"
+    rng = np.random.default_rng(1337)
+    out = {}
+
+    # ---- RandomTEA ----
+    seeds = np.array([[1, 0], [1, 1], [2, 12345], [64, 1920 * 1080 - 1], [0xFFFFFFFF, 0xDEADBEEF], [7, 99]], np.uint32)
+    draws = np.zeros((len(seeds), 8, 2), np.float32)
+    for k, (a, b) in enumerate(seeds):
+        L.ref_tea(C.c_uint32(int(a)), C.c_uint32(int(b)), 8, draws[k].ctypes.data_as(C.POINTER(C.c_float)))
+    out["tea_seeds"], out["tea_draws"] = seeds, draws
+
+    # ---- DDA: rays through grids, both the one-shot dda3 and the resumable DDAIter ----
+    grids = [(8, 8, 8), (32, 16, 8), (4, 7, 64)]
+    rays = []
+    MAXC = 256
+    for g in grids:
+        for _ in range(24):
+            gdim = np.array(g, np.float32)
+            org = (rng.uniform(-0.5, 1.5, 3) * gdim).astype(np.float32)
+            tgt = (rng.uniform(0.1, 0.9, 3) * gdim).astype(np.float32)
+            d = (tgt - org).astype(np.float32)
+            if rng.uniform() < 0.25:
+                d[rng.integers(3)] = 0.0  # axis-parallel component
+                org = np.clip(org, 0.25, gdim - 0.25).astype(np.float32)
+            d = (d / np.float32(np.linalg.norm(d)) * np.float32(rng.uniform(0.5, 2.0))).astype(np.float32)
+            ok, t0, t1 = pyoracle.clip(org, d, (0, 0, 0), g)  # entry/exit like the shaders do before the DDA
+            if not ok:
+                continue
+            rec = {}
+            for name, fn in (("dda3", L.ref_dda3), ("iter", L.ref_dda_iter)):
+                cells = np.zeros((MAXC, 3), np.int32)
+                tt = np.zeros((MAXC, 2), np.float32)
+                n = fn(f3(org), f3(d), C.c_float(t0), C.c_float(t1), i3(g), MAXC, cells.ctypes.data_as(C.c_void_p),
+                       tt.ctypes.data_as(C.POINTER(C.c_float)))
+                rec[name] = (cells[:n].copy(), tt[:n].copy())
+            rays.append((np.array(g, np.int32), org, d, np.float32(t0), np.float32(t1), rec))
+    out["dda_n"] = np.int32(len(rays))
+    for k, (g, org, d, t0, t1, rec) in enumerate(rays):
+        out[f"dda{k}_grid"], out[f"dda{k}_org"], out[f"dda{k}_dir"] = g, org, d
+        out[f"dda{k}_t"] = np.array([t0, t1], np.float32)
+        for name in ("dda3", "iter"):
+            out[f"dda{k}_{name}_cells"], out[f"dda{k}_{name}_t"] = rec[name]
+
+    # ---- gdt transforms ----
+    mats, vecs, res = [], [], []
+    for k in range(32):
+        if k % 2 == 0:  # translate * scale, what buildScene produces
+            s = rng.uniform(0.5, 600, 3)
+            o = rng.uniform(-10, 10, 3)
+            m = np.array([s[0], 0, 0, o[0], 0, s[1], 0, o[1], 0, 0, s[2], o[2]], np.float32)
+        else:
+            m = rng.uniform(-2, 2, 12).astype(np.float32)
+        v = rng.uniform(-3, 3, 3).astype(np.float32)
+        r = np.zeros(24, np.float32)
+        L.ref_xfm(m.ctypes.data_as(C.POINTER(C.c_float)), v.ctypes.data_as(C.POINTER(C.c_float)),
+                  r.ctypes.data_as(C.POINTER(C.c_float)))
+        mats.append(m), vecs.append(v), res.append(r)
+    out["xfm_m"], out["xfm_v"], out["xfm_out"] = np.array(mats), np.array(vecs), np.array(res)
+    np.savez_compressed(os.path.join(HERE, "ref_kat.npz"), **out)
+    print("wrote ref_kat.npz:", len(rays), "dda rays")
+
+    # ---- bundled scene C1 ----
+    js = json.load(open(os.path.join(REF, "data/configs/scene_vorts1.json")))
+    ds, view = js["dataSource"][0], js["view"]
+    vol, cam = view["volume"], view["camera"]
+    tf = vol["transferFunction"]
+    alpha = np.frombuffer(base64.b64decode(tf["alphaArray"]["data"]), dtype="<f4").astype(np.float32)
+    cc = np.array([[c["position"], c["color"]["r"], c["color"]["g"], c["color"]["b"]] for c in tf["colorControls"]], np.float32)
+    np.savez_compressed(
+        os.path.join(HERE, "scene_vorts1.npz"),
+        dims=np.array([ds["dimensions"][k] for k in "xyz"], np.int32), type=np.array(ds["type"]),
+        eye=np.array([cam["eye"][k] for k in "xyz"], np.float32), center=np.array([cam["center"][k] for k in "xyz"], np.float32),
+        up=np.array([cam["up"][k] for k in "xyz"], np.float32), fovy=np.float32(cam["fovy"]),
+        sample_distance=np.float32(vol["sampleDistance"]),
+        mapping_range=np.array([vol["scalarMappingRange"]["minimum"], vol["scalarMappingRange"]["maximum"]], np.float32),
+        alpha=alpha, color_controls=cc, resolution=np.int32(tf["resolution"]))
+    print("wrote scene_vorts1.npz: alpha", alpha.shape, "max", alpha.max())
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,285 @@
+"""GPU parity tests proper: the sm_100a kernels, called through the C ABI (ctypes -> libb200vr.so), against the CPU oracle
+on the same seeded inputs. Tolerances are the north star's: ray marching max-abs <= 1/255 per RGBA channel and
+PSNR >= 45 dB; integer / index work (noise lattice, macrocell ranges, majorants, RNG-driven structure) bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from helpers import max_abs, oracle_desc, ovr_b200, psnr, pyoracle
+
+pytestmark = pytest.mark.gpu
+S = ovr_b200.scenes
+capi = ovr_b200.capi
+TOL = 1.0 / 255.0
+
+
+def make_renderer(scene, w, h, shading=capi.SHADING_REF, sampler=capi.SAMPLER_TEX3D, skip=True, spp=1, path=False,
+                  accumulate=False):
+    r = ovr_b200.create_renderer("b200")
+    r.shading, r.sampler, r.skip_empty = shading, sampler, skip
+    r.set_fbsize((w, h))
+    r.set_sample_per_pixel(spp)
+    r.set_path_tracing(path)
+    r.set_frame_accumulation(accumulate)
+    r.init(scene, scene.camera)
+    r.commit()
+    return r
+
+
+def probe(r, pts, sampler, want_rgba=True):
+    pts = np.ascontiguousarray(pts, np.float32)
+    vals = np.empty(len(pts), np.float32)
+    rgba = np.empty((len(pts), 4), np.float32) if want_rgba else None
+    r._ck(capi.lib().b200vr_probe(r.handle, pts.ctypes.data_as(C.POINTER(C.c_float)), len(pts), sampler,
+                                  vals.ctypes.data_as(C.POINTER(C.c_float)),
+                                  rgba.ctypes.data_as(C.POINTER(C.c_float)) if want_rgba else None))
+    return vals, rgba
+
+
+def macrocells(r):
+    mc = (C.c_int32 * 3)()
+    r._ck(capi.lib().b200vr_get_macrocells(r.handle, mc, None, None))
+    ranges = np.empty((mc[2], mc[1], mc[0], 2), np.float32)
+    maj = np.empty((mc[2], mc[1], mc[0]), np.float32)
+    r._ck(capi.lib().b200vr_get_macrocells(r.handle, mc, ranges.ctypes.data_as(C.c_void_p), maj.ctypes.data_as(C.c_void_p)))
+    return ranges, maj
+
+
+def device_volume(r, dims):
+    v = np.empty((dims[2], dims[1], dims[0]), np.float32)
+    r._ck(capi.lib().b200vr_download_volume(r.handle, v.ctypes.data_as(C.c_void_p)))
+    return v
+
+
+def test_noise_volume_and_macrocells_bit_exact():
+    dims = (70, 45, 33)  # ragged: not multiples of 16
+    sc = S.noise_scene(70, dims=dims, org=(5, 9, 200))
+    r = make_renderer(sc, 32, 16)
+    vol = device_volume(r, dims)
+    want = pyoracle.noise(70, S.NOISE_SEED, (5, 9, 200), dims)
+    assert np.array_equal(vol.view(np.uint32), want.view(np.uint32))
+    assert r.value_range == (float(want.min()), float(want.max()))
+    ranges, maj = macrocells(r)
+    o_ranges = pyoracle.build_ranges(want)
+    assert np.array_equal(ranges, o_ranges)
+    o_maj = pyoracle.build_majorants(o_ranges, sc.tfn.opacity, *r.value_range)
+    assert np.array_equal(maj, o_maj) and (maj == 0).any() and (maj > 0).any()
+
+
+def test_sampler_and_tf_probe_against_oracle_model():
+    sc = S.noise_scene(40, dims=(40, 24, 17), tf="ramp")
+    r = make_renderer(sc, 16, 16)
+    vol = device_volume(r, (40, 24, 17))
+    rng = np.random.default_rng(5)
+    pts = np.concatenate([rng.uniform(-0.05, 1.05, (40000, 3)), rng.integers(0, 2, (64, 3)).astype(np.float64)]).astype(np.float32)
+    want = pyoracle.sample_volume(vol, pts, pyoracle.FILTER_FIXED8_RN)
+    v_man, c_man = probe(r, pts, capi.SAMPLER_MANUAL)
+    assert np.array_equal(v_man.view(np.uint32), want.view(np.uint32))          # software sampler == oracle model, bit for bit
+    d = oracle_desc(sc, 16, 16, volume=vol)
+    o = pyoracle.OracleScene(d)
+    assert np.array_equal(c_man, o.sample_tf(v_man))                               # shared-memory TF == oracle model
+    # hardware texture unit: same model up to the unit's internal rounding
+    v_tex, _ = probe(r, pts, capi.SAMPLER_TEX3D)
+    span = float(vol.max() - vol.min())
+    err = np.abs(v_tex - want)
+    assert err.max() < span * 2.5e-3, err.max()       # <= ~half a weight quantum times the local slope
+    e_rn = np.abs(v_tex - want).mean()
+    e_tr = np.abs(v_tex - pyoracle.sample_volume(vol, pts, pyoracle.FILTER_FIXED8_TRUNC)).mean()
+    e_fp = np.abs(v_tex - pyoracle.sample_volume(vol, pts, pyoracle.FILTER_FP32)).mean()
+    print(f"tex3D calibration: mean|err| RN {e_rn:.3e} TRUNC {e_tr:.3e} FP32 {e_fp:.3e} max RN {err.max():.3e}")
+    assert e_rn <= e_fp  # the fixed-point model explains the hardware better than exact fp32 weights
+
+
+MARCH_CASES = [
+    # name, n, tf, camera, rate, shading, sampler
+    ("oblique-ref-tex", 64, "sparse", "oblique", 1.0, capi.SHADING_REF, capi.SAMPLER_TEX3D),
+    ("oblique-ref-manual", 64, "sparse", "oblique", 1.0, capi.SHADING_REF, capi.SAMPLER_MANUAL),
+    ("front-none-tex", 64, "sparse", "front", 1.0, capi.SHADING_NONE, capi.SAMPLER_TEX3D),
+    ("inside-ref-tex", 48, "ramp", "inside", 2.0, capi.SHADING_REF, capi.SAMPLER_TEX3D),
+    ("dense-ref-tex", 40, "dense", "oblique", 1.0, capi.SHADING_REF, capi.SAMPLER_TEX3D),
+    ("front-rate4-manual", 32, "ramp", "front", 4.0, capi.SHADING_REF, capi.SAMPLER_MANUAL),
+]
+
+
+@pytest.mark.parametrize("case", MARCH_CASES, ids=[c[0] for c in MARCH_CASES])
+def test_raymarch_matches_oracle(case):
+    name, n, tf, cam, rate, shading, sampler = case
+    W, H = 200, 120
+    sc = S.noise_scene(n, tf=tf, camera=cam, rate=rate)
+    r = make_renderer(sc, W, H, shading=shading, sampler=sampler, skip=True)
+    r.render()
+    rgba, grad = r.download()
+    st = dict(r.last_stats)
+    d = oracle_desc(sc, W, H, shading=shading, volume=device_volume(r, (n, n, n)))
+    o_rgba, o_grad, o_cnt = pyoracle.OracleScene(d, skip_empty=True).render_march()
+    assert (o_rgba[..., 3] > 0).mean() > 0.05
+    e, p = max_abs(rgba, o_rgba), psnr(rgba, o_rgba)
+    eg = max_abs(grad, o_grad)
+    print(f"{name}: max-abs {e:.2e} psnr {p:.1f} dB grad max-abs {eg:.2e} gpu samples {st['primary_samples']}+{st['shadow_samples']}"
+          f" oracle {o_cnt['primary_samples']}+{o_cnt['shadow_samples']}")
+    assert e <= TOL and p >= 45.0
+    assert eg <= 4 * TOL
+    assert st["rays"] == W * H == o_cnt["rays"]
+    # both skip only provably empty samples, so executed counts agree to within the few samples fp rounding moves
+    assert abs(st["primary_samples"] - o_cnt["primary_samples"]) <= 0.02 * o_cnt["primary_samples"] + 16
+    # skipping never changes a bit of the image
+    r.skip_empty = False
+    r.apply_device_options()
+    r.render()
+    rgba2, grad2 = r.download()
+    assert np.array_equal(rgba.view(np.uint32), rgba2.view(np.uint32))
+    assert np.array_equal(grad.view(np.uint32), grad2.view(np.uint32))
+    assert r.last_stats["primary_samples"] >= st["primary_samples"]
+    r.close()
+
+
+def test_spp_jitter_and_accumulation_semantics():
+    W, H = 96, 64
+    sc = S.noise_scene(32, tf="ramp", camera="oblique")
+    r = make_renderer(sc, W, H, shading=capi.SHADING_NONE, spp=3, accumulate=True)
+    frames = []
+    for _ in range(3):
+        r.render()
+        frames.append(r.download()[0])
+        assert r.last_stats["frame_index"] == len(frames)
+    d = oracle_desc(sc, W, H, spp=3, shading=capi.SHADING_NONE, volume=device_volume(r, (32, 32, 32)))
+    o = pyoracle.OracleScene(d)
+    per = [o.render_march(frame_index=f)[0] for f in (1, 2, 3)]
+    assert max_abs(frames[0], per[0]) <= TOL
+    assert max_abs(frames[2], (per[0] + per[1] + per[2]) / 3) <= TOL
+    assert not np.array_equal(per[0], per[1])  # TEA reseeds per frame
+    r.set_camera(S.camera_preset("front", (32, 32, 32)))  # any change resets accumulation
+    r.commit()
+    r.render()
+    assert r.last_stats["frame_index"] == 1
+    r.close()
+
+
+def test_path_tracing_matches_oracle_statistically():
+    W, H, N = 96, 64, 32
+    sc = S.noise_scene(48, tf="pt", camera="front")
+    r = make_renderer(sc, W, H, path=True, accumulate=True)
+    for _ in range(N):
+        r.render()
+    gpu = r.download()[0]
+    assert r.last_stats["frame_index"] == N and r.last_stats["delta_samples"] > 0
+    d = oracle_desc(sc, W, H, volume=device_volume(r, (48, 48, 48)))
+    o = pyoracle.OracleScene(d)
+    acc = np.zeros((H, W, 4), np.float64)
+    first = None
+    for f in range(1, N + 1):
+        img = o.render_path(frame_index=f)[0]
+        first = img if first is None else first
+        acc += img
+    cpu = (acc / N).astype(np.float32)
+    assert np.array_equal(gpu[..., 3], cpu[..., 3])                      # coverage is deterministic: alpha = box hit
+    hit = cpu[..., 3] > 0
+    # same estimator and same RNG streams: the two means differ only where an fp rounding flipped a decision
+    mse = float(np.mean((gpu[hit][:, :3] - cpu[hit][:, :3]) ** 2))
+    var1 = float(np.var(first[hit][:, :3]))
+    print(f"path tracing: mse(gpu,oracle)@{N}spp {mse:.3e}  single-frame variance {var1:.3e}  mean gpu {gpu[hit][:, :3].mean():.4f} cpu {cpu[hit][:, :3].mean():.4f}")
+    assert mse <= 2.0 * var1 / N + 1e-6          # no worse than two independent N-spp estimates
+    assert abs(float(gpu[hit][:, :3].mean()) - float(cpu[hit][:, :3].mean())) < 0.01   # unbiased relative to the oracle
+    r.close()
+
+
+def test_sort_first_tiles_reassemble_bit_exact():
+    import torch
+    W, H = 200, 120
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    r = make_renderer(sc, W, H)
+    r.render()
+    full = r.download()[0]
+    L = capi.lib()
+    nranks = 3
+    slices = []
+    for rank in range(nranks):
+        L.b200vr_set_tile_partition(r.handle, rank, nranks)
+        r.render()
+        n = L.b200vr_tile_slice_floats(r.handle, rank, nranks)
+        buf = torch.empty(n, dtype=torch.float32, device="cuda")
+        r._ck(L.b200vr_pack_tiles(r.handle, C.c_void_p(buf.data_ptr())))
+        slices.append(buf)
+    # display rank: fresh frame, scatter every rank's slice
+    disp = make_renderer(sc, W, H)
+    for rank in range(nranks):
+        disp._ck(L.b200vr_unpack_tiles(disp.handle, C.c_void_p(slices[rank].data_ptr()), rank, nranks))
+    got = disp.download()[0]
+    assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
+    r.close(), disp.close()
+
+
+def test_sort_last_bricks_composite_to_the_full_image():
+    import torch
+    W, H = 160, 96
+    n = 64
+    sc = S.noise_scene(n, tf="ramp", camera="oblique")
+    ref = make_renderer(sc, W, H, shading=capi.SHADING_NONE)
+    ref.render()
+    want = ref.download()[0]
+    L = capi.lib()
+    parts = []
+    for lo, hi in (((0, 0, 0.5), (1, 1, 1)), ((0, 0, 0), (1, 1, 0.5))):   # camera sits at +z: the far-z half is in front
+        b = make_renderer(sc, W, H, shading=capi.SHADING_NONE)
+        b.premultiplied = True
+        b.apply_device_options()
+        b._ck(L.b200vr_set_clip_box(b.handle, (C.c_float * 3)(*lo), (C.c_float * 3)(*hi)))
+        b.render()
+        parts.append(b)
+    fb = [p.mapframe() for p in parts]
+    out = torch.empty(W * H * 4, dtype=torch.float32, device="cuda")
+    ref._ck(L.b200vr_composite_over(ref.handle, C.c_void_p(fb[0].rgba[0]), C.c_void_p(fb[1].rgba[0]), C.c_void_p(out.data_ptr()), W * H))
+    ref._ck(L.b200vr_finalize_premultiplied(ref.handle, C.c_void_p(out.data_ptr()), W * H))
+    got = out.cpu().numpy().reshape(H, W, 4)
+    # each brick restarts the t lattice at its own entry point and cannot early-terminate across the cut
+    print(f"sort-last 2 bricks: max-abs {max_abs(got, want):.2e} psnr {psnr(got, want):.1f} dB")
+    assert max_abs(got[..., 3], want[..., 3]) < 0.02 and psnr(got, want) > 35.0
+    for p in parts:
+        p.close()
+    ref.close()
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.int16, np.float64])
+def test_typed_volumes(dtype):
+    rng = np.random.default_rng(11)
+    base = pyoracle.noise(24, 3)
+    info_max = {np.uint8: 255, np.uint16: 4000, np.int16: 3000, np.float64: 7.5}[dtype]
+    data = (base * info_max).astype(dtype)
+    if dtype == np.uint8:
+        as_f32 = data.astype(np.float32) / np.float32(255)       # cudaReadModeNormalizedFloat
+        tf_range = (0.0, 255.0)                                   # file units -> integer_normalize -> [0, 1]
+        want_window = (0.0, 1.0)
+    else:
+        as_f32 = data.astype(np.float32)                          # converted without normalisation (array.cpp:335-346)
+        tf_range = (float(as_f32.min()), float(as_f32.max()))
+        want_window = tf_range
+    sc = S.Scene(S.Volume(data), S.make_tfn("ramp", value_range=tf_range), S.camera_preset("oblique", (24, 24, 24)))
+    r = make_renderer(sc, 96, 64, shading=capi.SHADING_NONE)
+    assert np.array_equal(device_volume(r, (24, 24, 24)), as_f32)
+    r.render()
+    rgba = r.download()[0]
+    sc_f = S.Scene(S.Volume(as_f32), sc.tfn, sc.camera)
+    o = pyoracle.OracleScene(oracle_desc(sc_f, 96, 64, shading=capi.SHADING_NONE, tf_range=want_window)).render_march()[0]
+    assert max_abs(rgba, o) <= TOL and (o[..., 3] > 0).any()
+    r.close()
+
+
+def test_error_codes_and_state_machine():
+    L = capi.lib()
+    h = C.c_void_p()
+    assert L.b200vr_create(C.byref(h), 0) == capi.OK
+    assert L.b200vr_render(h, None) == capi.ESTATE and b"no volume" in L.b200vr_last_error(h)
+    assert L.b200vr_resize(h, 0, 10) == capi.EINVAL
+    assert L.b200vr_set_volume(h, None, capi.TYPE_FLOAT, 4, 4, 4, None, 0) == capi.EINVAL
+    p = capi.Params()
+    L.b200vr_default_params(C.byref(p))
+    p.spp = 0
+    assert L.b200vr_set_params(h, C.byref(p)) == capi.EINVAL
+    assert L.b200vr_set_tile_partition(h, 2, 2) == capi.EINVAL
+    assert L.b200vr_create(C.byref(C.c_void_p()), 99) == capi.EINVAL
+    L.b200vr_destroy(h)
+    r = make_renderer(S.noise_scene(16), 32, 32)
+    with pytest.raises(RuntimeError):
+        r.init(S.noise_scene(16))       # init-once, like device_impl.cpp:73-75
+    r.close()

@@ -1,0 +1,50 @@
+"""Host-side logic that needs no GPU: tile ownership, synthetic scene definitions, TF rasterisation."""
+import numpy as np
+
+from helpers import ovr_b200
+
+S = ovr_b200.scenes
+
+
+def super_tiles(w, h):
+    return (w + 63) // 64, (h + 31) // 32
+
+
+def owned(rank, nranks, n):
+    return len(range(rank, n, nranks))
+
+
+def test_tile_partition_covers_every_pixel_once():
+    for (w, h) in [(1920, 1080), (100, 70), (64, 32)]:
+        sw, sh = super_tiles(w, h)
+        for nranks in (1, 2, 3, 8):
+            cover = np.zeros((sh * 32, sw * 64), np.int32)
+            for rank in range(nranks):
+                n_owned = owned(rank, nranks, sw * sh)
+                for k in range(n_owned * 64):  # warp tiles: same arithmetic as warp_tile_origin (launch_params.cuh)
+                    m, r = divmod(k, 64)
+                    s = rank + m * nranks
+                    px = (s % sw) * 64 + (r % 8) * 8
+                    py = (s // sw) * 32 + (r // 8) * 4
+                    cover[py:py + 4, px:px + 8] += 1
+            assert (cover == 1).all()
+
+
+def test_rainbow_rasterisation_and_presets():
+    c = S.rasterize_color_controls(n=1024)
+    assert c.shape == (1024, 4) and np.all(c[:, 3] == 1)
+    assert np.allclose(c[0, :3], [0, 0.364706, 1], atol=1e-6) and np.allclose(c[-1, :3], [0.662745, 0, 1], atol=1e-6)
+    a = S.alpha_preset("sparse")
+    assert a[0] == 0 and a[613] == 0 and a[-1] == np.float32(0.6) and (np.diff(a) >= 0).all()
+    assert S.alpha_preset("dense").min() > 0
+
+
+def test_scene_geometry():
+    sc = S.noise_scene(512)
+    assert sc.volume.dims == (512, 512, 512)
+    assert np.array_equal(sc.volume.obj_to_world(), np.array([512, 0, 0, 0, 0, 512, 0, 0, 0, 0, 512, 0], np.float32))
+    cam = S.camera_preset("front", (128, 128, 128))
+    assert np.allclose(cam.frm, (64, 64, 64 + 2.63 * 128)) and cam.fovy == 45.0
+    v = S.Volume(np.zeros((4, 6, 8), np.uint8), grid_origin=(1, 2, 3), grid_spacing=(2, 2, 2))
+    assert v.dims == (8, 6, 4)
+    assert np.array_equal(v.obj_to_world(), np.array([16, 0, 0, 1, 0, 12, 0, 2, 0, 0, 8, 3], np.float32))
