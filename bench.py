@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""Headline benchmark of the B200 volume device: Msamples/s and ms/frame of 1080p ray marching (BASELINE.json).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C2] [--impl b200|reference]
+
+A "step" is one frame of the workload through the hot path. One JSON line is printed by rank 0:
+  value       executed Msamples/s (TF-classified trilinear samples: primary + shadow + delta-tracking collisions), whole
+              job, volume / TF / macrocells already resident in HBM, timed on the device with CUDA events
+  e2e         the same metric through the plugin-facing API with host buffers: per step the camera and the transfer
+              function travel host -> device and the rgba + grad frame comes back device -> pinned host
+  roofline    texture/L1 sampling roofline of the dominant kernel (32 B per executed trilinear fetch) against the
+              fetch rate measured on this box by b200vr_bench_fetch, plus the HBM floor against MEASURED_PEAKS.json
+  cpu_baseline  the CPU oracle (a port of the reference's optix7 shader arithmetic) timed on the host cores on a strided
+              pixel sample of the same frame
+`--impl reference` times that CPU port alone (the reference's own devices need OptiX / OSPRay, neither installable here).
+N > 1 (torchrun): sort-first -- every rank renders the image tiles it owns of the same frame, slices are gathered to
+rank 0 over NCCL and scattered into the display frame; strong scaling.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Msamples/s & ms/frame, 1080p ray-march, 1/2/4/8 B200 vs OSPRay CPU device"
+UNIT = "Msamples/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=25)   # apps/main_batch.cpp:278-289: 5 warm-up + 25 timed frames
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--sampler", default="tex3d", choices=["tex3d", "manual"])
+    ap.add_argument("--no-skip", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-stride", type=int, default=0, help="pixel stride of the CPU sample (0 = auto)")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload_scene(name):
+    import ovr_b200
+    w = dict(ovr_b200.scenes.WORKLOADS[name])
+    scene = ovr_b200.scenes.noise_scene(w["n"], tf=w["tf"], camera=w["camera"], rate=w["rate"])
+    return w, scene
+
+
+def orbit_camera(scene, k, n):
+    """k-th camera of an orbit around the volume centre (the multi-frame mode of apps/main_batch.cpp:295-313)."""
+    import ovr_b200
+    cam = scene.camera
+    at, frm = np.array(cam.at), np.array(cam.frm)
+    ang = 2 * np.pi * k / max(n, 1) * 0.05  # a slow orbit: consecutive frames stay comparable in cost
+    d = frm - at
+    c, s = np.cos(ang), np.sin(ang)
+    d2 = np.array([c * d[0] + s * d[2], d[1], -s * d[0] + c * d[2]])
+    return ovr_b200.Camera(tuple(at + d2), tuple(at), cam.up, cam.fovy)
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+    try:
+        m = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        p = {"hbm_gbs": float(m["hbm_gbs"]), "source": "MEASURED_PEAKS.json"}
+    except Exception:
+        pass
+    return p
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (port of the reference's shader arithmetic) on the host cores, bounded pixel sample
+# ----------------------------------------------------------------------------------------------------------------------
+
+def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
+    """Renders every `stride`-th pixel in x and y of the workload's frame with the reference algorithm verbatim
+    (no skipping, every sample shaded and shadowed); returns (Msamples/s, ms per sampled frame, info)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle_desc
+    from oracle import pyoracle
+    shading = pyoracle.SHADING_REF if wl["shading"] == "ref" else pyoracle.SHADING_NONE
+    d = oracle_desc(scene, wl["width"], wl["height"], shading=shading, volume=volume)
+    o = pyoracle.OracleScene(d, skip_empty=False, build_macrocells=(wl["mode"] == "pathtrace"))
+    cores = pyoracle.hardware_threads()
+
+    def frame(fi):
+        t0 = time.perf_counter()
+        if wl["mode"] == "pathtrace":
+            _, cnt = o.render_path(stride=(stride, stride), threads=cores, frame_index=fi)
+        else:
+            _, _, cnt = o.render_march(stride=(stride, stride), threads=cores, frame_index=fi)
+        dt = time.perf_counter() - t0
+        return dt, cnt["primary_samples"] + cnt["shadow_samples"] + cnt["delta_samples"], cnt
+
+    for k in range(warmup):
+        frame(k + 1)
+    tot_t, tot_s, cnt = 0.0, 0, None
+    for k in range(steps):
+        dt, s, cnt = frame(k + 1)
+        tot_t += dt
+        tot_s += s
+    info = {"cores": cores, "kind": "port",
+            "sample": f"every {stride}th pixel in x and y (1/{stride * stride} of the rays) of the {wl['width']}x{wl['height']} frame, "
+                      f"reference algorithm without skipping, {steps} frame(s)", "rays": cnt["rays"], "samples_per_frame": tot_s // max(steps, 1)}
+    return tot_s / tot_t / 1e6, tot_t / steps * 1e3, info
+
+
+def auto_stride(cores):
+    return 4 if cores >= 32 else 8
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    pyoracle.build()
+    wl, scene = workload_scene(args.workload)
+    stride = args.cpu_stride or auto_stride(pyoracle.hardware_threads())
+    steps, warmup = min(args.steps, 3), min(args.warmup, 1)  # bounded: a CPU frame takes seconds
+    v, ms, info = cpu_oracle_run(wl, scene, steps, warmup, stride)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args, wl), "note": "reference devices need OptiX/OSPRay (absent); this is the CPU port of "
+                       "the optix7 shader arithmetic on the host cores; ms_per_step is for the sampled pixel subset"},
+            "cpu_baseline": dict(info, value=v, unit=UNIT),
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args, wl):
+    return (f"{args.workload}: noise({wl['n']},1337) f32 {wl['n']}^3, {wl['width']}x{wl['height']}, camera {wl['camera']}, TF {wl['tf']}, "
+            f"rate {wl['rate']}, {wl['mode']}, shading {wl['shading']}")
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ----------------------------------------------------------------------------------------------------------------------
+
+def measure_fetch_peak(r, capi, sampler):
+    """P_fetch of SURVEY 8d: best trilinear fetch rate of b200vr_bench_fetch over a few footprints (fetches/s)."""
+    best, rows = 0.0, []
+    d = (C.c_float * 3)(0.35, 0.25, 0.9)
+    for fp, iters in ((32, 4096), (64, 4096), (256, 2048)):
+        ms, n = C.c_float(), C.c_uint64()
+        rc = capi.lib().b200vr_bench_fetch(r.handle, sampler, fp, iters, d, 8, C.byref(ms), C.byref(n))
+        if rc != 0:
+            continue
+        rate = n.value / (ms.value * 1e-3)
+        rows.append({"footprint": fp, "gfetch_s": rate / 1e9})
+        best = max(best, rate)
+    return best, rows
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import ovr_b200
+    capi = ovr_b200.capi
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 volume device has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L = capi.lib()
+    wl, scene = workload_scene(args.workload)
+    W, H = wl["width"], wl["height"]
+
+    r = ovr_b200.create_renderer("b200", local_rank)
+    r.shading = capi.SHADING_REF if wl["shading"] == "ref" else capi.SHADING_NONE
+    r.sampler = capi.SAMPLER_MANUAL if args.sampler == "manual" else capi.SAMPLER_TEX3D
+    r.skip_empty = not args.no_skip
+    r.set_fbsize((W, H))
+    r.set_path_tracing(wl["mode"] == "pathtrace")
+    r.set_frame_accumulation(wl["mode"] == "pathtrace")
+    r.init(scene, scene.camera)
+    r.commit()
+    stream = torch.cuda.current_stream()
+    r._ck(L.b200vr_set_stream(r.handle, C.c_void_p(stream.cuda_stream)))
+    r._ck(L.b200vr_set_tile_partition(r.handle, rank, world))
+
+    # sort-first exchange buffers: equal-size padded slices, gathered to rank 0
+    slice_floats = max(int(L.b200vr_tile_slice_floats(r.handle, k, world)) for k in range(world))
+    my_slice = torch.zeros(slice_floats, dtype=torch.float32, device="cuda")
+    gathered = [torch.zeros(slice_floats, dtype=torch.float32, device="cuda") for _ in range(world)] if (world > 1 and rank == 0) else None
+    launches = [0]
+
+    def step():
+        r.render()
+        launches[0] += r.last_stats["kernel_launches"]
+        if world > 1:
+            r._ck(L.b200vr_pack_tiles(r.handle, C.c_void_p(my_slice.data_ptr())))
+            launches[0] += 1
+            dist.gather(my_slice, gathered, dst=0)
+            if rank == 0:
+                for k in range(1, world):
+                    r._ck(L.b200vr_unpack_tiles(r.handle, C.c_void_p(gathered[k].data_ptr()), k, world))
+                    launches[0] += 1
+        return r.last_stats
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) ----
+    for _ in range(args.warmup):
+        step()
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    launches[0] = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    samples = fetches = 0
+    kernel_ms = 0.0
+    barrier()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        st = step()
+        samples += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
+        fetches += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"] + st["gradient_fetches"]
+        kernel_ms += st["ms"]
+    ev1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    gpu_launches = launches[0]
+    t_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([samples, fetches], dtype=torch.float64, device="cuda")
+    kms = torch.tensor([kernel_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+    t_ms, samples, fetches, kernel_ms = float(t_ms.item()), float(tot[0].item()), float(tot[1].item()), float(kms.item())
+    value = samples / (t_ms * 1e-3) / 1e6
+    return dict(r=r, wl=wl, scene=scene, value=value, t_ms=t_ms, samples=samples, fetches=fetches, kernel_ms=kernel_ms, clk=clk,
+                gpu_launches=gpu_launches, step=step, barrier=barrier, stream=stream, world=world, rank=rank, local_rank=local_rank)
+
+
+def run_e2e(ctx, args):
+    """Same frames through the plugin-facing calls with host buffers: set_camera + set_transfer_function (host arrays ->
+    device, majorants rebuilt), commit, render, then the rgba + grad frame device -> pinned host."""
+    import torch
+    import ovr_b200
+    r, wl, scene, world, rank = ctx["r"], ctx["wl"], ctx["scene"], ctx["world"], ctx["rank"]
+    W, H = wl["width"], wl["height"]
+    L = ovr_b200.capi.lib()
+    tfn = scene.tfn
+    c = np.ascontiguousarray(np.asarray(tfn.color, np.float32)[:, :3]).ravel()
+    n_o = len(tfn.opacity)
+    o = np.empty(2 * n_o, np.float32)
+    o[0::2] = np.arange(n_o, dtype=np.float32) / np.float32(n_o - 1)
+    o[1::2] = tfn.opacity
+    rgba_host = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+    grad_host = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    h2d = c.nbytes + o.nbytes + 10 * 4
+    d2h = rgba_host.numel() * 4 + grad_host.numel() * 4
+
+    def e2e_step(k):
+        r.set_camera(orbit_camera(scene, k, args.steps))
+        r.set_transfer_function(c, o, (1.0, -1.0))
+        r.commit()
+        st = ctx["step"]()
+        if rank == 0:
+            r._ck(L.b200vr_download(r.handle, C.c_void_p(rgba_host.data_ptr()), C.c_void_p(grad_host.data_ptr())))
+        return st
+
+    for k in range(max(1, min(args.warmup, 3))):
+        e2e_step(k)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    samples = 0
+    ctx["barrier"]()
+    t0 = time.perf_counter()
+    ev0.record(ctx["stream"])
+    for k in range(args.steps):
+        st = e2e_step(k)
+        samples += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
+    ev1.record(ctx["stream"])
+    ctx["barrier"]()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    s = torch.tensor([samples], dtype=torch.float64, device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+    t_ms = float(t.item())
+    return {"value": float(s.item()) / (t_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "ms_per_step": t_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "path": "MainRenderer.set_camera/set_transfer_function/commit/render + b200vr_download to pinned host"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    ctx = run_b200(args)
+    r, wl, rank, world = ctx["r"], ctx["wl"], ctx["rank"], ctx["world"]
+    import ovr_b200
+    capi = ovr_b200.capi
+    e2e = run_e2e(ctx, args)
+    if rank != 0:
+        return
+    # ---- roofline of the render kernel: texture/L1 sampling rate (32 B per executed trilinear fetch) ----
+    capi.lib().b200vr_set_tile_partition(r.handle, 0, 1)
+    p_fetch, fetch_rows = measure_fetch_peak(r, capi, r.sampler)
+    pk = peaks()
+    n = wl["n"]
+    kernel_s = ctx["kernel_ms"] * 1e-3
+    ach = 32.0 * ctx["fetches"] / world / kernel_s / 1e9 if kernel_s > 0 else 0.0   # per GPU: rank-max kernel time
+    peak = 32.0 * p_fetch / 1e9
+    hbm_bytes = 4.0 * n ** 3 + 12.0 * ((n + 15) // 16) ** 3 + 28.0 * wl["width"] * wl["height"]
+    hbm_ach = hbm_bytes * args.steps / kernel_s / 1e9 if kernel_s > 0 else 0.0
+    roofline = {"bound": "tex", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if peak else None, "traffic": None,
+                "kernel": "raymarch_kernel" if wl["mode"] == "raymarch" else "pathtrace_kernel",
+                "note": "texture/L1 sampling roofline: 32 B x executed trilinear fetches / mean kernel time (CUDA events on the launch "
+                        "stream); peak = best b200vr_bench_fetch rate x 32 B measured in this run",
+                "kernel_ms_per_launch": ctx["kernel_ms"] / args.steps, "fetch_bench": fetch_rows,
+                "hbm": {"achieved": hbm_ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_ach / pk["hbm_gbs"],
+                        "bytes_per_launch_upper_bound": hbm_bytes, "peak_source": pk["source"]}}
+    line = {"metric": METRIC, "value": ctx["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ctx["t_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args, wl), "sampler": args.sampler, "skip_empty": not args.no_skip,
+                       "parallelism": f"sort-first x{world}" if world > 1 else "1 GPU",
+                       "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
+                       "samples_per_frame": ctx["samples"] / args.steps, "fetches_per_frame": ctx["fetches"] / args.steps},
+            "clocks": ctx["clk"], "e2e": e2e, "gpu_launches": ctx["gpu_launches"], "roofline": roofline}
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import pyoracle
+        vol = np.empty((n, n, n), np.float32)
+        r._ck(capi.lib().b200vr_download_volume(r.handle, vol.ctypes.data_as(C.c_void_p)))
+        stride = args.cpu_stride or auto_stride(pyoracle.hardware_threads())
+        v, ms, info = cpu_oracle_run(wl, ctx["scene"], 1, 0, stride, volume=vol)
+        line["cpu_baseline"] = dict(info, value=v, unit=UNIT, ms_sampled_frame=ms)
+    print(json.dumps(line), flush=True)
+    r.close()
+
+
+if __name__ == "__main__":
+    main()
