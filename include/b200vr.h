@@ -97,6 +97,13 @@ int b200vr_download_volume(b200vr_t* h, float* host_voxels); /* fp32 copy of the
  * values_out: n floats; rgba_out: 4n floats or NULL. */
 int b200vr_probe(b200vr_t* h, const float* points, int64_t n, int sampler, float* values_out, float* rgba_out);
 
+/* known-answer probe of the 1-D filter: builds the reference's hardware TF texture (1-D CUDA array, linear filter, clamp,
+ * normalised coordinates: CreateArray1DScalarOptix7 / CreateArray1DFloat4Optix7, array.cpp:116-141,217-245) from `table`
+ * (n entries of `channels` = 1 or 4 floats) and fetches it at n_u coordinates with tex1D (hw_out), and evaluates the
+ * kernels' shared-memory software filter at the same coordinates (sw_out). Both outputs: n_u * channels floats. */
+int b200vr_probe_tex1d(b200vr_t* h, const float* table, int n, int channels, const float* u, int64_t n_u,
+                       float* hw_out, float* sw_out);
+
 /* fetch-rate micro-benchmark on the resident volume (roofline denominator P_fetch): n_warps bundles of 8x4
  * parallel rays march `iters` unit steps along dir (voxels/step) inside a footprint^3-voxel cube; reports the CUDA-event
  * time and the number of trilinear fetches issued. */

@@ -51,6 +51,7 @@ SYMBOLS = {
     "b200vr_get_macrocells": (C.c_int, [_P, _IP, _P, _P]),
     "b200vr_download_volume": (C.c_int, [_P, _P]),
     "b200vr_probe": (C.c_int, [_P, _FP, C.c_int64, C.c_int, _FP, _FP]),
+    "b200vr_probe_tex1d": (C.c_int, [_P, _FP, C.c_int, C.c_int, _FP, C.c_int64, _FP, _FP]),
     "b200vr_bench_fetch": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _FP, C.c_int, _FP, C.POINTER(C.c_uint64)]),
     "b200vr_set_transfer_function": (C.c_int, [_P, _FP, C.c_int, _FP, C.c_int, C.c_float, C.c_float]),
     "b200vr_set_camera": (C.c_int, [_P, _FP, _FP, _FP, _FP]),

@@ -793,6 +793,54 @@ extern "C" int b200vr_probe(b200vr_t* h, const float* points, int64_t n, int sam
   return B200VR_OK;
 }
 
+extern "C" int b200vr_probe_tex1d(b200vr_t* h, const float* table, int n, int channels, const float* u, int64_t n_u, float* hw_out,
+                                  float* sw_out)
+{
+  if (!h || !table || !u || !hw_out || !sw_out || n <= 0 || n_u < 0 || (channels != 1 && channels != 4)) return B200VR_EINVAL;
+  if (n_u == 0) return B200VR_OK;
+  CK(cudaSetDevice(h->device));
+  const cudaChannelFormatDesc desc = channels == 1 ? cudaCreateChannelDesc<float>() : cudaCreateChannelDesc<float4>();
+  cudaArray_t arr = nullptr;
+  CK(cudaMallocArray(&arr, &desc, (size_t)n, 0));
+  const size_t row = (size_t)n * channels * sizeof(float);
+  CK(cudaMemcpy2DToArray(arr, 0, 0, table, row, row, 1, cudaMemcpyHostToDevice));
+  cudaResourceDesc rd;
+  std::memset(&rd, 0, sizeof(rd));
+  rd.resType = cudaResourceTypeArray;
+  rd.res.array.array = arr;
+  cudaTextureDesc td;
+  std::memset(&td, 0, sizeof(td));
+  td.addressMode[0] = cudaAddressModeClamp;
+  td.filterMode = cudaFilterModeLinear;
+  td.readMode = cudaReadModeElementType;
+  td.normalizedCoords = 1;
+  cudaTextureObject_t tex = 0;
+  CK(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
+  float *d_tab = nullptr, *d_u = nullptr, *d_hw = nullptr, *d_sw = nullptr;
+  CK(cudaMalloc(&d_tab, row));
+  CK(cudaMalloc(&d_u, (size_t)n_u * sizeof(float)));
+  CK(cudaMalloc(&d_hw, (size_t)n_u * channels * sizeof(float)));
+  CK(cudaMalloc(&d_sw, (size_t)n_u * channels * sizeof(float)));
+  CK(cudaMemcpyAsync(d_tab, table, row, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(d_u, u, (size_t)n_u * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+  const int grid = grid_for((size_t)n_u, 128, h->sm_count);
+  if (channels == 1)
+    probe_tex1d_kernel<1><<<grid, 128, 0, h->stream>>>(tex, d_tab, n, d_u, (long long)n_u, d_hw, d_sw);
+  else
+    probe_tex1d_kernel<4><<<grid, 128, 0, h->stream>>>(tex, d_tab, n, d_u, (long long)n_u, d_hw, d_sw);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(hw_out, d_hw, (size_t)n_u * channels * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(sw_out, d_sw, (size_t)n_u * channels * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  cudaFree(d_tab);
+  cudaFree(d_u);
+  cudaFree(d_hw);
+  cudaFree(d_sw);
+  cudaDestroyTextureObject(tex);
+  cudaFreeArray(arr);
+  return B200VR_OK;
+}
+
 extern "C" int b200vr_bench_fetch(b200vr_t* h, int sampler, int footprint, int iters, const float dir[3], int ctas_per_sm,
                                   float* ms_out, uint64_t* fetches_out)
 {

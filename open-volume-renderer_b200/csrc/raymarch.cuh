@@ -74,6 +74,26 @@ __global__ void probe_kernel(const __grid_constant__ LaunchParams P, const float
   }
 }
 
+// 1-D known-answer probe: hardware tex1D vs the software filter used for the shared-memory transfer function
+template<int CH>
+__global__ void probe_tex1d_kernel(cudaTextureObject_t tex, const float* __restrict__ table, int n, const float* __restrict__ u,
+                                   long long n_u, float* __restrict__ hw, float* __restrict__ sw)
+{
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_u; i += (long long)gridDim.x * blockDim.x) {
+    int i0, i1, a;
+    hw_coord(u[i], n, i0, i1, a);
+    if (CH == 1) {
+      hw[i] = tex1D<float>(tex, u[i]);
+      sw[i] = lerp_hw(table[i0], table[i1], a);
+    }
+    else {
+      const float4 t = tex1D<float4>(tex, u[i]);
+      hw[4 * i] = t.x, hw[4 * i + 1] = t.y, hw[4 * i + 2] = t.z, hw[4 * i + 3] = t.w;
+      for (int c = 0; c < 4; c++) sw[4 * i + c] = lerp_hw(table[4 * i0 + c], table[4 * i1 + c], a);
+    }
+  }
+}
+
 // fetch-rate micro-benchmark (the P_fetch denominator of SURVEY 8d): every warp marches an 8x4 bundle of parallel rays,
 // one voxel apart, `iters` unit steps through a cubic footprint of the resident volume; nothing but the fetch and an add.
 template<int SAMPLER>

@@ -21,9 +21,11 @@ extern "C" {
 #endif
 
 enum { OVR_ORACLE_SHADING_NONE = 0, OVR_ORACLE_SHADING_REF = 1 };
-/* how the texture unit's interpolation weight is quantised (CUDA Programming Guide, "Linear Filtering":
- * 9-bit fixed point with 8 fractional bits) */
-enum { OVR_ORACLE_FILTER_FIXED8_RN = 0, OVR_ORACLE_FILTER_FIXED8_TRUNC = 1, OVR_ORACLE_FILTER_FP32 = 2 };
+/* texture-filter model. HW = the B200 texture unit as measured on the GPU box (integer 8-tap weights split z -> x -> y,
+ * oracle_sample.cpp); the other three follow the CUDA Programming Guide text ("Linear Filtering": separable, weight in
+ * 9-bit fixed point with 8 fractional bits) and exist for the calibration tests. */
+enum { OVR_ORACLE_FILTER_FIXED8_RN = 0, OVR_ORACLE_FILTER_FIXED8_TRUNC = 1, OVR_ORACLE_FILTER_FP32 = 2,
+       OVR_ORACLE_FILTER_HW = 3 };
 /* macrocell value-range footprint */
 enum { OVR_ORACLE_MC_REFERENCE = 0 /* sp_singlemc.cu:36-42 as written (upper apron missing) */,
        OVR_ORACLE_MC_CONSERVATIVE = 1 /* voxels 16c-2 .. 16c+17, what the B200 device builds */ };
@@ -100,6 +102,8 @@ int ovr_oracle_clip(const float org[3], const float dir[3], const float lo[3], c
 void ovr_oracle_sample_volume(const float* voxels, const int32_t dims[3], int filter_mode, const float* pts,
                               int64_t n, float* out);
 void ovr_oracle_sample_tf(const ovr_oracle_scene* s, const float* values, int64_t n, float* rgba);
+/* 1-D texture fetch model (normalised coordinate, clamp, linear): table of n entries x channels (1 or 4) floats */
+void ovr_oracle_tex1d(const float* table, int n, int channels, int filter_mode, const float* u, int64_t n_u, float* out);
 /* synthetic procedural volume of SURVEY 8(d): brick [org, org+bdims) of noise(N, seed) */
 void ovr_oracle_noise(int32_t n, uint32_t seed, const int32_t org[3], const int32_t bdims[3], float* out,
                       int num_threads);

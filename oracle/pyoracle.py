@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 SHADING_NONE, SHADING_REF = 0, 1
-FILTER_FIXED8_RN, FILTER_FIXED8_TRUNC, FILTER_FP32 = 0, 1, 2
+FILTER_FIXED8_RN, FILTER_FIXED8_TRUNC, FILTER_FP32, FILTER_HW = 0, 1, 2, 3
 MC_REFERENCE, MC_CONSERVATIVE = 0, 1
 
 _f3 = C.c_float * 3
@@ -147,12 +147,22 @@ def clip(org, dr, lo=(0, 0, 0), hi=(1, 1, 1)):
     return bool(hit), t0.value, t1.value
 
 
-def sample_volume(vol, pts, filter_mode=FILTER_FIXED8_RN):
+def sample_volume(vol, pts, filter_mode=FILTER_HW):
     vol = np.ascontiguousarray(vol, np.float32)
     pts = np.ascontiguousarray(pts, np.float32)
     out = np.empty(len(pts), np.float32)
     dims = (vol.shape[2], vol.shape[1], vol.shape[0])
     lib().ovr_oracle_sample_volume(_fp(vol), _i3(*dims), filter_mode, _fp(pts), C.c_int64(len(pts)), _fp(out))
+    return out
+
+
+def tex1d(table, u, filter_mode=FILTER_HW):
+    """table [n] or [n, 4] float32; u [m] float32 normalised coordinates -> [m] or [m, 4]."""
+    table = np.ascontiguousarray(table, np.float32)
+    u = np.ascontiguousarray(u, np.float32)
+    ch = 1 if table.ndim == 1 else table.shape[1]
+    out = np.empty(len(u) if ch == 1 else (len(u), ch), np.float32)
+    lib().ovr_oracle_tex1d(_fp(table), len(table), ch, filter_mode, _fp(u), C.c_int64(len(u)), _fp(out))
     return out
 
 
@@ -169,7 +179,7 @@ class OracleScene:
     attributes: volume [nz,ny,nx] f32, obj_to_world (12,), tf_color [Nc,4], tf_alpha [Na], tf_range (lo,hi),
     step, base, cam (dict from camera()), width, height, spp, shading."""
 
-    def __init__(self, desc, skip_empty=False, filter_mode=FILTER_FIXED8_RN, mc_mode=MC_CONSERVATIVE,
+    def __init__(self, desc, skip_empty=False, filter_mode=FILTER_HW, mc_mode=MC_CONSERVATIVE,
                  build_macrocells=True):
         self.vol = np.ascontiguousarray(desc.volume, np.float32)
         self.tf_color = np.ascontiguousarray(desc.tf_color, np.float32).reshape(-1, 4)

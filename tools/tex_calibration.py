@@ -27,7 +27,7 @@ def probe(r, pts, sampler):
 
 
 for n in (2, 3, 40, 64, 512):
-    for axis in (0, 2):
+    for axis in (0, 1, 2):
         dims = [4, 4, 4]
         dims[axis] = n
         nx, ny, nz = dims
@@ -68,6 +68,22 @@ for n in (2, 3, 40, 64, 512):
         out[f"n{n}_a{axis}_whw"] = w_hw[::64]
         out[f"n{n}_a{axis}_steps"] = step_frac
         r.close()
+
+# random volume + random points: raw material for fitting the unit's lerp arithmetic offline
+rng = np.random.default_rng(7)
+for tag, dims in (("a", (16, 12, 10)), ("b", (37, 5, 64))):
+    nx, ny, nz = dims
+    vol = rng.uniform(0.0, 1.0, (nz, ny, nx)).astype(np.float32)
+    sc = S.Scene(S.Volume(vol), S.make_tfn("ramp", value_range=(0.0, 1.0)), S.camera_preset("front", dims))
+    r = ovr_b200.create_renderer("b200")
+    r.set_fbsize((16, 16))
+    r.init(sc, sc.camera)
+    pts = rng.uniform(0.0, 1.0, (200000, 3)).astype(np.float32)
+    out[f"rand_{tag}_vol"] = vol
+    out[f"rand_{tag}_pts"] = pts
+    out[f"rand_{tag}_tex"] = probe(r, pts, capi.SAMPLER_TEX3D)
+    out[f"rand_{tag}_man"] = probe(r, pts, capi.SAMPLER_MANUAL)
+    r.close()
 
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 np.savez_compressed(os.path.join(ROOT, "gpurun_out", "tex_calibration.npz"), **out)
