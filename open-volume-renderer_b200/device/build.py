@@ -1,0 +1,95 @@
+"""Builds the OVR plugin and the drop-in driver (needs the reference tree; the products travel to the GPU box prebuilt):
+
+  build/ovr/libdevice_b200.so   DeviceB200 : ovr::MainRenderer (device_b200.cpp) compiled against the reference's UNCHANGED
+                                headers, linked to open-volume-renderer_b200/libb200vr.so
+  build/ovr/renderbatch         the reference's own apps/main_batch.cpp + host sources (renderer.cpp, scene.cpp,
+                                serializer_{vidi3d,diva}.cpp, imageio.cpp, dylink/Library.cpp) compiled where they lie under
+                                /root/reference with OVR_BUILD_OPTIX7 / OVR_BUILD_OSPRAY undefined -- nothing is copied
+                                into this repo. `renderbatch --device b200 ...` then loads the plugin through
+                                create_renderer (ovr/renderer.cpp:42-61).
+
+The reference's CMake build is not used (it needs OptiX / OSPRay / TBB / GLFW); this is the short recipe the task allows.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = os.environ.get("OVR_REFERENCE", "/root/reference")
+OUT = os.path.join(ROOT, "build", "ovr")
+PKG = os.path.join(ROOT, "open-volume-renderer_b200")
+
+INC = [REF, f"{REF}/ovr", f"{REF}/ovr/common", f"{REF}/ovr/common/cuda", f"{REF}/extern", f"{REF}/extern/gdt",
+       f"{REF}/extern/tfn/colormaps", f"{REF}/extern/tfn", f"{REF}/apps", "/usr/local/cuda/include", f"{ROOT}/include"]
+# OVR_BUILD_CUDA_DEVICES must have the same value in the host executable and the plugin: it changes the layout of
+# CrossDeviceBuffer (ovr/common/cross_device_buffer.h:22-40)
+DEFS = ["-DOVR_BUILD_CUDA_DEVICES"]
+CXX = ["g++", "-std=c++17", "-fPIC", "-w"] + DEFS + [f"-I{i}" for i in INC]
+
+HOST_SOURCES = [
+    ("apps/main_batch.cpp", ["-O1"]),
+    ("ovr/renderer.cpp", ["-O1"]),
+    ("ovr/scene.cpp", ["-O1"]),
+    ("ovr/serializer/serializer_vidi3d.cpp", ["-O1"]),
+    # serializer_usda.cpp is optional in the reference (OVR_BUILD_SCENE_USD, ovr/CMakeLists.txt:90-94) and needs Pixar USD
+    # (pxr/...), which is not installed here: USDA scenes stay disabled exactly as in a reference build without USD
+    # create_json_scene is `inline` in its .cpp (serializer_diva.cpp:13) yet called from main_batch.cpp:245
+    ("ovr/serializer/serializer_diva.cpp", ["-O0", "-fkeep-inline-functions"]),
+    ("ovr/common/imageio.cpp", ["-O1"]),
+    ("ovr/common/dylink/Library.cpp", ["-O1"]),
+]
+
+
+def colormap_sources():
+    """extern/tfn/colormaps/**/*.cpp: the embedded colour tables scene.cpp's CreateColorMap links against
+    (extern/tfn/colormaps/CMakeLists.txt lists the same files)."""
+    out = []
+    base = os.path.join(REF, "extern", "tfn", "colormaps")
+    for d, _, files in os.walk(base):
+        for f in sorted(files):
+            if f.endswith(".cpp"):
+                out.append((os.path.relpath(os.path.join(d, f), REF), ["-O0"]))
+    return out
+
+
+def run(cmd):
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("command failed: " + " ".join(cmd) + "\n" + r.stdout[-4000:] + r.stderr[-4000:])
+
+
+def newer(target, deps):
+    return os.path.exists(target) and all(os.path.getmtime(target) >= os.path.getmtime(d) for d in deps if os.path.exists(d))
+
+
+def build(force=False):
+    if not os.path.isdir(os.path.join(REF, "ovr")):
+        print(f"[device/build.py] {REF} not present: keeping prebuilt build/ovr products")
+        return None
+    os.makedirs(OUT, exist_ok=True)
+    plugin = os.path.join(OUT, "libdevice_b200.so")
+    srcs = [os.path.join(HERE, "device_b200.cpp"), os.path.join(HERE, "device_b200.h"), os.path.join(ROOT, "include", "b200vr.h")]
+    if force or not newer(plugin, srcs):
+        run(CXX + ["-O2", "-shared", "-o", plugin, srcs[0], f"-L{PKG}", "-lb200vr",
+                   "-Wl,-rpath,$ORIGIN:$ORIGIN/../../open-volume-renderer_b200", "-L/usr/local/cuda/lib64", "-lcudart"])
+    exe = os.path.join(OUT, "renderbatch")
+    if force or not os.path.exists(exe):
+        def compile_one(item):
+            rel, flags = item
+            obj = os.path.join(OUT, rel.replace("/", "_").replace(".cpp", ".o"))
+            run(CXX + flags + ["-c", os.path.join(REF, rel), "-o", obj])
+            return obj
+        with ThreadPoolExecutor(max_workers=8) as ex:
+            objs = list(ex.map(compile_one, HOST_SOURCES + colormap_sources()))
+        # -rdynamic: objectFactory also searches the executable itself (Library.cpp:169-191)
+        run(["g++", "-rdynamic", "-o", exe] + objs + ["-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread",
+                                                       "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
+        for o in objs:
+            os.remove(o)
+    return exe
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv))

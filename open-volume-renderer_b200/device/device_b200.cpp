@@ -1,0 +1,218 @@
+// DeviceB200: ovr::MainRenderer back-end on top of the b200vr C ABI (see device_b200.h).
+// Host logic mirrors what DeviceOptix7::Impl does around its launch (ovr/devices/optix7/device_impl.cpp:70-302): which
+// parameter changes are applied in commit(), what resets the accumulation, what mapframe hands out. The arithmetic of
+// the frame itself lives in the CUDA kernels behind b200vr_render.
+#include "device_b200.h"
+
+#include "b200vr.h"
+
+#include <ovr/common/dylink/ObjectFactory.h>
+
+#include <chrono>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace ovr::b200 {
+
+namespace {
+
+int
+to_b200vr_type(ValueType t)
+{
+  switch (t) {
+  case VALUE_TYPE_UINT8: return B200VR_TYPE_UINT8;
+  case VALUE_TYPE_INT8: return B200VR_TYPE_INT8;
+  case VALUE_TYPE_UINT16: return B200VR_TYPE_UINT16;
+  case VALUE_TYPE_INT16: return B200VR_TYPE_INT16;
+  case VALUE_TYPE_UINT32: return B200VR_TYPE_UINT32;
+  case VALUE_TYPE_INT32: return B200VR_TYPE_INT32;
+  case VALUE_TYPE_FLOAT: return B200VR_TYPE_FLOAT;
+  case VALUE_TYPE_DOUBLE: return B200VR_TYPE_DOUBLE;
+  default: throw std::runtime_error("b200: unsupported volume value type"); // array.cpp:347
+  }
+}
+
+int
+env_int(const char* name, int fallback)
+{
+  const char* v = std::getenv(name);
+  return v ? std::atoi(v) : fallback;
+}
+
+} // namespace
+
+struct DeviceB200::Impl {
+  DeviceB200* parent = nullptr;
+  b200vr_t* handle = nullptr;
+  b200vr_params prm;
+  bool initialized = false;
+  bool prm_dirty = false;
+  vec2i fbsize = vec2i(0, 0);
+#ifndef OVR_BUILD_CUDA_DEVICES
+  std::vector<float> host_rgba, host_grad; // host executable built without CUDA buffers: frames are handed out on the CPU
+#endif
+
+  ~Impl()
+  {
+    if (handle) b200vr_destroy(handle);
+  }
+
+  void check(int rc, const char* what) const
+  {
+    if (rc != B200VR_OK)
+      throw std::runtime_error(std::string("b200: ") + what + ": " + b200vr_last_error(handle));
+  }
+
+  void init(DeviceB200* p)
+  {
+    if (initialized) throw std::runtime_error("b200: device already initialized!"); // device_impl.cpp:73-75
+    parent = p;
+    const int rc = b200vr_create(&handle, env_int("OVR_B200_CUDA_DEVICE", 0));
+    if (rc != B200VR_OK) throw std::runtime_error(std::string("b200: cannot create device: ") + b200vr_last_error(nullptr));
+    b200vr_default_params(&prm);
+    // device-private switches that MainRenderer has no setter for (they default to the reference's behaviour)
+    prm.shading = env_int("OVR_B200_SHADING", B200VR_SHADING_REF);
+    prm.sampler = env_int("OVR_B200_SAMPLER", B200VR_SAMPLER_TEX3D);
+    prm.skip_empty = env_int("OVR_B200_SKIP_EMPTY", 1);
+    build_scene(parent->current_scene);
+    initialized = true;
+  }
+
+  // buildScene (device_impl.cpp:283-302): exactly the scenes parse_single_volume_scene accepts
+  void build_scene(const Scene& scene)
+  {
+    const auto& v = parse_single_volume_scene(scene, scene::Volume::STRUCTURED_REGULAR_VOLUME).structured_regular;
+    const vec3f scale = v.grid_spacing * vec3f(v.data->dims);
+    const vec3f translate = v.grid_origin;
+    const float otw[12] = { scale.x, 0.f, 0.f, translate.x, 0.f, scale.y, 0.f, translate.y, 0.f, 0.f, scale.z, translate.z };
+    check(b200vr_set_volume(handle, v.data->data(), to_b200vr_type(v.data->type), v.data->dims.x, v.data->dims.y,
+                            v.data->dims.z, otw, /*on_device=*/0),
+          "set_volume");
+    prm.sampling_rate = scene.volume_sampling_rate;
+    prm_dirty = true;
+  }
+
+  void swap() { check(b200vr_swap(handle), "swap"); }
+
+  // Impl::commit (device_impl.cpp:113-197): only changed parameters are applied; every change resets the accumulation
+  // (the C ABI setters do that themselves)
+  void commit()
+  {
+    auto& pp = parent->params;
+    bool size_changed = false;
+    if (pp.fbsize.update()) {
+      fbsize = pp.fbsize.ref();
+      if (fbsize.x > 0 && fbsize.y > 0) check(b200vr_resize(handle, fbsize.x, fbsize.y), "resize");
+      size_changed = true;
+    }
+    if (pp.camera.update() || size_changed) {
+      const Camera& c = pp.camera.ref();
+      const float from[3] = { c.from.x, c.from.y, c.from.z }, at[3] = { c.at.x, c.at.y, c.at.z }, up[3] = { c.up.x, c.up.y, c.up.z };
+      check(b200vr_set_camera_lookat(handle, from, at, up, c.perspective.fovy), "set_camera");
+    }
+    if (pp.tfn.update()) {
+      const auto& t = pp.tfn.ref();
+      if (!t.tfn_colors.empty() && !t.tfn_alphas.empty())
+        check(b200vr_set_transfer_function(handle, t.tfn_colors.data(), (int)(t.tfn_colors.size() / 3), t.tfn_alphas.data(),
+                                           (int)(t.tfn_alphas.size() / 2), t.tfn_value_range.x, t.tfn_value_range.y),
+              "set_transfer_function");
+    }
+    if (pp.sample_per_pixel.update()) {
+      prm.spp = pp.sample_per_pixel.ref();
+      prm_dirty = true;
+    }
+    if (pp.path_tracing.update()) {
+      prm.mode = pp.path_tracing.ref() ? B200VR_MODE_PATHTRACE : B200VR_MODE_RAYMARCH;
+      prm_dirty = true;
+    }
+    if (pp.frame_accumulation.update()) {
+      prm.accumulate = pp.frame_accumulation.ref() ? 1 : 0;
+      prm_dirty = true;
+    }
+    if (pp.volume_sampling_rate.update()) {
+      prm.sampling_rate = pp.volume_sampling_rate.get();
+      prm_dirty = true;
+    }
+    // sparse sampling / focus / lights / materials: accepted and ignored, like the optix7 device ignores scene lights
+    // and materials; sparse sampling is a "next" row
+    pp.focus_center.update();
+    pp.focus_scale.update();
+    pp.base_noise.update();
+    pp.sparse_sampling.update();
+    if (prm_dirty) {
+      check(b200vr_set_params(handle, &prm), "set_params");
+      prm_dirty = false;
+    }
+  }
+
+  void render()
+  {
+    if (fbsize.x <= 0 || fbsize.y <= 0) return; // device_impl.cpp:215-216
+    check(b200vr_render(handle, nullptr), "render"); // synchronous, like DeviceOptix7::render (device.cpp:34-43)
+    parent->variance = 0.f;                          // device_impl.cpp:266
+  }
+
+  void mapframe(FrameBufferData* fb)
+  {
+    const size_t n = (size_t)fbsize.x * (size_t)fbsize.y;
+#ifdef OVR_BUILD_CUDA_DEVICES
+    void *rgba = nullptr, *grad = nullptr;
+    check(b200vr_map(handle, &rgba, &grad), "map");
+    fb->rgba->set_data(rgba, n * sizeof(vec4f), CrossDeviceBuffer::DEVICE_CUDA); // non-owning (device_impl.cpp:271-281)
+    fb->grad->set_data(grad, n * sizeof(vec3f), CrossDeviceBuffer::DEVICE_CUDA);
+#else
+    host_rgba.resize(n * 4);
+    host_grad.resize(n * 3);
+    check(b200vr_download(handle, host_rgba.data(), host_grad.data()), "download");
+    fb->rgba->set_data(host_rgba.data(), n * sizeof(vec4f), CrossDeviceBuffer::DEVICE_CPU);
+    fb->grad->set_data(host_grad.data(), n * sizeof(vec3f), CrossDeviceBuffer::DEVICE_CPU);
+#endif
+  }
+};
+
+DeviceB200::~DeviceB200()
+{
+  pimpl.reset();
+}
+
+DeviceB200::DeviceB200() : MainRenderer(), pimpl(new Impl()) {}
+
+void
+DeviceB200::init(int /*argc*/, const char** /*argv*/)
+{
+  pimpl->init(this);
+  pimpl->commit();
+}
+
+void
+DeviceB200::swap()
+{
+  pimpl->swap();
+}
+
+void
+DeviceB200::commit()
+{
+  pimpl->commit();
+}
+
+void
+DeviceB200::render()
+{
+  const auto start = std::chrono::high_resolution_clock::now();
+  pimpl->render();
+  const auto end = std::chrono::high_resolution_clock::now();
+  render_time += std::chrono::duration<double, std::milli>(end - start).count();
+}
+
+void
+DeviceB200::mapframe(FrameBufferData* fb)
+{
+  pimpl->mapframe(fb);
+}
+
+} // namespace ovr::b200
+
+OVR_REGISTER_OBJECT(ovr::MainRenderer, renderer, ovr::b200::DeviceB200, b200)

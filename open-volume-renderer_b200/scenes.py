@@ -66,14 +66,23 @@ RAINBOW_CONTROLS = [  # tfn::TransferFunctionCore::fromRainbowMap / the bundled 
 
 
 def rasterize_color_controls(controls=RAINBOW_CONTROLS, n=1024):
-    """Piecewise-linear rasterisation of colour control points into n float4 entries (w = 1), the job of
-    tfn::TransferFunctionCore::updateColorMap (extern/tfn/core.h:598-634)."""
-    pos = np.array([c[0] for c in controls], np.float64)
-    rgb = np.array([c[1] for c in controls], np.float64)
-    x = np.arange(n, dtype=np.float64) / (n - 1)
-    out = np.ones((n, 4), np.float32)
-    for ch in range(3):
-        out[:, ch] = np.interp(x, pos, rgb[:, ch]).astype(np.float32)
+    """Colour control points -> n float4 entries (w = 1): tfn::TransferFunctionCore::updateColorMap
+    (extern/tfn/core.h:598-634) restated -- entry i is evaluated at the cell centre (i + 0.5) / n in fp32, between the
+    controls found by upper_bound, clamped to the end controls outside their span."""
+    f32 = np.float32
+    ctl = sorted(controls, key=lambda c: c[0])
+    pos = np.array([c[0] for c in ctl], f32)
+    rgb = np.array([c[1] for c in ctl], f32)
+    value = (np.arange(n, dtype=f32) + f32(0.5)) / f32(n)
+    ub = np.searchsorted(pos, value, side="right")          # first control with position > value
+    lo = np.clip(ub - 1, 0, len(ctl) - 1)
+    hi = np.clip(ub, 0, len(ctl) - 1)
+    span = np.abs(pos[hi] - pos[lo])
+    w = np.where((ub <= 0) | (ub >= len(ctl)), f32(0), np.abs(value - pos[lo]) / np.where(span > 0, span, f32(1))).astype(f32)
+    out = np.ones((n, 4), f32)
+    out[:, :3] = rgb[lo] + w[:, None] * (rgb[hi] - rgb[lo])          # mix(x, y, a) = x + a * (y - x), core.h:77-81
+    out[ub <= 0, :3] = rgb[0]
+    out[ub >= len(ctl), :3] = rgb[-1]
     return out
 
 
