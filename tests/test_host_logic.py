@@ -33,7 +33,10 @@ def test_tile_partition_covers_every_pixel_once():
 def test_rainbow_rasterisation_and_presets():
     c = S.rasterize_color_controls(n=1024)
     assert c.shape == (1024, 4) and np.all(c[:, 3] == 1)
-    assert np.allclose(c[0, :3], [0, 0.364706, 1], atol=1e-6) and np.allclose(c[-1, :3], [0.662745, 0, 1], atol=1e-6)
+    # updateColorMap evaluates entry i at the cell centre (i + 0.5) / n (extern/tfn/core.h:606)
+    w = (0.5 / 1024) / (1 / 6)
+    assert np.allclose(c[0, :3], [0, 0.364706 + w * (1 - 0.364706), 1 + w * (0.976471 - 1)], atol=1e-6)
+    assert np.allclose(c[-1, :3], [1 + (1 - w) * (0.662745 - 1), 0, (1 - w) * 1], atol=1e-5)
     a = S.alpha_preset("sparse")
     assert a[0] == 0 and a[613] == 0 and a[-1] == np.float32(0.6) and (np.diff(a) >= 0).all()
     assert S.alpha_preset("dense").min() > 0
