@@ -70,7 +70,9 @@ def test_renderbatch_drives_the_b200_device(tmp_path, mode):
     W, H, n = 200, 120, 48
     path, vol = write_scene(tmp_path, n=n, sample_distance=0.5 if mode.endswith("rate2") else 1.0)
     exp = str(tmp_path / "out")
-    r = run_batch(path, exp, (W, H))
+    # main_batch always calls set_volume_sampling_rate(--sampling-rate, default 1), which overrides the scene file's
+    # 1 / sampleDistance in commit (main_batch.cpp:260, device_impl.cpp:189-195)
+    r = run_batch(path, exp, (W, H), extra=("--sampling-rate", "2") if mode.endswith("rate2") else ())
     assert r.returncode == 0, r.stderr[-2000:]
     assert "fps = " in r.stdout
     png = np.asarray(Image.open(exp + "000000.png").convert("RGBA"), np.uint8)
