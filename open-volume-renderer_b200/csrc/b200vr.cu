@@ -7,9 +7,12 @@
 #include "build.cuh"
 #include "pathtrace.cuh"
 #include "raymarch.cuh"
+#include "march_sm.cuh"
+#include "march_q.cuh"
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -41,6 +44,7 @@ struct b200vr {
   i3 mc = { 0, 0, 0 };
   float2* ranges = nullptr;
   float* majorants = nullptr;
+  float* maj_pad = nullptr;
   int* minmax = nullptr;
   // transfer function
   float4* tf_color = nullptr;
@@ -158,6 +162,8 @@ static void free_volume(b200vr_t* h)
   cudaFree(h->lin);
   cudaFree(h->ranges);
   cudaFree(h->majorants);
+  cudaFree(h->maj_pad);
+  h->maj_pad = nullptr;
   h->tex = 0;
   h->array = nullptr;
   h->lin = nullptr;
@@ -237,6 +243,9 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12])
   CK(cudaMalloc(&h->ranges, n_cells * sizeof(float2)));
   CK(cudaMalloc(&h->majorants, n_cells * sizeof(float)));
   CK(cudaMemsetAsync(h->majorants, 0, n_cells * sizeof(float), h->stream));
+  const size_t n_pad = (size_t)(h->mc.x + 1) * (h->mc.y + 1) * (h->mc.z + 1);
+  CK(cudaMalloc(&h->maj_pad, n_pad * sizeof(float)));
+  CK(cudaMemsetAsync(h->maj_pad, 0, n_pad * sizeof(float), h->stream));
   const int init[2] = { 0x7fffffff, (int)0x80000000 };
   CK(cudaMemcpyAsync(h->minmax, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
   macrocell_range_kernel<<<(unsigned)n_cells, RANGE_THREADS, 0, h->stream>>>(h->lin, h->nx, h->ny, h->nz, h->mc.x, h->mc.y,
@@ -375,6 +384,10 @@ static int rebuild_majorants(b200vr_t* h)
   const int grid = std::max(1, std::min((n_cells + threads - 1) / threads, h->sm_count * 8));
   majorant_kernel<<<grid, threads, (size_t)h->n_alpha * sizeof(float), h->stream>>>(h->ranges, n_cells, h->tf_alpha, h->n_alpha,
                                                                                      h->tf_lower, h->tf_upper, h->majorants);
+  CK(cudaGetLastError());
+  const int n_pad = (h->mc.x + 1) * (h->mc.y + 1) * (h->mc.z + 1);
+  majorant_pad_kernel<<<std::max(1, std::min((n_pad + threads - 1) / threads, h->sm_count * 8)), threads, 0, h->stream>>>(
+    h->majorants, h->mc.x, h->mc.y, h->mc.z, h->maj_pad);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));
   return B200VR_OK;
@@ -544,21 +557,53 @@ extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
 
 typedef void (*render_kernel_t)(const LaunchParams);
 
-static render_kernel_t pick_kernel(const b200vr_params& p)
+// Which kernel renders a frame. Texture sampler: deferred-shading queue kernel (march_q.cuh) for the reference's
+// gradient + shadow shading, the lean single-loop kernel (march_sm.cuh) without shading. Software sampler: the first
+// generation nested-loop kernel (raymarch.cuh). B200VR_KERNEL=legacy|sm forces the older ones for A/B runs.
+struct KernelChoice {
+  render_kernel_t fn;
+  int threads;
+  size_t smem;
+};
+
+static KernelChoice pick_kernel(const b200vr_t* h)
 {
-  if (p.mode == B200VR_MODE_PATHTRACE)
-    return p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
+  const b200vr_params& p = h->prm;
+  const char* force = std::getenv("B200VR_KERNEL");
+  const bool legacy = force && std::strcmp(force, "legacy") == 0, sm = force && std::strcmp(force, "sm") == 0;
+  KernelChoice k;
+  k.threads = RENDER_THREADS;
+  k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
+  if (p.mode == B200VR_MODE_PATHTRACE) {
+    k.fn = p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
+    return k;
+  }
+  if (p.sampler == B200VR_SAMPLER_TEX3D && !legacy) {
+    if (p.shading == B200VR_SHADING_REF && !sm) {
+      k.fn = p.skip_empty ? raymarch_q_kernel<true> : raymarch_q_kernel<false>;
+      k.threads = Q_THREADS;
+      k.smem = q_shared_bytes(h->n_color, h->n_alpha);
+      return k;
+    }
+    k.smem = tf_fast_shared_bytes(h->n_color, h->n_alpha);
+    if (p.shading == B200VR_SHADING_REF)
+      k.fn = p.skip_empty ? raymarch_sm_kernel<SHADING_REF, true> : raymarch_sm_kernel<SHADING_REF, false>;
+    else
+      k.fn = p.skip_empty ? raymarch_sm_kernel<SHADING_NONE, true> : raymarch_sm_kernel<SHADING_NONE, false>;
+    return k;
+  }
   const int key = (p.shading == B200VR_SHADING_REF ? 4 : 0) | (p.sampler == B200VR_SAMPLER_MANUAL ? 2 : 0) | (p.skip_empty ? 1 : 0);
   switch (key) {
-  case 0: return raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, false>;
-  case 1: return raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, true>;
-  case 2: return raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, false>;
-  case 3: return raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, true>;
-  case 4: return raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, false>;
-  case 5: return raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, true>;
-  case 6: return raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, false>;
-  default: return raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, true>;
+  case 0: k.fn = raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, false>; break;
+  case 1: k.fn = raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, true>; break;
+  case 2: k.fn = raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, false>; break;
+  case 3: k.fn = raymarch_kernel<SHADING_NONE, SAMPLER_MANUAL, true>; break;
+  case 4: k.fn = raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, false>; break;
+  case 5: k.fn = raymarch_kernel<SHADING_REF, SAMPLER_TEX3D, true>; break;
+  case 6: k.fn = raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, false>; break;
+  default: k.fn = raymarch_kernel<SHADING_REF, SAMPLER_MANUAL, true>; break;
   }
+  return k;
 }
 
 static void fill_launch_params(b200vr_t* h, LaunchParams& P)
@@ -578,6 +623,30 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.tf_lower = h->tf_lower, P.tf_upper = h->tf_upper;
   P.tf_scale = 1.f / (h->tf_upper - h->tf_lower); // volume.scale (volume.cpp:145)
   P.majorants = h->majorants;
+  P.maj_pad = h->maj_pad;
+  P.mcp_sy = h->mc.x + 1;
+  P.mcp_sz = (h->mc.x + 1) * (h->mc.y + 1);
+  {
+    // texture-unit coordinate of array1d_nodal for a table of n = 2^m entries:
+    // u*2^21 = fma(v, n-1, 0.5) * 2^(21-m); t = ((xi << (m+8)) + 2^20 >> 21) - 128 = (xi + 2^(12-m) - 128*2^(13-m)) >> (13-m)
+    auto setup = [](int n, float& mul, float& addf, int& addi, int& shift) {
+      int m = 0;
+      while ((1 << m) < n) m++;
+      if ((1 << m) != n || m > 12 || m < 1) {
+        mul = addf = 0.f;
+        addi = 0;
+        shift = -1;
+        return;
+      }
+      const float sc = (float)(1 << (21 - m));
+      mul = (float)(n - 1) * sc;
+      addf = 0.5f * sc;
+      shift = 13 - m;
+      addi = (1 << (12 - m)) - (128 << shift);
+    };
+    setup(h->n_alpha, P.tfa_mul, P.tfa_addf, P.tfa_addi, P.tfa_shift);
+    setup(h->n_color, P.tfc_mul, P.tfc_addf, P.tfc_addi, P.tfc_shift);
+  }
   P.mc = h->mc;
   P.cells_per_unit = mk3((float)h->nx, (float)h->ny, (float)h->nz) / (float)MC_SIZE;
   {
@@ -631,13 +700,14 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
 
   LaunchParams P;
   fill_launch_params(h, P);
-  const render_kernel_t kernel = pick_kernel(h->prm);
-  const size_t smem = tf_shared_bytes(h->n_color, h->n_alpha);
+  const KernelChoice kc = pick_kernel(h);
+  const render_kernel_t kernel = kc.fn;
+  const size_t smem = kc.smem;
   if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kernel, RENDER_THREADS, smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kernel, kc.threads, smem));
   if (per_sm < 1) return fail(h, B200VR_ECUDA, "render: kernel does not fit on an SM");
-  const int warps_per_cta = RENDER_THREADS / 32;
+  const int warps_per_cta = kc.threads / 32;
   const int want = (P.n_warp_tiles + warps_per_cta - 1) / warps_per_cta;
   const int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
   CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
@@ -645,7 +715,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   CK(cudaEventRecord(h->ev0, h->stream));
   if (P.n_warp_tiles > 0) {
     void* args[] = { (void*)&P };
-    CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3(RENDER_THREADS), args, smem, h->stream));
+    CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3((unsigned)kc.threads), args, smem, h->stream));
   }
   CK(cudaEventRecord(h->ev1, h->stream));
   Counters c;

@@ -158,6 +158,17 @@ __global__ void majorant_kernel(const float2* __restrict__ ranges, int n_cells, 
   }
 }
 
+// padded copy: cell (x, y, z) of the (mc+1)^3 grid = cell (min(x, mx-1), ...) of the mc^3 grid
+__global__ void majorant_pad_kernel(const float* __restrict__ maj, int mx, int my, int mz, float* __restrict__ pad)
+{
+  const int px = mx + 1, py = my + 1, pz = mz + 1;
+  const int n = px * py * pz;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int x = i % px, y = (i / px) % py, z = i / (px * py);
+    pad[i] = maj[min(x, mx - 1) + mx * (min(y, my - 1) + my * min(z, mz - 1))];
+  }
+}
+
 // ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------
 // slice layout: [owned super tile m][y in 32][x in 64][rgba]; pixels outside the image are zero in the slice
 template<bool PACK>

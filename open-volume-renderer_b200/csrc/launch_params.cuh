@@ -32,8 +32,14 @@ struct LaunchParams {
   const float* tf_alpha;
   int n_color, n_alpha;
   float tf_lower, tf_upper, tf_scale;
+  // power-of-two table fast path of the texture-unit coordinate model (sampling.cuh): q = (int(v*mul + add_f) + add_i) >> shift
+  // is the unit's 1/256-texel coordinate t; shift < 0 selects the generic 64-bit path
+  float tfa_mul, tfa_addf, tfc_mul, tfc_addf;
+  int tfa_addi, tfa_shift, tfc_addi, tfc_shift;
   // ---- macrocells ----
   const float* majorants;
+  const float* maj_pad;     // the same majorants on a grid padded by one replicated cell per axis: (mc+1)^3, so the cell
+  int mcp_sy, mcp_sz;       // of any position in [0, 1] (1.0 included) is addressable without clamps; strides in floats
   i3 mc;
   f3 cells_per_unit;        // dims / 16: object-space position -> macrocell coordinate
   f3 spac_rcp;              // 1 / (16 / dims) computed like sp_singlemc.cu:99-111 (delta tracking DDA)
