@@ -243,7 +243,7 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12])
   CK(cudaMalloc(&h->ranges, n_cells * sizeof(float2)));
   CK(cudaMalloc(&h->majorants, n_cells * sizeof(float)));
   CK(cudaMemsetAsync(h->majorants, 0, n_cells * sizeof(float), h->stream));
-  const size_t n_pad = (size_t)(h->mc.x + 1) * (h->mc.y + 1) * (h->mc.z + 1);
+  const size_t n_pad = (size_t)(h->mc.x + 2) * (h->mc.y + 2) * (h->mc.z + 2);
   CK(cudaMalloc(&h->maj_pad, n_pad * sizeof(float)));
   CK(cudaMemsetAsync(h->maj_pad, 0, n_pad * sizeof(float), h->stream));
   const int init[2] = { 0x7fffffff, (int)0x80000000 };
@@ -385,7 +385,7 @@ static int rebuild_majorants(b200vr_t* h)
   majorant_kernel<<<grid, threads, (size_t)h->n_alpha * sizeof(float), h->stream>>>(h->ranges, n_cells, h->tf_alpha, h->n_alpha,
                                                                                      h->tf_lower, h->tf_upper, h->majorants);
   CK(cudaGetLastError());
-  const int n_pad = (h->mc.x + 1) * (h->mc.y + 1) * (h->mc.z + 1);
+  const int n_pad = (h->mc.x + 2) * (h->mc.y + 2) * (h->mc.z + 2);
   majorant_pad_kernel<<<std::max(1, std::min((n_pad + threads - 1) / threads, h->sm_count * 8)), threads, 0, h->stream>>>(
     h->majorants, h->mc.x, h->mc.y, h->mc.z, h->maj_pad);
   CK(cudaGetLastError());
@@ -624,8 +624,10 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.tf_scale = 1.f / (h->tf_upper - h->tf_lower); // volume.scale (volume.cpp:145)
   P.majorants = h->majorants;
   P.maj_pad = h->maj_pad;
-  P.mcp_sy = h->mc.x + 1;
-  P.mcp_sz = (h->mc.x + 1) * (h->mc.y + 1);
+  P.mcp_sy = h->mc.x + 2;
+  P.mcp_sz = (h->mc.x + 2) * (h->mc.y + 2);
+  P.mcp_bias = (0x4B400000u - 1u) * (1u + (unsigned)P.mcp_sy + (unsigned)P.mcp_sz); // see pad_index_magic()
+  P.mcp_last = (unsigned)((h->mc.x + 2) * (h->mc.y + 2) * (h->mc.z + 2)) - 1u;
   {
     // texture-unit coordinate of array1d_nodal for a table of n = 2^m entries:
     // u*2^21 = fma(v, n-1, 0.5) * 2^(21-m); t = ((xi << (m+8)) + 2^20 >> 21) - 128 = (xi + 2^(12-m) - 128*2^(13-m)) >> (13-m)

@@ -158,14 +158,14 @@ __global__ void majorant_kernel(const float2* __restrict__ ranges, int n_cells, 
   }
 }
 
-// padded copy: cell (x, y, z) of the (mc+1)^3 grid = cell (min(x, mx-1), ...) of the mc^3 grid
+// padded copy: cell (x, y, z) of the (mc+2)^3 grid = cell (clamp(x-1), clamp(y-1), clamp(z-1)) of the mc^3 grid
 __global__ void majorant_pad_kernel(const float* __restrict__ maj, int mx, int my, int mz, float* __restrict__ pad)
 {
-  const int px = mx + 1, py = my + 1, pz = mz + 1;
+  const int px = mx + 2, py = my + 2, pz = mz + 2;
   const int n = px * py * pz;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int x = i % px, y = (i / px) % py, z = i / (px * py);
-    pad[i] = maj[min(x, mx - 1) + mx * (min(y, my - 1) + my * min(z, mz - 1))];
+    const int x = i % px - 1, y = (i / px) % py - 1, z = i / (px * py) - 1;
+    pad[i] = maj[min(max(x, 0), mx - 1) + mx * (min(max(y, 0), my - 1) + my * min(max(z, 0), mz - 1))];
   }
 }
 

@@ -38,8 +38,10 @@ struct LaunchParams {
   int tfa_addi, tfa_shift, tfc_addi, tfc_shift;
   // ---- macrocells ----
   const float* majorants;
-  const float* maj_pad;     // the same majorants on a grid padded by one replicated cell per axis: (mc+1)^3, so the cell
-  int mcp_sy, mcp_sz;       // of any position in [0, 1] (1.0 included) is addressable without clamps; strides in floats
+  const float* maj_pad;     // the same majorants on a grid padded by one replicated cell on every side: (mc+2)^3, so the
+  int mcp_sy, mcp_sz;       // cell of any position in [-eps, 1+eps] is addressable without per-axis clamps; strides in floats
+  unsigned int mcp_bias;    // folds the float->int magic constant and the +1 pad offset of pad_index_magic()
+  unsigned int mcp_last;    // number of padded cells - 1
   i3 mc;
   f3 cells_per_unit;        // dims / 16: object-space position -> macrocell coordinate
   f3 spac_rcp;              // 1 / (16 / dims) computed like sp_singlemc.cu:99-111 (delta tracking DDA)

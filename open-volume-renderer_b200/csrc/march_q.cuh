@@ -15,6 +15,10 @@
 namespace b200k {
 
 constexpr int Q_THREADS = 256;                 // 8 warps share one staged transfer function
+#ifndef B200VR_Q_MIN_CTAS
+#define B200VR_Q_MIN_CTAS 3
+#endif
+constexpr int Q_MIN_CTAS = B200VR_Q_MIN_CTAS;  // resident CTAs/SM wanted: 3 -> 24 warps/SM at <= 80 registers (4 -> 64 registers spills and measured slower)
 constexpr int Q_SLOTS = 64;                    // per-warp queue capacity: flushed at >= 32, one step adds <= 32
 constexpr int Q_SLOT_FLOATS = 8;               // task: p.xyz, s, w, -, -, -   result: C.xyz, G.xyz, -, -
 
@@ -25,7 +29,7 @@ __host__ __device__ __forceinline__ size_t q_shared_bytes(int n_color, int n_alp
 }
 
 template<bool SKIP>
-__global__ void __launch_bounds__(Q_THREADS, 2)
+__global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -42,7 +46,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
   S.rcp = mk3(__frcp_rn(S.d.x), __frcp_rn(S.d.y), __frcp_rn(S.d.z));
   S.sx = fabsf(S.d.x) < FLT_MIN, S.sy = fabsf(S.d.y) < FLT_MIN, S.sz = fabsf(S.d.z) < FLT_MIN;
   const lin3 wto_t = transposed(P.wto.l); // xfmNormal(otw, n) = transpose(inverse(otw.l)) * n
-  unsigned long long n_primary = 0, n_shadow = 0, n_gradient = 0, n_rays = 0; // warp totals, kept by lane 0
+  const f3 dcell = S.d * P.cells_per_unit;  // shadow direction in macrocell units
+  unsigned int c_primary = 0, c_shadow = 0, c_shaded = 0, c_rays = 0; // per lane, over all tiles of this warp
   const unsigned int lt_mask = (1u << lane) - 1u;
 
   for (;;) {
@@ -56,7 +61,6 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
     const bool inside = ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
     Tea rng((unsigned)P.frame_index, pixel_index);
-    unsigned int c_primary = 0, c_shadow = 0, c_shaded = 0, c_rays = 0;
     float out_a = 0.f;
     f3 out_c = mk3(0.f), out_g = mk3(0.f);
 
@@ -75,7 +79,6 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
       if (inside) c_rays++;
       float ty = fminf(t1, tx + step);
       alive = alive && ty > tx;
-      const f3 od_rcp = mk3(1.f / od.x, 1.f / od.y, 1.f / od.z);
       float A = 0.f;
       f3 C = mk3(0.f), G = mk3(0.f);
       float cell_exit = -1.f; // macrocell the ray is in: valid while the sample parameter stays below cell_exit
@@ -106,26 +109,41 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             c_shaded++;
             // shadow ray from the sample toward the light (__closesthit__volume_shadow + raymarching_shadow,
             // shaders_raymarching.cu:205-229,44-85), transmittance accumulated as a sum of logs
+            // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
+            // while sample k is classified the fetch of k+1 and the majorant of k+2 are already in flight.
             float slog = 0.f, stx, st1;
             if (clip_shadow(S, p, stx, st1)) {
+              const f3 ph = mk3(__fmaf_rn(p.x, P.cells_per_unit.x, -0.5f), __fmaf_rn(p.y, P.cells_per_unit.y, -0.5f),
+                                __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in cell units - 1/2
+              auto cell_live = [&](float tm) {
+                return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, dcell.x, ph.x), __fmaf_rn(tm, dcell.y, ph.y),
+                                                         __fmaf_rn(tm, dcell.z, ph.z))) != 0.f;
+              };
+              auto fetch = [&](float tm) {
+                return tex3D<float>(P.tex, __fmaf_rn(tm, S.d.x, p.x), __fmaf_rn(tm, S.d.y, p.y), __fmaf_rn(tm, S.d.z, p.z));
+              };
               float sty = fminf(st1, stx + sstep);
+              float tm_c = 0.5f * (stx + sty);
+              bool live_c = !SKIP || cell_live(tm_c);
+              float s_c = 0.f;
+              if (live_c && sty > stx) s_c = fetch(tm_c);
+              float ntx = sty, nty = fminf(ntx + sstep, st1);
+              float tm_n = 0.5f * (ntx + nty);
+              bool live_n = !SKIP || cell_live(tm_n);
               while (sty > stx && slog > log_ert) {
-                const float tm = 0.5f * (stx + sty);
-                const f3 ps = mk3(__fmaf_rn(tm, S.d.x, p.x), __fmaf_rn(tm, S.d.y, p.y), __fmaf_rn(tm, S.d.z, p.z));
-                bool live = true;
-                if (SKIP) {
-                  i3 c;
-                  live = __ldg(P.maj_pad + pad_cell(P, ps, c)) != 0.f;
-                }
-                if (live) {
-                  const float ss = tex3D<float>(P.tex, ps.x, ps.y, ps.z);
+                float s_n = 0.f;
+                if (live_n && nty > ntx) s_n = fetch(tm_n); // prefetch; unused if the ray terminates at this sample
+                const float n2tx = nty, n2ty = fminf(n2tx + sstep, st1);
+                const float tm_n2 = 0.5f * (n2tx + n2ty);
+                const bool live_n2 = !SKIP || cell_live(tm_n2);
+                if (live_c) {
                   c_shadow++;
-                  const float a = alpha_fast(P, tf, ss);
+                  const float a = alpha_fast(P, tf, s_c);
                   // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
                   slog = __fmaf_rn(P.base * (sty - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog);
                 }
-                stx = sty;
-                sty = fminf(stx + sstep, st1);
+                stx = ntx, sty = nty, ntx = n2tx, nty = n2ty;
+                s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
               }
             }
             const f3 normal_o = -normalize3(mk3(gx, gy, gz) / stp);
@@ -177,7 +195,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
               if (!(tm < cell_exit)) {
                 i3 c;
                 cell_empty = __ldg(P.maj_pad + pad_cell(P, p, c)) == 0.f;
-                cell_exit = cell_exit_t(P, c, oo, od_rcp, od);
+                cell_exit = cell_exit_t(P, c, oo, mk3(1.f / od.x, 1.f / od.y, 1.f / od.z), od);
               }
               if (cell_empty) {
                 // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
@@ -258,17 +276,16 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
       g[1] = out_g.y;
       g[2] = out_g.z;
     }
-    n_primary += __reduce_add_sync(0xffffffffu, c_primary);
-    n_shadow += __reduce_add_sync(0xffffffffu, c_shadow);
-    n_gradient += __reduce_add_sync(0xffffffffu, 3u * c_shaded);
-    n_rays += __reduce_add_sync(0xffffffffu, c_rays);
   }
 
-  if (lane == 0) { // one atomic set per warp
-    atomicAdd(&P.counters->primary_samples, n_primary);
-    atomicAdd(&P.counters->shadow_samples, n_shadow);
-    atomicAdd(&P.counters->gradient_fetches, n_gradient);
-    atomicAdd(&P.counters->rays, n_rays);
+  // executed-sample counters: one atomic set per warp
+  const unsigned int n_primary = __reduce_add_sync(0xffffffffu, c_primary), n_shadow = __reduce_add_sync(0xffffffffu, c_shadow);
+  const unsigned int n_shaded = __reduce_add_sync(0xffffffffu, c_shaded), n_rays = __reduce_add_sync(0xffffffffu, c_rays);
+  if (lane == 0) {
+    atomicAdd(&P.counters->primary_samples, (unsigned long long)n_primary);
+    atomicAdd(&P.counters->shadow_samples, (unsigned long long)n_shadow);
+    atomicAdd(&P.counters->gradient_fetches, 3ull * n_shaded);
+    atomicAdd(&P.counters->rays, (unsigned long long)n_rays);
   }
 }
 

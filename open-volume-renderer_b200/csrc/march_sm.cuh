@@ -101,13 +101,23 @@ __device__ __forceinline__ float ex2_fast(float x)
   return r;
 }
 
-// macrocell of an object-space position on the padded grid
+// macrocell of an object-space position on the padded grid (cell c sits at c + 1 on every axis)
 __device__ __forceinline__ int pad_cell(const LaunchParams& P, f3 p, i3& c)
 {
   c.x = min((unsigned)__float2int_rz(p.x * P.cells_per_unit.x), (unsigned)P.mc.x);
   c.y = min((unsigned)__float2int_rz(p.y * P.cells_per_unit.y), (unsigned)P.mc.y);
   c.z = min((unsigned)__float2int_rz(p.z * P.cells_per_unit.z), (unsigned)P.mc.z);
-  return c.x + c.y * P.mcp_sy + c.z * P.mcp_sz;
+  return (c.x + 1) + (c.y + 1) * P.mcp_sy + (c.z + 1) * P.mcp_sz;
+}
+
+// Same index for a position given in CELL units minus one half (x = p * cells_per_unit - 0.5), without any conversion
+// instruction: x + 1.5 * 2^23 rounds x to the nearest integer n (= floor of the cell coordinate) and leaves 0x4B400000 + n
+// in the float's bits; the three magic constants and the +1 pad offsets are folded into P.mcp_bias. n may be -1 .. mc
+// (positions a rounding error outside the box): that is what the pad ring is for; one clamp guards everything else.
+__device__ __forceinline__ unsigned int pad_index_magic(const LaunchParams& P, float xh, float yh, float zh)
+{
+  const unsigned int bx = __float_as_uint(xh + 12582912.f), by = __float_as_uint(yh + 12582912.f), bz = __float_as_uint(zh + 12582912.f);
+  return min(bx + by * (unsigned)P.mcp_sy + bz * (unsigned)P.mcp_sz - P.mcp_bias, P.mcp_last);
 }
 
 constexpr int SM_MIN_BLOCKS = 4; // 128 threads x 4 CTAs/SM wanted at least (register cap 128/thread; ptxas reports the real use)
