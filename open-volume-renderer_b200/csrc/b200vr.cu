@@ -580,7 +580,9 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   }
   if (p.sampler == B200VR_SAMPLER_TEX3D && !legacy) {
     if (p.shading == B200VR_SHADING_REF && !sm) {
-      k.fn = p.skip_empty ? raymarch_q_kernel<true> : raymarch_q_kernel<false>;
+      const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
+      k.fn = p.skip_empty ? (pow2 ? raymarch_q_kernel<true, true> : raymarch_q_kernel<true, false>)
+                          : (pow2 ? raymarch_q_kernel<false, true> : raymarch_q_kernel<false, false>);
       k.threads = Q_THREADS;
       k.smem = q_shared_bytes(h->n_color, h->n_alpha);
       return k;
@@ -668,6 +670,14 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
     P.wtc = transposed(inverse(l));
   }
   P.light_dir = normalize3(mk3(h->prm.light_pos[0], h->prm.light_pos[1], h->prm.light_pos[2]));
+  P.cam_oo = xfm_point(P.wto, P.cam_pos);
+  P.sh_d = xfm_vector(P.wto.l, P.light_dir);
+  P.sh_rcp = mk3(1.f / P.sh_d.x, 1.f / P.sh_d.y, 1.f / P.sh_d.z); // IEEE division = __frcp_rn
+  P.sh_deg_x = std::fabs(P.sh_d.x) < FLT_MIN, P.sh_deg_y = std::fabs(P.sh_d.y) < FLT_MIN, P.sh_deg_z = std::fabs(P.sh_d.z) < FLT_MIN;
+  P.sh_dcell = P.sh_d * P.cells_per_unit;
+  P.sstep = (P.step * 10.f) * P.step;
+  P.log_ert = std::log2(1.f - 0.9999f);
+  P.wto_t = transposed(P.wto.l);
   P.light_ambient = h->prm.light_ambient;
   P.max_num_scatters = h->prm.max_num_scatters;
   P.rgba = h->rgba[h->current];

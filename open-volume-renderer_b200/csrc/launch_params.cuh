@@ -53,6 +53,14 @@ struct LaunchParams {
   f3 light_dir;             // normalize(light_directional_pos), params.h:79
   float light_ambient;
   int max_num_scatters;
+  // ---- kernel-wide constants derived on the host so that they are plain constant-bank operands in the kernels ----
+  f3 cam_oo;                // camera position in object space: xfmPoint(wto, cam_pos)
+  f3 sh_d, sh_rcp;          // shadow-ray direction in object space wto.l * light_dir, and __frcp_rn of it
+  int sh_deg_x, sh_deg_y, sh_deg_z; // |sh_d| < FLT_MIN on that axis (intersect_box, shaders_common.h:163-171)
+  f3 sh_dcell;              // sh_d in macrocell units (sh_d * cells_per_unit)
+  float sstep;              // shadow step (step * 10) * step  (shaders_raymarching.cu:220, A.7-q1)
+  float log_ert;            // log2(1 - 0.9999f): early-ray-termination threshold on log2-transmittance
+  lin3 wto_t;               // transpose(wto.l): xfmNormal(otw, n) = wto_t * n
   // ---- frame ----
   float4* rgba;
   float* grad;              // 3 floats per pixel (vec3f)

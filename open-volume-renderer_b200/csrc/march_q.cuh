@@ -22,31 +22,54 @@ constexpr int Q_MIN_CTAS = B200VR_Q_MIN_CTAS;  // resident CTAs/SM wanted: 3 -> 
 constexpr int Q_SLOTS = 64;                    // per-warp queue capacity: flushed at >= 32, one step adds <= 32
 constexpr int Q_SLOT_FLOATS = 8;               // task: p.xyz, s, w, -, -, -   result: C.xyz, G.xyz, -, -
 
+// dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][task queues, one per warp][colour table (n_color + 1) x float4]
+// (the alpha pairs sit at offset 0 so that the hot lookup is a plain LDS [i * 8 + base])
+__host__ __device__ __forceinline__ size_t q_alpha_bytes(int n_alpha) { return (sizeof(float2) * (size_t)(n_alpha + 1) + 15) & ~(size_t)15; }
+__host__ __device__ __forceinline__ size_t q_queue_bytes() { return sizeof(float) * Q_SLOT_FLOATS * Q_SLOTS * (Q_THREADS / 32); }
 __host__ __device__ __forceinline__ size_t q_shared_bytes(int n_color, int n_alpha)
 {
-  const size_t tf = (tf_fast_shared_bytes(n_color, n_alpha) + 15) & ~(size_t)15;
-  return tf + sizeof(float) * Q_SLOT_FLOATS * Q_SLOTS * (Q_THREADS / 32);
+  return q_alpha_bytes(n_alpha) + q_queue_bytes() + sizeof(float4) * (size_t)(n_color + 1);
 }
 
-template<bool SKIP>
+// alpha lookup of one sample: texture-unit coordinate model (POW2: exact integer fast path for tables of 2^m entries),
+// then value + fraction * slope from the pair table
+template<bool POW2>
+__device__ __forceinline__ float alpha_lookup(const LaunchParams& P, const float2* __restrict__ apair, float s)
+{
+  const float v = tf_unit(P, s);
+  int i, a;
+  if (POW2) {
+    const int q = (__float2int_rz(__fmaf_rn(v, P.tfa_mul, P.tfa_addf)) + P.tfa_addi) >> P.tfa_shift;
+    i = q >> 8;
+    a = q & 255;
+  }
+  else {
+    int i1;
+    hw_coord(nodal_coord(v, P.n_alpha), P.n_alpha, i, i1, a);
+  }
+  const float2 e = apair[i];
+  return __fmaf_rn((float)a, e.y, e.x);
+}
+
+template<bool SKIP, bool POW2>
 __global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 {
   extern __shared__ __align__(16) unsigned char smem[];
-  const TfFast tf = stage_tf_fast(P, smem);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float4* const queue = reinterpret_cast<float4*>(smem + ((tf_fast_shared_bytes(P.n_color, P.n_alpha) + 15) & ~(size_t)15)) +
-                        (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
-  const f3 oo = xfm_point(P.wto, P.cam_pos);
+  float2* const s_apair = reinterpret_cast<float2*>(smem);
+  float4* const queue = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha)) + (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
+  TfFast tf; // colour lookups (once per shaded sample) go through the generic helper
+  tf.apair = s_apair;
+  tf.color = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha) + q_queue_bytes());
+  for (int i = threadIdx.x; i <= P.n_color; i += blockDim.x) const_cast<float4*>(tf.color)[i] = P.tf_color[min(i, P.n_color - 1)];
+  for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
+    const float v0 = P.tf_alpha[min(i, P.n_alpha - 1)], v1 = P.tf_alpha[min(i + 1, P.n_alpha - 1)];
+    s_apair[i] = make_float2(v0, (v1 - v0) * (1.f / 256.f));
+  }
+  __syncthreads();
+  const f3 oo = P.cam_oo;
   const float step = P.step;
-  const float sstep = (P.step * 10.f) * P.step; // q1: sampling_scale * self.step with sampling_scale = step * 10
-  const float log_ert = lg2_fast(1.f - 0.9999f); // A >= 0.9999  <=>  log2(1 - A) <= log2(1 - 0.9999f)
-  ShadowDir S;
-  S.d = xfm_vector(P.wto.l, P.light_dir);
-  S.rcp = mk3(__frcp_rn(S.d.x), __frcp_rn(S.d.y), __frcp_rn(S.d.z));
-  S.sx = fabsf(S.d.x) < FLT_MIN, S.sy = fabsf(S.d.y) < FLT_MIN, S.sz = fabsf(S.d.z) < FLT_MIN;
-  const lin3 wto_t = transposed(P.wto.l); // xfmNormal(otw, n) = transpose(inverse(otw.l)) * n
-  const f3 dcell = S.d * P.cells_per_unit;  // shadow direction in macrocell units
   unsigned int c_primary = 0, c_shadow = 0, c_shaded = 0, c_rays = 0; // per lane, over all tiles of this warp
   const unsigned int lt_mask = (1u << lane) - 1u;
 
@@ -112,42 +135,45 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
             // while sample k is classified the fetch of k+1 and the majorant of k+2 are already in flight.
             float slog = 0.f, stx, st1;
-            if (clip_shadow(S, p, stx, st1)) {
+            if (clip_shadow_p(P, p, stx, st1)) {
+              const float sstep = P.sstep;
               const f3 ph = mk3(__fmaf_rn(p.x, P.cells_per_unit.x, -0.5f), __fmaf_rn(p.y, P.cells_per_unit.y, -0.5f),
-                                __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in cell units - 1/2
+                                __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in macrocell units - 1/2
               auto cell_live = [&](float tm) {
-                return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, dcell.x, ph.x), __fmaf_rn(tm, dcell.y, ph.y),
-                                                         __fmaf_rn(tm, dcell.z, ph.z))) != 0.f;
+                return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, P.sh_dcell.x, ph.x), __fmaf_rn(tm, P.sh_dcell.y, ph.y),
+                                                         __fmaf_rn(tm, P.sh_dcell.z, ph.z))) != 0.f;
               };
               auto fetch = [&](float tm) {
-                return tex3D<float>(P.tex, __fmaf_rn(tm, S.d.x, p.x), __fmaf_rn(tm, S.d.y, p.y), __fmaf_rn(tm, S.d.z, p.z));
+                return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
               };
+              // intervals: current [stx, sty], next [sty, nty], the one after [nty, n2ty]
               float sty = fminf(st1, stx + sstep);
-              float tm_c = 0.5f * (stx + sty);
+              const float tm_c = 0.5f * (stx + sty);
               bool live_c = !SKIP || cell_live(tm_c);
               float s_c = 0.f;
               if (live_c && sty > stx) s_c = fetch(tm_c);
-              float ntx = sty, nty = fminf(ntx + sstep, st1);
-              float tm_n = 0.5f * (ntx + nty);
+              float nty = fminf(sty + sstep, st1);
+              float tm_n = 0.5f * (sty + nty);
               bool live_n = !SKIP || cell_live(tm_n);
-              while (sty > stx && slog > log_ert) {
+#pragma unroll 2
+              while (sty > stx && slog > P.log_ert) {
                 float s_n = 0.f;
-                if (live_n && nty > ntx) s_n = fetch(tm_n); // prefetch; unused if the ray terminates at this sample
-                const float n2tx = nty, n2ty = fminf(n2tx + sstep, st1);
-                const float tm_n2 = 0.5f * (n2tx + n2ty);
+                if (live_n && nty > sty) s_n = fetch(tm_n); // prefetch; unused if the ray ends at this sample
+                const float n2ty = fminf(nty + sstep, st1);
+                const float tm_n2 = 0.5f * (nty + n2ty);
                 const bool live_n2 = !SKIP || cell_live(tm_n2);
                 if (live_c) {
                   c_shadow++;
-                  const float a = alpha_fast(P, tf, s_c);
+                  const float a = alpha_lookup<POW2>(P, s_apair, s_c);
                   // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
                   slog = __fmaf_rn(P.base * (sty - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog);
                 }
-                stx = ntx, sty = nty, ntx = n2tx, nty = n2ty;
+                stx = sty, sty = nty, nty = n2ty;
                 s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
               }
             }
             const f3 normal_o = -normalize3(mk3(gx, gy, gz) / stp);
-            const f3 normal_w = normalize3(xfm_vector(wto_t, normal_o));
+            const f3 normal_w = normalize3(xfm_vector(P.wto_t, normal_o));
             const f3 normal_c = normalize3(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
             const float cosNL = fabsf(dot3(P.light_dir, normal_w));
             const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(slog); // light_rgb = 2; 1 - shadow.alpha = 2^slog
@@ -216,7 +242,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             }
             const float s = tex3D<float>(P.tex, p.x, p.y, p.z);
             c_primary++;
-            float a = alpha_fast(P, tf, s);
+            float a = alpha_lookup<POW2>(P, s_apair, s);
             {
               const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
               if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));

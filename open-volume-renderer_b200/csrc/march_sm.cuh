@@ -79,6 +79,16 @@ __device__ __forceinline__ float alpha_fast(const LaunchParams& P, const TfFast&
   return __fmaf_rn((float)a, e.y, e.x);
 }
 
+// the same lookup through a 32-bit shared-window address (no generic-to-shared conversion in the loop)
+__device__ __forceinline__ float alpha_fast_s(const LaunchParams& P, unsigned int apair_addr, float s)
+{
+  int i, a;
+  tf_coord(tf_unit(P, s), P.n_alpha, P.tfa_mul, P.tfa_addf, P.tfa_addi, P.tfa_shift, i, a);
+  float ex, ey;
+  asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(ex), "=f"(ey) : "r"(apair_addr + 8u * (unsigned int)i));
+  return __fmaf_rn((float)a, ey, ex);
+}
+
 __device__ __forceinline__ f3 color_fast(const LaunchParams& P, const TfFast& tf, float s)
 {
   int i, a;
@@ -134,6 +144,19 @@ __device__ __forceinline__ bool clip_shadow(const ShadowDir& S, f3 o, float& t0,
   const float lx = S.sx ? FLT_MAX : __fmul_rn(0.f - o.x, S.rcp.x), hx = S.sx ? -FLT_MAX : __fmul_rn(1.f - o.x, S.rcp.x);
   const float ly = S.sy ? FLT_MAX : __fmul_rn(0.f - o.y, S.rcp.y), hy = S.sy ? -FLT_MAX : __fmul_rn(1.f - o.y, S.rcp.y);
   const float lz = S.sz ? FLT_MAX : __fmul_rn(0.f - o.z, S.rcp.z), hz = S.sz ? -FLT_MAX : __fmul_rn(1.f - o.z, S.rcp.z);
+  const float nr = fmaxf(fmaxf(fminf(lx, hx), fminf(ly, hy)), fminf(lz, hz));
+  const float fr = fminf(fminf(fmaxf(lx, hx), fmaxf(ly, hy)), fmaxf(lz, hz));
+  t0 = fmaxf(0.f, nr);
+  t1 = fminf(FLT_MAX, fr);
+  return t1 > t0;
+}
+
+// the same test with the host-derived constants of LaunchParams (constant-bank operands)
+__device__ __forceinline__ bool clip_shadow_p(const LaunchParams& P, f3 o, float& t0, float& t1)
+{
+  const float lx = P.sh_deg_x ? FLT_MAX : __fmul_rn(0.f - o.x, P.sh_rcp.x), hx = P.sh_deg_x ? -FLT_MAX : __fmul_rn(1.f - o.x, P.sh_rcp.x);
+  const float ly = P.sh_deg_y ? FLT_MAX : __fmul_rn(0.f - o.y, P.sh_rcp.y), hy = P.sh_deg_y ? -FLT_MAX : __fmul_rn(1.f - o.y, P.sh_rcp.y);
+  const float lz = P.sh_deg_z ? FLT_MAX : __fmul_rn(0.f - o.z, P.sh_rcp.z), hz = P.sh_deg_z ? -FLT_MAX : __fmul_rn(1.f - o.z, P.sh_rcp.z);
   const float nr = fmaxf(fmaxf(fminf(lx, hx), fminf(ly, hy)), fminf(lz, hz));
   const float fr = fminf(fminf(fmaxf(lx, hx), fmaxf(ly, hy)), fmaxf(lz, hz));
   t0 = fmaxf(0.f, nr);
