@@ -169,6 +169,11 @@ __global__ void majorant_pad_kernel(const float* __restrict__ maj, int mx, int m
   }
 }
 
+__global__ void occupancy_kernel(const float* __restrict__ maj, int n, unsigned char* __restrict__ occ)
+{
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) occ[i] = maj[i] != 0.f ? 255 : 0;
+}
+
 // ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------
 // slice layout: [owned super tile m][y in 32][x in 64][rgba]; pixels outside the image are zero in the slice
 template<bool PACK>

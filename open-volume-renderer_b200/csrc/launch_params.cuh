@@ -42,6 +42,8 @@ struct LaunchParams {
   int mcp_sy, mcp_sz;       // cell of any position in [-eps, 1+eps] is addressable without per-axis clamps; strides in floats
   unsigned int mcp_bias;    // folds the float->int magic constant and the +1 pad offset of pad_index_magic()
   unsigned int mcp_last;    // number of padded cells - 1
+  cudaTextureObject_t occ_tex; // macrocell occupancy (majorant != 0) as a point-sampled u8 3-D texture, unnormalised coords
+  f3 occ_scale;             // object-space position -> occupancy texel coordinate (= cells_per_unit)
   i3 mc;
   f3 cells_per_unit;        // dims / 16: object-space position -> macrocell coordinate
   f3 spac_rcp;              // 1 / (16 / dims) computed like sp_singlemc.cu:99-111 (delta tracking DDA)
@@ -79,14 +81,18 @@ struct LaunchParams {
   Counters* counters;
 };
 
-// k-th warp tile owned by (rank, nranks) -> pixel origin
+// k-th warp tile owned by (rank, nranks) -> pixel origin. Inside a super tile the 64 warp tiles are ordered so that 16
+// consecutive ones form a 4 x 4 block of tiles (32 x 16 pixels): a CTA that takes 16 consecutive tiles works on one compact
+// screen region, i.e. on one compact bundle of primary and shadow rays (L1 / texture-cache locality).
+constexpr int TILE_CHUNK = 16;
 __host__ __device__ __forceinline__ void warp_tile_origin(int k, int rank, int nranks, int super_w, int& px, int& py)
 {
   const int m = k / WARP_TILES_PER_SUPER, r = k % WARP_TILES_PER_SUPER;
   const int s = rank + m * nranks;
   const int sx = s % super_w, sy = s / super_w;
-  px = sx * SUPER_TILE_W + (r % (SUPER_TILE_W / WARP_TILE_W)) * WARP_TILE_W;
-  py = sy * SUPER_TILE_H + (r / (SUPER_TILE_W / WARP_TILE_W)) * WARP_TILE_H;
+  const int b = r / TILE_CHUNK, i = r % TILE_CHUNK; // block (2 x 2 per super tile), tile inside the block (4 x 4)
+  px = sx * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W;
+  py = sy * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
 }
 __host__ __device__ __forceinline__ int owned_super_tiles(int rank, int nranks, int n_super)
 {

@@ -14,7 +14,10 @@
 
 namespace b200k {
 
-constexpr int Q_THREADS = 256;                 // 8 warps share one staged transfer function
+#ifndef B200VR_Q_THREADS
+#define B200VR_Q_THREADS 256
+#endif
+constexpr int Q_THREADS = B200VR_Q_THREADS;    // warps of a CTA share one staged alpha table
 #ifndef B200VR_Q_MIN_CTAS
 #define B200VR_Q_MIN_CTAS 3
 #endif
@@ -22,13 +25,20 @@ constexpr int Q_MIN_CTAS = B200VR_Q_MIN_CTAS;  // resident CTAs/SM wanted: 3 -> 
 constexpr int Q_SLOTS = 64;                    // per-warp queue capacity: flushed at >= 32, one step adds <= 32
 constexpr int Q_SLOT_FLOATS = 8;               // task: p.xyz, s, w, -, -, -   result: C.xyz, G.xyz, -, -
 
-// dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][task queues, one per warp][colour table (n_color + 1) x float4]
-// (the alpha pairs sit at offset 0 so that the hot lookup is a plain LDS [i * 8 + base])
+// dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][task queues, one per warp][register stash, word-major per warp]
+// (the alpha pairs sit at offset 0 so that the hot lookup is a plain LDS [i * 8 + base]; the colour table is read once
+// per shaded sample and stays in global memory / L1)
 __host__ __device__ __forceinline__ size_t q_alpha_bytes(int n_alpha) { return (sizeof(float2) * (size_t)(n_alpha + 1) + 15) & ~(size_t)15; }
 __host__ __device__ __forceinline__ size_t q_queue_bytes() { return sizeof(float) * Q_SLOT_FLOATS * Q_SLOTS * (Q_THREADS / 32); }
+#ifndef B200VR_Q_STASH
+#define B200VR_Q_STASH 0
+#endif
+constexpr int Q_STASH_WORDS = B200VR_Q_STASH ? 14 : 0;              // primary-ray registers parked in shared memory during a shading pass
+__host__ __device__ __forceinline__ size_t q_stash_bytes() { return sizeof(float) * Q_STASH_WORDS * Q_THREADS; }
 __host__ __device__ __forceinline__ size_t q_shared_bytes(int n_color, int n_alpha)
 {
-  return q_alpha_bytes(n_alpha) + q_queue_bytes() + sizeof(float4) * (size_t)(n_color + 1);
+  (void)n_color;
+  return q_alpha_bytes(n_alpha) + q_queue_bytes() + q_stash_bytes();
 }
 
 // alpha lookup of one sample: texture-unit coordinate model (POW2: exact integer fast path for tables of 2^m entries),
@@ -51,18 +61,28 @@ __device__ __forceinline__ float alpha_lookup(const LaunchParams& P, const float
   return __fmaf_rn((float)a, e.y, e.x);
 }
 
+// colour lookup of a shaded sample straight from the global table (L1-resident, once per task)
+template<bool POW2>
+__device__ __forceinline__ f3 color_global(const LaunchParams& P, float s)
+{
+  int i, a;
+  tf_coord(tf_unit(P, s), P.n_color, P.tfc_mul, P.tfc_addf, P.tfc_addi, P.tfc_shift, i, a);
+  const float4 c0 = __ldg(P.tf_color + i), c1 = __ldg(P.tf_color + min(i + 1, P.n_color - 1));
+  const float w = (float)a * (1.f / 256.f);
+  return mk3(__fmaf_rn(w, c1.x - c0.x, c0.x), __fmaf_rn(w, c1.y - c0.y, c0.y), __fmaf_rn(w, c1.z - c0.z, c0.z));
+}
+
 template<bool SKIP, bool POW2>
 __global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 {
   extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ unsigned int s_ticket;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_ticket = (unsigned)TILE_CHUNK; // empty chunk: the first warp to arrive refills
   float2* const s_apair = reinterpret_cast<float2*>(smem);
   float4* const queue = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha)) + (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
-  TfFast tf; // colour lookups (once per shaded sample) go through the generic helper
-  tf.apair = s_apair;
-  tf.color = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha) + q_queue_bytes());
-  for (int i = threadIdx.x; i <= P.n_color; i += blockDim.x) const_cast<float4*>(tf.color)[i] = P.tf_color[min(i, P.n_color - 1)];
+  float* const stash = reinterpret_cast<float*>(smem + q_alpha_bytes(P.n_alpha) + q_queue_bytes()) + warp * (Q_STASH_WORDS * 32) + lane;
   for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
     const float v0 = P.tf_alpha[min(i, P.n_alpha - 1)], v1 = P.tf_alpha[min(i + 1, P.n_alpha - 1)];
     s_apair[i] = make_float2(v0, (v1 - v0) * (1.f / 256.f));
@@ -74,8 +94,36 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
   const unsigned int lt_mask = (1u << lane) - 1u;
 
   for (;;) {
+    // tiles are handed out in chunks of TILE_CHUNK consecutive indices per CTA (one compact 32 x 16 pixel block), the warps
+    // of the CTA draw from the chunk through a shared ticket word: (chunk base << 8) | next index, 0xff = refill in progress
     int k = 0;
-    if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
+#ifndef B200VR_Q_CHUNK
+#define B200VR_Q_CHUNK 0
+#endif
+    if (!B200VR_Q_CHUNK) {
+      if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
+    }
+    else if (lane == 0) {
+      for (;;) {
+        const unsigned int w = *(volatile unsigned int*)&s_ticket;
+        const unsigned int idx = w & 0xffu;
+        if (idx < (unsigned)TILE_CHUNK) {
+          if (atomicCAS(&s_ticket, w, w + 1u) == w) {
+            k = (int)((w >> 8) + idx);
+            break;
+          }
+        }
+        else if (idx == (unsigned)TILE_CHUNK) {
+          if (atomicCAS(&s_ticket, w, w | 0xffu) == w) { // this warp refills
+            const unsigned int base = min(atomicAdd(P.tile_counter, (unsigned)TILE_CHUNK), 0x00ffff00u);
+            k = (int)base;
+            __threadfence_block();
+            atomicExch(&s_ticket, (base << 8) | 1u);
+            break;
+          }
+        }
+      }
+    }
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
@@ -83,20 +131,21 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
     const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     const bool inside = ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
-    Tea rng((unsigned)P.frame_index, pixel_index);
-    float out_a = 0.f;
-    f3 out_c = mk3(0.f), out_g = mk3(0.f);
+    // per-pixel sums over the spp loop are kept in the frame itself (same thread reads and writes its own pixel) and the
+    // RNG state is re-derived per sample, so that neither occupies registers during the march
 
     for (int sidx = 0; sidx < P.spp; sidx++) {
       // ---- ray generation + clip (shaders_common.h:400-404, shaders_raymarching.cu:351-362, shaders_common.h:156-184) ----
       float sx = ((float)ix + .5f) * P.rw, sy = ((float)iy + .5f) * P.rh;
       if (P.spp > 1) {
-        const float2 j = rng.draw();
+        Tea rng((unsigned)P.frame_index, pixel_index); // RandomTEA(v0 = frame_index, v1 = pixel_index): draw number sidx + 1
+        float2 j = rng.draw();
+        for (int d = 0; d < sidx; d++) j = rng.draw();
         sx += (j.x - 0.5f) * P.rw;
         sy += (j.y - 0.5f) * P.rh;
       }
       const f3 dir = normalize3(P.cam_dir + (sx - 0.5f) * P.cam_hor + (sy - 0.5f) * P.cam_ver);
-      const f3 od = xfm_vector(P.wto.l, dir);
+      f3 od = xfm_vector(P.wto.l, dir);
       float tx = 0.f, t1 = FLT_MAX;
       bool alive = inside && intersect_box(tx, t1, oo, od, P.clip_lo, P.clip_hi);
       if (inside) c_rays++;
@@ -114,13 +163,20 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
         if (count >= 32 || (!any_alive && count > 0)) {
           // =================== shading pass: lane j takes task j ===================
           const int n = min(count, 32);
+#if B200VR_Q_STASH
+          // park the primary ray in shared memory: the shading pass needs the registers
+          stash[0 * 32] = tx, stash[1 * 32] = ty, stash[2 * 32] = t1, stash[3 * 32] = A;
+          stash[4 * 32] = od.x, stash[5 * 32] = od.y, stash[6 * 32] = od.z, stash[7 * 32] = cell_exit;
+          stash[8 * 32] = C.x, stash[9 * 32] = C.y, stash[10 * 32] = C.z;
+          stash[11 * 32] = G.x, stash[12 * 32] = G.y, stash[13 * 32] = G.z;
+#endif
           __syncwarp();
           f3 cC = mk3(0.f), cG = mk3(0.f);
           if (lane < n) {
             const float4 q0 = queue[2 * lane], q1 = queue[2 * lane + 1];
             const f3 p = mk3(q0.x, q0.y, q0.z);
             const float s = q0.w, w = q1.x;
-            const f3 rgb = color_fast(P, tf, s);
+            const f3 rgb = color_global<POW2>(P, s);
             // compute_volume_gradient_object_space (shaders_common.h:195-215): forward differences, step 1/dims
             f3 stp = P.rdim;
             if (p.x + stp.x > 1.f) stp.x = -stp.x;
@@ -137,9 +193,16 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             float slog = 0.f, stx, st1;
             if (clip_shadow_p(P, p, stx, st1)) {
               const float sstep = P.sstep;
+              const f3 pcell = p * P.occ_scale; // ray origin in macrocell units
               const f3 ph = mk3(__fmaf_rn(p.x, P.cells_per_unit.x, -0.5f), __fmaf_rn(p.y, P.cells_per_unit.y, -0.5f),
                                 __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in macrocell units - 1/2
+#ifndef B200VR_OCC_TEX
+#define B200VR_OCC_TEX 0
+#endif
               auto cell_live = [&](float tm) {
+                if (B200VR_OCC_TEX) // point-sampled occupancy texture: the texture unit does the addressing
+                  return tex3D<unsigned char>(P.occ_tex, __fmaf_rn(tm, P.sh_dcell.x, pcell.x), __fmaf_rn(tm, P.sh_dcell.y, pcell.y),
+                                              __fmaf_rn(tm, P.sh_dcell.z, pcell.z)) != 0;
                 return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, P.sh_dcell.x, ph.x), __fmaf_rn(tm, P.sh_dcell.y, ph.y),
                                                          __fmaf_rn(tm, P.sh_dcell.z, ph.z))) != 0.f;
               };
@@ -147,6 +210,13 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
                 return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
               };
               // intervals: current [stx, sty], next [sty, nty], the one after [nty, n2ty]
+#ifndef B200VR_Q_SHADOW_BATCH
+#define B200VR_Q_SHADOW_BATCH 0
+#endif
+#if B200VR_Q_SHADOW_BATCH == 0
+              // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
+              // while sample k is classified the fetch of k+1 and the macrocell test of k+2 are already in flight.
+              // (Measured alternatives, same frame: batches of 4/8 independent samples 3.09/3.07 ms, this pipeline 2.95 ms.)
               float sty = fminf(st1, stx + sstep);
               const float tm_c = 0.5f * (stx + sty);
               bool live_c = !SKIP || cell_live(tm_c);
@@ -172,6 +242,44 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
                 s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
               }
             }
+#else
+              // Sample positions do not depend on fetched data (fixed t lattice), so the march runs in batches: the
+              // macrocell tests of B consecutive samples are issued together, then their fetches together, and only the
+              // classification + compositing is sequential (it carries the early-termination test).
+              constexpr int B = B200VR_Q_SHADOW_BATCH;
+              float t_lo = stx;
+              bool more = true;
+              while (more) {
+                float e[B], sv[B];
+                bool lv[B];
+#pragma unroll
+                for (int i = 0; i < B; i++) e[i] = fminf((i == 0 ? t_lo : e[i - 1]) + sstep, st1);
+#pragma unroll
+                for (int i = 0; i < B; i++) {
+                  const float lo = i == 0 ? t_lo : e[i - 1];
+                  lv[i] = e[i] > lo && (!SKIP || cell_live(0.5f * (lo + e[i])));
+                }
+#pragma unroll
+                for (int i = 0; i < B; i++) {
+                  const float lo = i == 0 ? t_lo : e[i - 1];
+                  sv[i] = 0.f;
+                  if (lv[i]) sv[i] = fetch(0.5f * (lo + e[i])); // speculative past an early termination inside the batch
+                }
+#pragma unroll
+                for (int i = 0; i < B; i++) {
+                  const float lo = i == 0 ? t_lo : e[i - 1];
+                  if (more && !(e[i] > lo && slog > P.log_ert)) more = false; // the reference's loop condition
+                  if (more && lv[i]) {
+                    c_shadow++;
+                    const float a = alpha_lookup<POW2>(P, s_apair, sv[i]);
+                    // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
+                    slog = __fmaf_rn(P.base * (e[i] - lo), lg2_fast(fmaxf(1.f - a, 0.f)), slog);
+                  }
+                }
+                t_lo = e[B - 1];
+              }
+            }
+#endif
             const f3 normal_o = -normalize3(mk3(gx, gy, gz) / stp);
             const f3 normal_w = normalize3(xfm_vector(P.wto_t, normal_o));
             const f3 normal_c = normalize3(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
@@ -186,6 +294,12 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             queue[2 * lane + 1] = make_float4(cG.y, cG.z, 0.f, 0.f);
           }
           __syncwarp();
+#if B200VR_Q_STASH
+          tx = stash[0 * 32], ty = stash[1 * 32], t1 = stash[2 * 32], A = stash[3 * 32];
+          od.x = stash[4 * 32], od.y = stash[5 * 32], od.z = stash[6 * 32], cell_exit = stash[7 * 32];
+          C = mk3(stash[8 * 32], stash[9 * 32], stash[10 * 32]);
+          G = mk3(stash[11 * 32], stash[12 * 32], stash[13 * 32]);
+#endif
           // every pixel adds its own samples' contributions in march order (= slot order)
           unsigned int own = (unsigned int)(mine & 0xffffffffull);
           if (n < 32) own &= (1u << n) - 1u;
@@ -269,38 +383,41 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
         count += __popc(m);
       }
       // render_raymarching (shaders_raymarching.cu:260-321): background is always 0 -> alpha_blend = C / A
-      out_a += A;
-      if (P.premultiplied) {
-        out_c = out_c + C;
-        out_g = out_g + G;
+      if (!P.premultiplied) { // un-premultiply; A == 0 adds nothing, as alpha_blend does
+        C = A > 0.f ? C / A : mk3(0.f);
+        G = A > 0.f ? G / A : mk3(0.f);
       }
-      else if (A > 0.f) {
-        out_c = out_c + C / A;
-        out_g = out_g + G / A;
-      }
-    }
-    if (inside) {
-      const float rspp = 1.f / (float)P.spp;
-      float4 px4 = make_float4(out_c.x * rspp, out_c.y * rspp, out_c.z * rspp, out_a * rspp);
-      out_g = out_g * rspp;
-      // frame write / progressive accumulation (shaders_raymarching.cu:389-406)
-      if (P.accumulate) {
-        if (P.frame_index == 1) {
-          P.accum[pixel_index] = px4;
+      if (inside) {
+        float4 px4 = make_float4(C.x, C.y, C.z, A);
+        float* g = P.grad + 3 * (size_t)pixel_index;
+        if (sidx > 0) { // running sums over the samples of this pixel
+          const float4 prev = P.rgba[pixel_index];
+          px4 = make_float4(prev.x + px4.x, prev.y + px4.y, prev.z + px4.z, prev.w + px4.w);
+          G = G + mk3(g[0], g[1], g[2]);
         }
-        else {
-          const float4 acc = P.accum[pixel_index];
-          const float4 sum = make_float4(acc.x + px4.x, acc.y + px4.y, acc.z + px4.z, acc.w + px4.w);
-          P.accum[pixel_index] = sum;
-          const float fi = (float)P.frame_index;
-          px4 = make_float4(sum.x / fi, sum.y / fi, sum.z / fi, sum.w / fi);
+        if (sidx == P.spp - 1) {
+          const float rspp = 1.f / (float)P.spp;
+          px4 = make_float4(px4.x * rspp, px4.y * rspp, px4.z * rspp, px4.w * rspp);
+          G = G * rspp;
+          // frame write / progressive accumulation (shaders_raymarching.cu:389-406)
+          if (P.accumulate) {
+            if (P.frame_index == 1) {
+              P.accum[pixel_index] = px4;
+            }
+            else {
+              const float4 acc = P.accum[pixel_index];
+              const float4 sum = make_float4(acc.x + px4.x, acc.y + px4.y, acc.z + px4.z, acc.w + px4.w);
+              P.accum[pixel_index] = sum;
+              const float fi = (float)P.frame_index;
+              px4 = make_float4(sum.x / fi, sum.y / fi, sum.z / fi, sum.w / fi);
+            }
+          }
         }
+        P.rgba[pixel_index] = px4;
+        g[0] = G.x;
+        g[1] = G.y;
+        g[2] = G.z;
       }
-      P.rgba[pixel_index] = px4;
-      float* g = P.grad + 3 * (size_t)pixel_index;
-      g[0] = out_g.x;
-      g[1] = out_g.y;
-      g[2] = out_g.z;
     }
   }
 

@@ -24,8 +24,9 @@ def test_tile_partition_covers_every_pixel_once():
                 for k in range(n_owned * 64):  # warp tiles: same arithmetic as warp_tile_origin (launch_params.cuh)
                     m, r = divmod(k, 64)
                     s = rank + m * nranks
-                    px = (s % sw) * 64 + (r % 8) * 8
-                    py = (s // sw) * 32 + (r // 8) * 4
+                    b, i = divmod(r, 16)  # 2 x 2 blocks of 4 x 4 tiles
+                    px = (s % sw) * 64 + ((b & 1) * 4 + (i & 3)) * 8
+                    py = (s // sw) * 32 + ((b >> 1) * 4 + (i >> 2)) * 4
                     cover[py:py + 4, px:px + 8] += 1
             assert (cover == 1).all()
 
