@@ -142,6 +142,10 @@ int b200vr_render(b200vr_t* h, b200vr_stats* stats);
 int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev);
 int b200vr_swap(b200vr_t* h);
 int b200vr_download(b200vr_t* h, float* rgba_host, float* grad_host_or_null);
+/* same copy enqueued on a caller-owned cudaStream_t without waiting (pinned host memory): lets the application read frame
+ * k while frame k+1 renders into the other buffer after b200vr_swap, the loop of apps/main_app.cpp:244-263
+ * (commit -> mapframe -> to_cpu -> swap -> render). The caller synchronises the stream before touching the host arrays. */
+int b200vr_download_async(b200vr_t* h, float* rgba_host, float* grad_host_or_null, void* cuda_stream);
 
 /* sort-first exchange helpers: pack the tiles owned by (rank, nranks) of the current frame into a dense slice /
  * scatter a slice received from `rank` back into this handle's frame. Slices are device pointers. */

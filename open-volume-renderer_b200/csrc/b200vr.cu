@@ -426,8 +426,7 @@ static int rebuild_majorants(b200vr_t* h)
     cp.kind = cudaMemcpyDeviceToDevice;
     CK(cudaMemcpy3DAsync(&cp, h->stream));
   }
-  CK(cudaStreamSynchronize(h->stream));
-  return B200VR_OK;
+  return B200VR_OK; // stream-ordered: the next render on this stream sees the new majorants
 }
 
 extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, int n_colors, const float* alphas, int n_alphas,
@@ -442,14 +441,17 @@ extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, in
   for (int i = 0; i < n_colors; i++) c[i] = make_float4(colors[3 * i], colors[3 * i + 1], colors[3 * i + 2], 1.f);
   std::vector<float> a((size_t)n_alphas);
   for (int i = 0; i < n_alphas; i++) a[i] = alphas[2 * i + 1];
-  cudaFree(h->tf_color);
-  cudaFree(h->tf_alpha);
-  h->tf_color = nullptr;
-  h->tf_alpha = nullptr;
-  CK(cudaMalloc(&h->tf_color, c.size() * sizeof(float4)));
-  CK(cudaMalloc(&h->tf_alpha, a.size() * sizeof(float)));
-  CK(cudaMemcpy(h->tf_color, c.data(), c.size() * sizeof(float4), cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(h->tf_alpha, a.data(), a.size() * sizeof(float), cudaMemcpyHostToDevice));
+  if (n_colors != h->n_color || n_alphas != h->n_alpha || !h->tf_color) { // same-size edits (the common case) reuse the tables
+    cudaFree(h->tf_color);
+    cudaFree(h->tf_alpha);
+    h->tf_color = nullptr;
+    h->tf_alpha = nullptr;
+    CK(cudaMalloc(&h->tf_color, c.size() * sizeof(float4)));
+    CK(cudaMalloc(&h->tf_alpha, a.size() * sizeof(float)));
+  }
+  // pageable sources: the runtime stages them before returning, the copies themselves run in stream order
+  CK(cudaMemcpyAsync(h->tf_color, c.data(), c.size() * sizeof(float4), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->tf_alpha, a.data(), a.size() * sizeof(float), cudaMemcpyHostToDevice, h->stream));
   h->n_color = n_colors;
   h->n_alpha = n_alphas;
   // set_value_range (volume.cpp:131-145): only a non-empty range replaces the lookup window
@@ -802,6 +804,18 @@ extern "C" int b200vr_swap(b200vr_t* h)
   CK(cudaSetDevice(h->device));
   CK(cudaStreamSynchronize(h->stream));
   h->current ^= 1;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_download_async(b200vr_t* h, float* rgba_host, float* grad_host, void* cuda_stream)
+{
+  if (!h || !rgba_host) return B200VR_EINVAL;
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "download_async: framebuffer size not set");
+  CK(cudaSetDevice(h->device));
+  const size_t n = (size_t)h->width * h->height;
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+  CK(cudaMemcpyAsync(rgba_host, h->rgba[h->current], n * sizeof(float4), cudaMemcpyDeviceToHost, st));
+  if (grad_host) CK(cudaMemcpyAsync(grad_host, h->grad[h->current], n * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
   return B200VR_OK;
 }
 

@@ -1,4 +1,4 @@
-B200VR_NVCC_EXTRA="-DB200VR_Q_CHUNK=1 -DB200VR_Q_SHADOW_BATCH=4" python -c "import ovr_b200; ovr_b200.capi.build(force=True)"
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r1n_plain.log 2>&1 && ncu --section MemoryWorkloadAnalysis --section LaunchStats --section Occupancy --section WarpStateStats --section SpeedOfLight --metrics l1tex__t_sector_hit_rate.pct,lts__t_sectors_srcunit_tex.sum,sm__warps_active.avg.pct_of_peak_sustained_active,l1tex__t_sectors_pipe_tex_mem_texture.sum,l1tex__t_requests_pipe_tex_mem_texture.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__cycles_active.avg,sm__cycles_active.max,sm__cycles_active.min,sm__cycles_elapsed.max --clock-control none -k regex:raymarch -s 3 -c 1 --csv --page raw --log-file gpurun_out/r1n_chunk1.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r1n_ncu.log 2>&1
-B200VR_NVCC_EXTRA="-DB200VR_Q_CHUNK=0 -DB200VR_Q_SHADOW_BATCH=4" python -c "import ovr_b200; ovr_b200.capi.build(force=True)"
-ncu --metrics l1tex__t_sector_hit_rate.pct,lts__t_sectors_srcunit_tex.sum,sm__warps_active.avg.pct_of_peak_sustained_active,l1tex__t_sectors_pipe_tex_mem_texture.sum,l1tex__t_requests_pipe_tex_mem_texture.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__cycles_active.avg,sm__cycles_active.max,sm__cycles_active.min,sm__cycles_elapsed.max,gpu__time_duration.sum --clock-control none -k regex:raymarch -s 3 -c 1 --csv --page raw --log-file gpurun_out/r1n_chunk0.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r1n_ncu0.log 2>&1
+set -x
+mkdir -p gpurun_out
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1q_pre.json 2>&1; echo "pre rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:raymarch_q_kernel -s 3 -c 1 -f -o gpurun_out/r1q_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1q_ncu.log 2>&1; echo "ncu rc=$?"
