@@ -45,9 +45,8 @@ struct b200vr {
   float2* ranges = nullptr;
   float* majorants = nullptr;
   float* maj_pad = nullptr;
-  unsigned char* occ_lin = nullptr;
-  cudaArray_t occ_array = nullptr;
-  cudaTextureObject_t occ_tex = 0;
+  unsigned int* occ_bits = nullptr;
+  int occ_words = 0;
   int* minmax = nullptr;
   // transfer function
   float4* tf_color = nullptr;
@@ -167,12 +166,8 @@ static void free_volume(b200vr_t* h)
   cudaFree(h->majorants);
   cudaFree(h->maj_pad);
   h->maj_pad = nullptr;
-  if (h->occ_tex) cudaDestroyTextureObject(h->occ_tex);
-  if (h->occ_array) cudaFreeArray(h->occ_array);
-  cudaFree(h->occ_lin);
-  h->occ_tex = 0;
-  h->occ_array = nullptr;
-  h->occ_lin = nullptr;
+  cudaFree(h->occ_bits);
+  h->occ_bits = nullptr;
   h->tex = 0;
   h->array = nullptr;
   h->lin = nullptr;
@@ -255,23 +250,9 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12])
   const size_t n_pad = (size_t)(h->mc.x + 2) * (h->mc.y + 2) * (h->mc.z + 2);
   CK(cudaMalloc(&h->maj_pad, n_pad * sizeof(float)));
   CK(cudaMemsetAsync(h->maj_pad, 0, n_pad * sizeof(float), h->stream));
-  {
-    // occupancy texture: one byte per macrocell, point filter, clamp, unnormalised coordinates
-    CK(cudaMalloc(&h->occ_lin, n_cells));
-    const cudaChannelFormatDesc od = cudaCreateChannelDesc<unsigned char>();
-    CK(cudaMalloc3DArray(&h->occ_array, &od, make_cudaExtent((size_t)h->mc.x, (size_t)h->mc.y, (size_t)h->mc.z)));
-    cudaResourceDesc ord;
-    std::memset(&ord, 0, sizeof(ord));
-    ord.resType = cudaResourceTypeArray;
-    ord.res.array.array = h->occ_array;
-    cudaTextureDesc otd;
-    std::memset(&otd, 0, sizeof(otd));
-    otd.addressMode[0] = otd.addressMode[1] = otd.addressMode[2] = cudaAddressModeClamp;
-    otd.filterMode = cudaFilterModePoint;
-    otd.readMode = cudaReadModeElementType;
-    otd.normalizedCoords = 0;
-    CK(cudaCreateTextureObject(&h->occ_tex, &ord, &otd, nullptr));
-  }
+  h->occ_words = (int)((n_pad + 31) / 32);
+  CK(cudaMalloc(&h->occ_bits, (size_t)h->occ_words * sizeof(unsigned int)));
+  CK(cudaMemsetAsync(h->occ_bits, 0, (size_t)h->occ_words * sizeof(unsigned int), h->stream));
   const int init[2] = { 0x7fffffff, (int)0x80000000 };
   CK(cudaMemcpyAsync(h->minmax, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
   macrocell_range_kernel<<<(unsigned)n_cells, RANGE_THREADS, 0, h->stream>>>(h->lin, h->nx, h->ny, h->nz, h->mc.x, h->mc.y,
@@ -415,17 +396,9 @@ static int rebuild_majorants(b200vr_t* h)
   majorant_pad_kernel<<<std::max(1, std::min((n_pad + threads - 1) / threads, h->sm_count * 8)), threads, 0, h->stream>>>(
     h->majorants, h->mc.x, h->mc.y, h->mc.z, h->maj_pad);
   CK(cudaGetLastError());
-  occupancy_kernel<<<grid, threads, 0, h->stream>>>(h->majorants, n_cells, h->occ_lin);
+  occupancy_bits_kernel<<<std::max(1, (h->occ_words + threads - 1) / threads), threads, 0, h->stream>>>(h->maj_pad, n_pad, h->occ_bits,
+                                                                                                            h->occ_words);
   CK(cudaGetLastError());
-  {
-    cudaMemcpy3DParms cp;
-    std::memset(&cp, 0, sizeof(cp));
-    cp.srcPtr = make_cudaPitchedPtr(h->occ_lin, (size_t)h->mc.x, (size_t)h->mc.x, (size_t)h->mc.y);
-    cp.dstArray = h->occ_array;
-    cp.extent = make_cudaExtent((size_t)h->mc.x, (size_t)h->mc.y, (size_t)h->mc.z);
-    cp.kind = cudaMemcpyDeviceToDevice;
-    CK(cudaMemcpy3DAsync(&cp, h->stream));
-  }
   return B200VR_OK; // stream-ordered: the next render on this stream sees the new majorants
 }
 
@@ -620,10 +593,12 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   if (p.sampler == B200VR_SAMPLER_TEX3D && !legacy) {
     if (p.shading == B200VR_SHADING_REF && !sm) {
       const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
-      k.fn = p.skip_empty ? (pow2 ? raymarch_q_kernel<true, true> : raymarch_q_kernel<true, false>)
-                          : (pow2 ? raymarch_q_kernel<false, true> : raymarch_q_kernel<false, false>);
+      const bool occs = p.skip_empty && q_occ_in_smem(h->occ_words);
+      if (!p.skip_empty) k.fn = pow2 ? raymarch_q_kernel<false, true, false> : raymarch_q_kernel<false, false, false>;
+      else if (occs) k.fn = pow2 ? raymarch_q_kernel<true, true, true> : raymarch_q_kernel<true, false, true>;
+      else k.fn = pow2 ? raymarch_q_kernel<true, true, false> : raymarch_q_kernel<true, false, false>;
       k.threads = Q_THREADS;
-      k.smem = q_shared_bytes(h->n_color, h->n_alpha);
+      k.smem = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0) + q_queue_bytes();
       return k;
     }
     k.smem = tf_fast_shared_bytes(h->n_color, h->n_alpha);
@@ -665,8 +640,8 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.tf_scale = 1.f / (h->tf_upper - h->tf_lower); // volume.scale (volume.cpp:145)
   P.majorants = h->majorants;
   P.maj_pad = h->maj_pad;
-  P.occ_tex = h->occ_tex;
-  P.occ_scale = mk3((float)h->nx, (float)h->ny, (float)h->nz) / (float)MC_SIZE;
+  P.occ_bits = h->occ_bits;
+  P.occ_words = h->occ_words;
   P.mcp_sy = h->mc.x + 2;
   P.mcp_sz = (h->mc.x + 2) * (h->mc.y + 2);
   P.mcp_bias = (0x4B400000u - 1u) * (1u + (unsigned)P.mcp_sy + (unsigned)P.mcp_sz); // see pad_index_magic()

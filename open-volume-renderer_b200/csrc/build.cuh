@@ -169,9 +169,17 @@ __global__ void majorant_pad_kernel(const float* __restrict__ maj, int mx, int m
   }
 }
 
-__global__ void occupancy_kernel(const float* __restrict__ maj, int n, unsigned char* __restrict__ occ)
+// occupancy mask of the padded grid: bit i of word w = (majorant of padded cell 32 w + i != 0)
+__global__ void occupancy_bits_kernel(const float* __restrict__ maj_pad, int n_pad, unsigned int* __restrict__ bits, int n_words)
 {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) occ[i] = maj[i] != 0.f ? 255 : 0;
+  for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += gridDim.x * blockDim.x) {
+    unsigned int v = 0u;
+    for (int b = 0; b < 32; b++) {
+      const int i = w * 32 + b;
+      if (i < n_pad && maj_pad[i] != 0.f) v |= 1u << b;
+    }
+    bits[w] = v;
+  }
 }
 
 // ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------

@@ -42,8 +42,8 @@ struct LaunchParams {
   int mcp_sy, mcp_sz;       // cell of any position in [-eps, 1+eps] is addressable without per-axis clamps; strides in floats
   unsigned int mcp_bias;    // folds the float->int magic constant and the +1 pad offset of pad_index_magic()
   unsigned int mcp_last;    // number of padded cells - 1
-  cudaTextureObject_t occ_tex; // macrocell occupancy (majorant != 0) as a point-sampled u8 3-D texture, unnormalised coords
-  f3 occ_scale;             // object-space position -> occupancy texel coordinate (= cells_per_unit)
+  const unsigned int* occ_bits; // one bit per padded macrocell: majorant != 0 (build.cuh occupancy_bits_kernel)
+  int occ_words;            // words in occ_bits
   i3 mc;
   f3 cells_per_unit;        // dims / 16: object-space position -> macrocell coordinate
   f3 spac_rcp;              // 1 / (16 / dims) computed like sp_singlemc.cu:99-111 (delta tracking DDA)

@@ -25,26 +25,60 @@ constexpr int Q_MIN_CTAS = B200VR_Q_MIN_CTAS;  // resident CTAs/SM wanted: 3 -> 
 constexpr int Q_SLOTS = 64;                    // per-warp queue capacity: flushed at >= 32, one step adds <= 32
 constexpr int Q_SLOT_FLOATS = 8;               // task: p.xyz, s, w, -, -, -   result: C.xyz, G.xyz, -, -
 
-// dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][task queues, one per warp][register stash, word-major per warp]
+// dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][macrocell occupancy bits][task queues, one per warp]
 // (the alpha pairs sit at offset 0 so that the hot lookup is a plain LDS [i * 8 + base]; the colour table is read once
 // per shaded sample and stays in global memory / L1)
+constexpr int Q_OCC_SMEM_WORDS = 3072; // occupancy bit masks up to 12 KB (padded grids up to 46^3 cells) are staged per CTA
 __host__ __device__ __forceinline__ size_t q_alpha_bytes(int n_alpha) { return (sizeof(float2) * (size_t)(n_alpha + 1) + 15) & ~(size_t)15; }
+__host__ __device__ __forceinline__ size_t q_occ_bytes(int occ_words) { return (sizeof(unsigned int) * (size_t)occ_words + 15) & ~(size_t)15; }
 __host__ __device__ __forceinline__ size_t q_queue_bytes() { return sizeof(float) * Q_SLOT_FLOATS * Q_SLOTS * (Q_THREADS / 32); }
-#ifndef B200VR_Q_STASH
-#define B200VR_Q_STASH 0
-#endif
-constexpr int Q_STASH_WORDS = B200VR_Q_STASH ? 14 : 0;              // primary-ray registers parked in shared memory during a shading pass
-__host__ __device__ __forceinline__ size_t q_stash_bytes() { return sizeof(float) * Q_STASH_WORDS * Q_THREADS; }
-__host__ __device__ __forceinline__ size_t q_shared_bytes(int n_color, int n_alpha)
+__host__ __device__ __forceinline__ bool q_occ_in_smem(int occ_words) { return occ_words <= Q_OCC_SMEM_WORDS; }
+__host__ __device__ __forceinline__ size_t q_shared_bytes(int n_alpha, int occ_words)
 {
-  (void)n_color;
-  return q_alpha_bytes(n_alpha) + q_queue_bytes() + q_stash_bytes();
+  return q_alpha_bytes(n_alpha) + (q_occ_in_smem(occ_words) ? q_occ_bytes(occ_words) : 0) + q_queue_bytes();
+}
+
+// One bit per padded macrocell: majorant != 0. A shadow ray tests the cell of EVERY sample (its step is about one cell),
+// so the test has to be cheap and must not queue behind the texture fetches in L1TEX: the mask of a 512^3 volume is
+// 4.9 KB and lives in shared memory; larger masks are read through the read-only path.
+// Loads from the staged tables go through 32-bit shared-space addresses (ld.shared), not through generic pointers derived
+// from the extern array: nvcc rebuilt the shared-window base (S2UR CgaCtaId + ULEA) at every such use inside the loops.
+__device__ __forceinline__ unsigned int lds_u32(unsigned int addr)
+{
+  unsigned int v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float2 lds_f32x2(unsigned int addr)
+{
+  float2 v;
+  asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+
+template<bool OCCS>
+__device__ __forceinline__ bool occ_bit(const LaunchParams& P, unsigned int occ_base, unsigned int idx)
+{
+  const unsigned int w = OCCS ? lds_u32(occ_base + ((idx >> 5) << 2)) : __ldg(P.occ_bits + (idx >> 5));
+  return ((w >> (idx & 31u)) & 1u) != 0u;
+}
+
+// padded-grid index of the macrocell holding position q (object space, [0,1]^3 up to rounding): the FMA rounds toward
+// -inf at 1.5 * 2^23, which leaves 0x4B400000 + floor(q * cells_per_unit) in the float's bits (floor = -1 .. mc are all
+// addressable thanks to the pad ring; the one clamp guards against garbage positions). Cells carry a two-voxel apron
+// (build.cuh MC_APRON), so a position that rounds into the neighbouring cell at a boundary is still classified safely.
+__device__ __forceinline__ unsigned int pad_index_floor(const LaunchParams& P, f3 q)
+{
+  const unsigned int bx = __float_as_uint(__fmaf_rd(q.x, P.cells_per_unit.x, 12582912.f));
+  const unsigned int by = __float_as_uint(__fmaf_rd(q.y, P.cells_per_unit.y, 12582912.f));
+  const unsigned int bz = __float_as_uint(__fmaf_rd(q.z, P.cells_per_unit.z, 12582912.f));
+  return min(bx + by * (unsigned)P.mcp_sy + bz * (unsigned)P.mcp_sz - P.mcp_bias, P.mcp_last);
 }
 
 // alpha lookup of one sample: texture-unit coordinate model (POW2: exact integer fast path for tables of 2^m entries),
 // then value + fraction * slope from the pair table
 template<bool POW2>
-__device__ __forceinline__ float alpha_lookup(const LaunchParams& P, const float2* __restrict__ apair, float s)
+__device__ __forceinline__ float alpha_lookup(const LaunchParams& P, unsigned int apair_base, float s)
 {
   const float v = tf_unit(P, s);
   int i, a;
@@ -57,7 +91,7 @@ __device__ __forceinline__ float alpha_lookup(const LaunchParams& P, const float
     int i1;
     hw_coord(nodal_coord(v, P.n_alpha), P.n_alpha, i, i1, a);
   }
-  const float2 e = apair[i];
+  const float2 e = lds_f32x2(apair_base + ((unsigned)i << 3));
   return __fmaf_rn((float)a, e.y, e.x);
 }
 
@@ -72,17 +106,20 @@ __device__ __forceinline__ f3 color_global(const LaunchParams& P, float s)
   return mk3(__fmaf_rn(w, c1.x - c0.x, c0.x), __fmaf_rn(w, c1.y - c0.y, c0.y), __fmaf_rn(w, c1.z - c0.z, c0.z));
 }
 
-template<bool SKIP, bool POW2>
+template<bool SKIP, bool POW2, bool OCCS>
 __global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 {
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ unsigned int s_ticket;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_ticket = (unsigned)TILE_CHUNK; // empty chunk: the first warp to arrive refills
   float2* const s_apair = reinterpret_cast<float2*>(smem);
-  float4* const queue = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha)) + (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
-  float* const stash = reinterpret_cast<float*>(smem + q_alpha_bytes(P.n_alpha) + q_queue_bytes()) + warp * (Q_STASH_WORDS * 32) + lane;
+  unsigned int* const s_occ = reinterpret_cast<unsigned int*>(smem + q_alpha_bytes(P.n_alpha));
+  const unsigned int apair_base = (unsigned int)__cvta_generic_to_shared(smem);
+  const unsigned int occ_base = apair_base + (unsigned int)q_alpha_bytes(P.n_alpha);
+  float4* const queue = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha) + (OCCS ? q_occ_bytes(P.occ_words) : 0)) +
+                        (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
+  if (SKIP && OCCS)
+    for (int i = threadIdx.x; i < P.occ_words; i += blockDim.x) s_occ[i] = P.occ_bits[i];
   for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
     const float v0 = P.tf_alpha[min(i, P.n_alpha - 1)], v1 = P.tf_alpha[min(i + 1, P.n_alpha - 1)];
     s_apair[i] = make_float2(v0, (v1 - v0) * (1.f / 256.f));
@@ -94,36 +131,9 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
   const unsigned int lt_mask = (1u << lane) - 1u;
 
   for (;;) {
-    // tiles are handed out in chunks of TILE_CHUNK consecutive indices per CTA (one compact 32 x 16 pixel block), the warps
-    // of the CTA draw from the chunk through a shared ticket word: (chunk base << 8) | next index, 0xff = refill in progress
+    // one 8x4 warp tile per atomic ticket (CTA-wide chunks of 16 tiles measured slower: tail imbalance)
     int k = 0;
-#ifndef B200VR_Q_CHUNK
-#define B200VR_Q_CHUNK 0
-#endif
-    if (!B200VR_Q_CHUNK) {
-      if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
-    }
-    else if (lane == 0) {
-      for (;;) {
-        const unsigned int w = *(volatile unsigned int*)&s_ticket;
-        const unsigned int idx = w & 0xffu;
-        if (idx < (unsigned)TILE_CHUNK) {
-          if (atomicCAS(&s_ticket, w, w + 1u) == w) {
-            k = (int)((w >> 8) + idx);
-            break;
-          }
-        }
-        else if (idx == (unsigned)TILE_CHUNK) {
-          if (atomicCAS(&s_ticket, w, w | 0xffu) == w) { // this warp refills
-            const unsigned int base = min(atomicAdd(P.tile_counter, (unsigned)TILE_CHUNK), 0x00ffff00u);
-            k = (int)base;
-            __threadfence_block();
-            atomicExch(&s_ticket, (base << 8) | 1u);
-            break;
-          }
-        }
-      }
-    }
+    if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
@@ -163,13 +173,6 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
         if (count >= 32 || (!any_alive && count > 0)) {
           // =================== shading pass: lane j takes task j ===================
           const int n = min(count, 32);
-#if B200VR_Q_STASH
-          // park the primary ray in shared memory: the shading pass needs the registers
-          stash[0 * 32] = tx, stash[1 * 32] = ty, stash[2 * 32] = t1, stash[3 * 32] = A;
-          stash[4 * 32] = od.x, stash[5 * 32] = od.y, stash[6 * 32] = od.z, stash[7 * 32] = cell_exit;
-          stash[8 * 32] = C.x, stash[9 * 32] = C.y, stash[10 * 32] = C.z;
-          stash[11 * 32] = G.x, stash[12 * 32] = G.y, stash[13 * 32] = G.z;
-#endif
           __syncwarp();
           f3 cC = mk3(0.f), cG = mk3(0.f);
           if (lane < n) {
@@ -193,30 +196,38 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             float slog = 0.f, stx, st1;
             if (clip_shadow_p(P, p, stx, st1)) {
               const float sstep = P.sstep;
-              const f3 pcell = p * P.occ_scale; // ray origin in macrocell units
+              // All lanes walk the fixed t lattice in lockstep (neighbouring shadow rays then fetch neighbouring texels: letting
+              // each lane run ahead to its next live sample measured 3.60 ms against 2.95 ms); a sample in an empty macrocell
+              // (alpha == 0 exactly, adds 0 to the log sum) costs the cell test only.
+#ifndef B200VR_Q_OCC_BITS
+#define B200VR_Q_OCC_BITS 1
+#endif
+#ifndef B200VR_Q_DEPTH
+#define B200VR_Q_DEPTH 1
+#endif
               const f3 ph = mk3(__fmaf_rn(p.x, P.cells_per_unit.x, -0.5f), __fmaf_rn(p.y, P.cells_per_unit.y, -0.5f),
                                 __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in macrocell units - 1/2
-#ifndef B200VR_OCC_TEX
-#define B200VR_OCC_TEX 0
-#endif
               auto cell_live = [&](float tm) {
-                if (B200VR_OCC_TEX) // point-sampled occupancy texture: the texture unit does the addressing
-                  return tex3D<unsigned char>(P.occ_tex, __fmaf_rn(tm, P.sh_dcell.x, pcell.x), __fmaf_rn(tm, P.sh_dcell.y, pcell.y),
-                                              __fmaf_rn(tm, P.sh_dcell.z, pcell.z)) != 0;
+                if (B200VR_Q_OCC_BITS)
+                  return occ_bit<OCCS>(P, occ_base, pad_index_floor(P, mk3(__fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y),
+                                                                           __fmaf_rn(tm, P.sh_d.z, p.z))));
                 return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, P.sh_dcell.x, ph.x), __fmaf_rn(tm, P.sh_dcell.y, ph.y),
                                                          __fmaf_rn(tm, P.sh_dcell.z, ph.z))) != 0.f;
               };
               auto fetch = [&](float tm) {
                 return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
               };
+              auto classify = [&](float sv, float dt) {
+                c_shadow++;
+                const float a = alpha_lookup<POW2>(P, apair_base, sv);
+                // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
+                slog = __fmaf_rn(P.base * dt, lg2_fast(fmaxf(1.f - a, 0.f)), slog);
+              };
+#if B200VR_Q_DEPTH == 1
+              // Software pipeline: sample positions do not depend on fetched data (fixed t lattice), so while sample k is
+              // classified the fetch of k+1 and the macrocell test of k+2 are already in flight.
               // intervals: current [stx, sty], next [sty, nty], the one after [nty, n2ty]
-#ifndef B200VR_Q_SHADOW_BATCH
-#define B200VR_Q_SHADOW_BATCH 0
-#endif
-#if B200VR_Q_SHADOW_BATCH == 0
-              // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
-              // while sample k is classified the fetch of k+1 and the macrocell test of k+2 are already in flight.
-              // (Measured alternatives, same frame: batches of 4/8 independent samples 3.09/3.07 ms, this pipeline 2.95 ms.)
+              // (Measured alternatives on C2: batches of 4/8 independent samples per ray 3.09/3.07 ms, this pipeline 2.95 ms.)
               float sty = fminf(st1, stx + sstep);
               const float tm_c = 0.5f * (stx + sty);
               bool live_c = !SKIP || cell_live(tm_c);
@@ -232,54 +243,32 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
                 const float n2ty = fminf(nty + sstep, st1);
                 const float tm_n2 = 0.5f * (nty + n2ty);
                 const bool live_n2 = !SKIP || cell_live(tm_n2);
-                if (live_c) {
-                  c_shadow++;
-                  const float a = alpha_lookup<POW2>(P, s_apair, s_c);
-                  // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
-                  slog = __fmaf_rn(P.base * (sty - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog);
-                }
+                if (live_c) classify(s_c, sty - stx);
                 stx = sty, sty = nty, nty = n2ty;
                 s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
               }
-            }
 #else
-              // Sample positions do not depend on fetched data (fixed t lattice), so the march runs in batches: the
-              // macrocell tests of B consecutive samples are issued together, then their fetches together, and only the
-              // classification + compositing is sequential (it carries the early-termination test).
-              constexpr int B = B200VR_Q_SHADOW_BATCH;
-              float t_lo = stx;
-              bool more = true;
-              while (more) {
-                float e[B], sv[B];
-                bool lv[B];
-#pragma unroll
-                for (int i = 0; i < B; i++) e[i] = fminf((i == 0 ? t_lo : e[i - 1]) + sstep, st1);
-#pragma unroll
-                for (int i = 0; i < B; i++) {
-                  const float lo = i == 0 ? t_lo : e[i - 1];
-                  lv[i] = e[i] > lo && (!SKIP || cell_live(0.5f * (lo + e[i])));
-                }
-#pragma unroll
-                for (int i = 0; i < B; i++) {
-                  const float lo = i == 0 ? t_lo : e[i - 1];
-                  sv[i] = 0.f;
-                  if (lv[i]) sv[i] = fetch(0.5f * (lo + e[i])); // speculative past an early termination inside the batch
-                }
-#pragma unroll
-                for (int i = 0; i < B; i++) {
-                  const float lo = i == 0 ? t_lo : e[i - 1];
-                  if (more && !(e[i] > lo && slog > P.log_ert)) more = false; // the reference's loop condition
-                  if (more && lv[i]) {
-                    c_shadow++;
-                    const float a = alpha_lookup<POW2>(P, s_apair, sv[i]);
-                    // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
-                    slog = __fmaf_rn(P.base * (e[i] - lo), lg2_fast(fmaxf(1.f - a, 0.f)), slog);
-                  }
-                }
-                t_lo = e[B - 1];
+              // two fetches in flight per ray: while sample k is classified, k+1 and k+2 are being fetched and the cell test
+              // of k+3 is issued. intervals: [t0, t1_], [t1_, t2], [t2, t3], [t3, t4]
+              float t0 = stx, t1_ = fminf(st1, t0 + sstep), t2 = fminf(st1, t1_ + sstep), t3 = fminf(st1, t2 + sstep);
+              bool live_c = !SKIP || cell_live(0.5f * (t0 + t1_));
+              bool live_n = !SKIP || cell_live(0.5f * (t1_ + t2));
+              bool live_n2 = !SKIP || cell_live(0.5f * (t2 + t3));
+              float s_c = 0.f, s_n = 0.f;
+              if (live_c && t1_ > t0) s_c = fetch(0.5f * (t0 + t1_));
+              if (live_n && t2 > t1_) s_n = fetch(0.5f * (t1_ + t2));
+#pragma unroll 2
+              while (t1_ > t0 && slog > P.log_ert) {
+                float s_n2 = 0.f;
+                if (live_n2 && t3 > t2) s_n2 = fetch(0.5f * (t2 + t3));
+                const float t4 = fminf(st1, t3 + sstep);
+                const bool live_n3 = !SKIP || cell_live(0.5f * (t3 + t4));
+                if (live_c) classify(s_c, t1_ - t0);
+                t0 = t1_, t1_ = t2, t2 = t3, t3 = t4;
+                s_c = s_n, s_n = s_n2, live_c = live_n, live_n = live_n2, live_n2 = live_n3;
               }
-            }
 #endif
+            }
             const f3 normal_o = -normalize3(mk3(gx, gy, gz) / stp);
             const f3 normal_w = normalize3(xfm_vector(P.wto_t, normal_o));
             const f3 normal_c = normalize3(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
@@ -294,12 +283,6 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             queue[2 * lane + 1] = make_float4(cG.y, cG.z, 0.f, 0.f);
           }
           __syncwarp();
-#if B200VR_Q_STASH
-          tx = stash[0 * 32], ty = stash[1 * 32], t1 = stash[2 * 32], A = stash[3 * 32];
-          od.x = stash[4 * 32], od.y = stash[5 * 32], od.z = stash[6 * 32], cell_exit = stash[7 * 32];
-          C = mk3(stash[8 * 32], stash[9 * 32], stash[10 * 32]);
-          G = mk3(stash[11 * 32], stash[12 * 32], stash[13 * 32]);
-#endif
           // every pixel adds its own samples' contributions in march order (= slot order)
           unsigned int own = (unsigned int)(mine & 0xffffffffull);
           if (n < 32) own &= (1u << n) - 1u;
@@ -334,7 +317,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             if (SKIP) {
               if (!(tm < cell_exit)) {
                 i3 c;
-                cell_empty = __ldg(P.maj_pad + pad_cell(P, p, c)) == 0.f;
+                cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
                 cell_exit = cell_exit_t(P, c, oo, mk3(1.f / od.x, 1.f / od.y, 1.f / od.z), od);
               }
               if (cell_empty) {
@@ -356,7 +339,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             }
             const float s = tex3D<float>(P.tex, p.x, p.y, p.z);
             c_primary++;
-            float a = alpha_lookup<POW2>(P, s_apair, s);
+            float a = alpha_lookup<POW2>(P, apair_base, s);
             {
               const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
               if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));

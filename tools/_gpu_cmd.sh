@@ -1,4 +1,17 @@
-set -x
 mkdir -p gpurun_out
-python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1q_pre.json 2>&1; echo "pre rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:raymarch_q_kernel -s 3 -c 1 -f -o gpurun_out/r1q_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1q_ncu.log 2>&1; echo "ncu rc=$?"
+run() {
+  B200VR_NVCC_EXTRA="$1" python -c "
+import sys, importlib
+sys.path.insert(0,'.')
+m=importlib.import_module('open-volume-renderer_b200._capi'); m.build(force=True)" > /dev/null 2>&1 || echo "build failed $1"
+  python bench.py --steps 15 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import sys, json
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', 'ms', round(d['ms_per_step'],3), 'kernel', round(d['roofline']['kernel_ms_per_launch'],3), 'e2e', round(d['e2e']['ms_per_step'],3), 'frac', round(d['roofline']['frac'],3))"
+}
+run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=1"
+run "-DB200VR_Q_OCC_BITS=0 -DB200VR_Q_DEPTH=1"
+run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=2"
+run "-DB200VR_Q_OCC_BITS=0 -DB200VR_Q_DEPTH=2"
+run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=2 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
+run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=1 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
