@@ -56,6 +56,20 @@ __device__ __forceinline__ float2 lds_f32x2(unsigned int addr)
   return v;
 }
 
+__device__ __forceinline__ float rcp_fast(float x)
+{
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ f3 normalize3_fast(f3 v)
+{
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(dot3(v, v)));
+  return v * r;
+}
+
 template<bool OCCS>
 __device__ __forceinline__ bool occ_bit(const LaunchParams& P, unsigned int occ_base, unsigned int idx)
 {
@@ -165,6 +179,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
       f3 C = mk3(0.f), G = mk3(0.f);
       float cell_exit = -1.f; // macrocell the ray is in: valid while the sample parameter stays below cell_exit
       bool cell_empty = false;
+      float s_pre = 0.f;     // prefetched value of the sample at (tx, ty), valid while have_pre
+      bool have_pre = false;
       unsigned long long mine = 0ull; // queue slots holding this pixel's tasks
       int count = 0;                  // tasks waiting (warp-uniform)
 
@@ -269,9 +285,11 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
               }
 #endif
             }
-            const f3 normal_o = -normalize3(mk3(gx, gy, gz) / stp);
-            const f3 normal_w = normalize3(xfm_vector(P.wto_t, normal_o));
-            const f3 normal_c = normalize3(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
+            // shading normals: v * rsqrt.approx(|v|^2) (2 ulp) instead of the reference's v / sqrt(|v|^2) -- three IEEE
+            // square roots and nine divisions per shaded sample otherwise; the zero-gradient case gives NaN -> clamp -> 0 in both
+            const f3 normal_o = -normalize3_fast(mk3(gx * rcp_fast(stp.x), gy * rcp_fast(stp.y), gz * rcp_fast(stp.z)));
+            const f3 normal_w = normalize3_fast(xfm_vector(P.wto_t, normal_o));
+            const f3 normal_c = normalize3_fast(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
             const float cosNL = fabsf(dot3(P.light_dir, normal_w));
             const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(slog); // light_rgb = 2; 1 - shadow.alpha = 2^slog
             cC = clamp01(rgb * k_sh) * w; // shaders_raymarching.cu:156-165
@@ -318,7 +336,9 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
               if (!(tm < cell_exit)) {
                 i3 c;
                 cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
-                cell_exit = cell_exit_t(P, c, oo, mk3(1.f / od.x, 1.f / od.y, 1.f / od.z), od);
+                // approximate reciprocals: cell_exit only decides which samples are skipped with their (empty) cell, and a
+                // sample a rounding error past the boundary still has its footprint inside the cell's two-voxel apron
+                cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od);
               }
               if (cell_empty) {
                 // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
@@ -337,7 +357,19 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
                 break;
               }
             }
-            const float s = tex3D<float>(P.tex, p.x, p.y, p.z);
+#ifndef B200VR_Q_PRIMARY_PREFETCH
+#define B200VR_Q_PRIMARY_PREFETCH 1
+#endif
+            float s;
+            if (B200VR_Q_PRIMARY_PREFETCH && have_pre) s = s_pre;
+            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+            if (B200VR_Q_PRIMARY_PREFETCH) {
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+              // (speculative past early termination): its latency overlaps the classification and the queue traffic
+              const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
+              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
+            }
             c_primary++;
             float a = alpha_lookup<POW2>(P, apair_base, s);
             {

@@ -8,10 +8,7 @@ m=importlib.import_module('open-volume-renderer_b200._capi'); m.build(force=True
 import sys, json
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', 'ms', round(d['ms_per_step'],3), 'kernel', round(d['roofline']['kernel_ms_per_launch'],3), 'e2e', round(d['e2e']['ms_per_step'],3), 'frac', round(d['roofline']['frac'],3))"
 }
-run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=1"
-run "-DB200VR_Q_OCC_BITS=0 -DB200VR_Q_DEPTH=1"
-run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=2"
-run "-DB200VR_Q_OCC_BITS=0 -DB200VR_Q_DEPTH=2"
-run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=2 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
-run "-DB200VR_Q_OCC_BITS=1 -DB200VR_Q_DEPTH=1 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
+run "-DB200VR_Q_PRIMARY_PREFETCH=0"
+run "-DB200VR_Q_PRIMARY_PREFETCH=1 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
+run "-DB200VR_Q_PRIMARY_PREFETCH=1"
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
