@@ -56,6 +56,25 @@ __device__ __forceinline__ float2 lds_f32x2(unsigned int addr)
   return v;
 }
 
+__device__ __forceinline__ float4 lds_f32x4(unsigned int addr)
+{
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_f32x4(unsigned int addr, float4 v)
+{
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" : : "r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// keeps a loop-invariant address in a register: ptxas otherwise rebuilds it (5-7 instructions) at every use under the
+// register cap of this kernel
+__device__ __forceinline__ unsigned int pin_u32(unsigned int x)
+{
+  unsigned int y;
+  asm volatile("mov.u32 %0, %1;" : "=r"(y) : "r"(x));
+  return y;
+}
+
 __device__ __forceinline__ float rcp_fast(float x)
 {
   float y;
@@ -128,10 +147,11 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float2* const s_apair = reinterpret_cast<float2*>(smem);
   unsigned int* const s_occ = reinterpret_cast<unsigned int*>(smem + q_alpha_bytes(P.n_alpha));
-  const unsigned int apair_base = (unsigned int)__cvta_generic_to_shared(smem);
-  const unsigned int occ_base = apair_base + (unsigned int)q_alpha_bytes(P.n_alpha);
-  float4* const queue = reinterpret_cast<float4*>(smem + q_alpha_bytes(P.n_alpha) + (OCCS ? q_occ_bytes(P.occ_words) : 0)) +
-                        (size_t)warp * (Q_SLOTS * Q_SLOT_FLOATS / 4);
+  const unsigned int apair_base = pin_u32((unsigned int)__cvta_generic_to_shared(smem));
+  const unsigned int occ_base = pin_u32(apair_base + (unsigned int)q_alpha_bytes(P.n_alpha));
+  // this warp's task queue: slot j = 32 bytes at queue_base + 32 j
+  const unsigned int queue_base = pin_u32(occ_base + (unsigned int)(OCCS ? q_occ_bytes(P.occ_words) : 0) +
+                                          (unsigned int)warp * (unsigned int)(Q_SLOTS * Q_SLOT_FLOATS * sizeof(float)));
   if (SKIP && OCCS)
     for (int i = threadIdx.x; i < P.occ_words; i += blockDim.x) s_occ[i] = P.occ_bits[i];
   for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
@@ -192,7 +212,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
           __syncwarp();
           f3 cC = mk3(0.f), cG = mk3(0.f);
           if (lane < n) {
-            const float4 q0 = queue[2 * lane], q1 = queue[2 * lane + 1];
+            const float4 q0 = lds_f32x4(queue_base + 32u * (unsigned)(lane)), q1 = lds_f32x4(queue_base + 32u * (unsigned)(lane) + 16u);
             const f3 p = mk3(q0.x, q0.y, q0.z);
             const float s = q0.w, w = q1.x;
             const f3 rgb = color_global<POW2>(P, s);
@@ -297,8 +317,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
           }
           __syncwarp();
           if (lane < n) {
-            queue[2 * lane] = make_float4(cC.x, cC.y, cC.z, cG.x);
-            queue[2 * lane + 1] = make_float4(cG.y, cG.z, 0.f, 0.f);
+            sts_f32x4(queue_base + 32u * (unsigned)(lane), make_float4(cC.x, cC.y, cC.z, cG.x));
+            sts_f32x4(queue_base + 32u * (unsigned)(lane) + 16u, make_float4(cG.y, cG.z, 0.f, 0.f));
           }
           __syncwarp();
           // every pixel adds its own samples' contributions in march order (= slot order)
@@ -307,7 +327,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
           while (own) {
             const int j = __ffs(own) - 1;
             own &= own - 1u;
-            const float4 r0 = queue[2 * j], r1 = queue[2 * j + 1];
+            const float4 r0 = lds_f32x4(queue_base + 32u * (unsigned)(j)), r1 = lds_f32x4(queue_base + 32u * (unsigned)(j) + 16u);
             C = C + mk3(r0.x, r0.y, r0.z);
             G = G + mk3(r0.w, r1.x, r1.y);
           }
@@ -315,9 +335,9 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
           // move the tasks that did not fit (at most 31) to the front
           const int rest = count - n;
           float4 m0, m1;
-          if (lane < rest) m0 = queue[2 * (n + lane)], m1 = queue[2 * (n + lane) + 1];
+          if (lane < rest) m0 = lds_f32x4(queue_base + 32u * (unsigned)(n + lane)), m1 = lds_f32x4(queue_base + 32u * (unsigned)(n + lane) + 16u);
           __syncwarp();
-          if (lane < rest) queue[2 * lane] = m0, queue[2 * lane + 1] = m1;
+          if (lane < rest) sts_f32x4(queue_base + 32u * (unsigned)(lane), m0), sts_f32x4(queue_base + 32u * (unsigned)(lane) + 16u, m1);
           mine = n < 32 ? 0ull : (mine >> 32);
           count = rest;
           continue;
@@ -391,8 +411,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
         const unsigned int m = __ballot_sync(0xffffffffu, want);
         if (want) {
           const int slot = count + __popc(m & lt_mask);
-          queue[2 * slot] = make_float4(tp.x, tp.y, tp.z, ts);
-          queue[2 * slot + 1] = make_float4(tw, 0.f, 0.f, 0.f);
+          sts_f32x4(queue_base + 32u * (unsigned)(slot), make_float4(tp.x, tp.y, tp.z, ts));
+          sts_f32x4(queue_base + 32u * (unsigned)(slot) + 16u, make_float4(tw, 0.f, 0.f, 0.f));
           mine |= 1ull << slot;
         }
         count += __popc(m);

@@ -8,7 +8,7 @@ m=importlib.import_module('open-volume-renderer_b200._capi'); m.build(force=True
 import sys, json
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', 'ms', round(d['ms_per_step'],3), 'kernel', round(d['roofline']['kernel_ms_per_launch'],3), 'e2e', round(d['e2e']['ms_per_step'],3), 'frac', round(d['roofline']['frac'],3))"
 }
-run "-DB200VR_Q_PRIMARY_PREFETCH=0"
-run "-DB200VR_Q_PRIMARY_PREFETCH=1 -DB200VR_Q_THREADS=128 -DB200VR_Q_MIN_CTAS=5"
-run "-DB200VR_Q_PRIMARY_PREFETCH=1"
+run "-DB200VR_Q_THREADS=352 -DB200VR_Q_MIN_CTAS=2"
+run "-DB200VR_Q_THREADS=224 -DB200VR_Q_MIN_CTAS=3"
+run "-DB200VR_Q_THREADS=256 -DB200VR_Q_MIN_CTAS=3"
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
