@@ -216,8 +216,19 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = capi.lib()
+    from ovr_b200 import distributed as D
     wl, scene = workload_scene(args.workload)
     W, H = wl["width"], wl["height"]
+    sortlast = bool(wl.get("sortlast"))
+    brick = None
+    if sortlast:
+        # weak scaling: every rank owns one n^3 brick of a (grid * n) volume; explicit TF window (a brick's data range is not the volume's)
+        g = D.brick_grid(world)
+        dims = tuple(g[a] * wl["n"] for a in range(3))
+        scene = ovr_b200.scenes.noise_scene(wl["n"], tf=wl["tf"], camera=wl["camera"], rate=wl["rate"], dims=dims)
+        scene.tfn.value_range = (0.0, 1.0)
+        full_scene = scene
+        scene, brick = D.brick_scene(full_scene, rank, world)
 
     r = ovr_b200.create_renderer("b200", local_rank)
     r.shading = capi.SHADING_REF if wl["shading"] == "ref" else capi.SHADING_NONE
@@ -230,26 +241,34 @@ def run_b200(args):
     r.commit()
     stream = torch.cuda.current_stream()
     r._ck(L.b200vr_set_stream(r.handle, C.c_void_p(stream.cuda_stream)))
-    r._ck(L.b200vr_set_tile_partition(r.handle, rank, world))
-
-    # sort-first exchange buffers: equal-size padded slices, gathered to rank 0
-    slice_floats = max(int(L.b200vr_tile_slice_floats(r.handle, k, world)) for k in range(world))
-    my_slice = torch.zeros(slice_floats, dtype=torch.float32, device="cuda")
-    gathered = [torch.zeros(slice_floats, dtype=torch.float32, device="cuda") for _ in range(world)] if (world > 1 and rank == 0) else None
     launches = [0]
 
-    def step():
-        r.render()
-        launches[0] += r.last_stats["kernel_launches"]
-        if world > 1:
-            r._ck(L.b200vr_pack_tiles(r.handle, C.c_void_p(my_slice.data_ptr())))
-            launches[0] += 1
-            dist.gather(my_slice, gathered, dst=0)
-            if rank == 0:
-                for k in range(1, world):
-                    r._ck(L.b200vr_unpack_tiles(r.handle, C.c_void_p(gathered[k].data_ptr()), k, world))
-                    launches[0] += 1
-        return r.last_stats
+    if sortlast:
+        D.setup_brick_renderer(r, brick)
+        swap = D.SortLast(rank, world, full_scene.volume.dims, W * H, handle_renderer=r)
+
+        def step():
+            eye = r.params["camera"].get().frm   # visibility order follows the committed camera
+            # all pixels against this rank's brick -> premultiplied layer; binary swap; display rank un-premultiplies
+            r.render()
+            launches[0] += r.last_stats["kernel_launches"]
+            img = D.frame_tensor(r)
+            n0 = swap.launches
+            out = swap.composite(img, eye)
+            launches[0] += swap.launches - n0
+            if out is not None:
+                r._ck(L.b200vr_finalize_premultiplied(r.handle, C.c_void_p(out.data_ptr()), W * H))
+                launches[0] += 1
+            return r.last_stats
+    else:
+        # sort-first: own tiles rendered, dense slices gathered on rank 0 (one exchange step)
+        sf = D.SortFirst(r, rank, world)
+
+        def step():
+            n0 = sf.launches
+            st = sf.step()
+            launches[0] += sf.launches - n0
+            return st
 
     def barrier():
         if world > 1:
@@ -286,7 +305,7 @@ def run_b200(args):
         dist.all_reduce(kms, op=dist.ReduceOp.MAX)
     t_ms, samples, fetches, kernel_ms = float(t_ms.item()), float(tot[0].item()), float(tot[1].item()), float(kms.item())
     value = samples / (t_ms * 1e-3) / 1e6
-    return dict(r=r, wl=wl, scene=scene, value=value, t_ms=t_ms, samples=samples, fetches=fetches, kernel_ms=kernel_ms, clk=clk,
+    return dict(r=r, wl=wl, scene=full_scene if sortlast else scene, value=value, t_ms=t_ms, samples=samples, fetches=fetches, kernel_ms=kernel_ms, clk=clk,
                 gpu_launches=gpu_launches, step=step, barrier=barrier, stream=stream, world=world, rank=rank, local_rank=local_rank)
 
 
@@ -316,7 +335,7 @@ def run_e2e(ctx, args):
         # device->host copy of frame k-1 runs on its own stream while frame k renders into the other buffer; both are
         # complete before the step returns. (Under sort-first, rank 0 copies the gathered frame.)
         r.set_camera(orbit_camera(scene, k, args.steps))
-        r.set_transfer_function(c, o, (1.0, -1.0))
+        r.set_transfer_function(c, o, tuple(tfn.value_range))
         r.commit()
         if rank == 0:
             r._ck(L.b200vr_download_async(r.handle, C.c_void_p(rgba_host.data_ptr()), C.c_void_p(grad_host.data_ptr()),
@@ -397,14 +416,16 @@ def main():
                 "hbm": {"achieved": hbm_ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_ach / pk["hbm_gbs"],
                         "bytes_per_launch_upper_bound": hbm_bytes, "peak_source": pk["source"]}}
     line = {"metric": METRIC, "value": ctx["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ctx["t_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ctx["t_ms"] / args.steps, "higher_is_better": True, "scaling": "weak" if wl.get("sortlast") else "strong",
+            "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": workload_name(args, wl), "sampler": args.sampler, "skip_empty": not args.no_skip,
-                       "parallelism": f"sort-first x{world}" if world > 1 else "1 GPU",
+                       "parallelism": (f"sort-last x{world}: one {n}^3 brick per GPU, binary swap over NCCL" if wl.get("sortlast") else
+                                       f"sort-first x{world}" if world > 1 else "1 GPU"),
                        "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                        "samples_per_frame": ctx["samples"] / args.steps, "fetches_per_frame": ctx["fetches"] / args.steps},
             "clocks": ctx["clk"], "e2e": e2e, "gpu_launches": ctx["gpu_launches"], "roofline": roofline}
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and n <= 1024:   # the CPU port needs the whole volume on the host
         from oracle import pyoracle
         vol = np.empty((n, n, n), np.float32)
         r._ck(capi.lib().b200vr_download_volume(r.handle, vol.ctypes.data_as(C.c_void_p)))

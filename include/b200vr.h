@@ -132,6 +132,15 @@ int b200vr_reset_accumulation(b200vr_t* h);               /* framebuffer_reset, 
 
 /* sort-last: clip rays against a sub-box of the object-space unit cube (one brick), default [0,1]^3 */
 int b200vr_set_clip_box(b200vr_t* h, const float lo[3], const float hi[3]);
+/* sort-last with pixel-matched results: this handle holds ONE BRICK of a larger volume (its own voxels plus ghost layers,
+ * placed by obj_to_world). vol_lo..vol_hi is the world-space box of the whole volume, own_lo..own_hi the world-space box of
+ * the voxels this brick is responsible for. Every ray walks the sample lattice t_k of the WHOLE volume (it starts where the
+ * ray enters vol_lo..vol_hi) and the handle renders exactly the samples whose midpoint lies inside own_lo..own_hi. Both
+ * intervals are computed in world space, so that all bricks agree bit for bit on a shared cut plane: the union over the
+ * bricks is the sample set of the single-device march (shaders_raymarching.cu:87-171), only early termination is per
+ * brick. All four NULL restores the default. Ray marching with SHADING_NONE only (shadow rays leave the brick). */
+int b200vr_set_brick(b200vr_t* h, const float own_lo_or_null[3], const float own_hi_or_null[3], const float vol_lo_or_null[3],
+                     const float vol_hi_or_null[3]);
 /* sort-first: render only the image tiles owned by `rank` of `nranks` (64x32-pixel tiles, round robin) */
 int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks);
 

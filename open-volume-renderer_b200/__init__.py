@@ -12,3 +12,4 @@ from .scenes import Camera, Scene, TransferFunction, Volume  # noqa: F401
 __all__ = ["capi", "scenes", "MainRenderer", "FrameBufferData", "create_renderer", "Camera", "Scene", "TransferFunction",
            "Volume"]
 from . import scene_io  # noqa: F401,E402
+from . import distributed  # noqa: F401,E402

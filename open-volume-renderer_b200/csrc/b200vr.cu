@@ -62,6 +62,9 @@ struct b200vr {
   // params
   b200vr_params prm;
   f3 clip_lo = { 0.f, 0.f, 0.f }, clip_hi = { 1.f, 1.f, 1.f };
+  bool has_lattice = false; // sort-last brick: the t lattice starts where the ray enters lat_lo..lat_hi, not the clip box
+  f3 lat_lo = { 0.f, 0.f, 0.f }, lat_hi = { 1.f, 1.f, 1.f }; // world space: the whole volume
+  f3 own_lo = { 0.f, 0.f, 0.f }, own_hi = { 1.f, 1.f, 1.f }; // world space: the part this handle renders
   int rank = 0, nranks = 1;
   // frame: double buffer {rgba, grad} + accumulation (optix7_common.h:256-414, device_impl.cpp:204-241)
   int width = 0, height = 0;
@@ -553,6 +556,25 @@ extern "C" int b200vr_set_clip_box(b200vr_t* h, const float lo[3], const float h
   return B200VR_OK;
 }
 
+extern "C" int b200vr_set_brick(b200vr_t* h, const float own_lo[3], const float own_hi[3], const float vol_lo[3], const float vol_hi[3])
+{
+  if (!h) return B200VR_EINVAL;
+  if (!own_lo || !own_hi || !vol_lo || !vol_hi) { // back to the default: one volume, lattice starts at the clip box
+    h->has_lattice = false;
+    h->reset = true;
+    return B200VR_OK;
+  }
+  for (int i = 0; i < 3; i++)
+    if (!(own_hi[i] > own_lo[i]) || !(vol_hi[i] > vol_lo[i])) return fail(h, B200VR_EINVAL, "set_brick: empty box");
+  h->own_lo = mk3(own_lo[0], own_lo[1], own_lo[2]);
+  h->own_hi = mk3(own_hi[0], own_hi[1], own_hi[2]);
+  h->lat_lo = mk3(vol_lo[0], vol_lo[1], vol_lo[2]);
+  h->lat_hi = mk3(vol_hi[0], vol_hi[1], vol_hi[2]);
+  h->has_lattice = true;
+  h->reset = true;
+  return B200VR_OK;
+}
+
 extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
 {
   if (!h) return B200VR_EINVAL;
@@ -633,6 +655,11 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.wto = h->wto;
   P.clip_lo = h->clip_lo;
   P.clip_hi = h->clip_hi;
+  P.brick = h->has_lattice ? 1 : 0;
+  P.lat_lo = h->lat_lo;
+  P.lat_hi = h->lat_hi;
+  P.own_lo = h->own_lo;
+  P.own_hi = h->own_hi;
   P.tf_color = h->tf_color;
   P.tf_alpha = h->tf_alpha;
   P.n_color = h->n_color, P.n_alpha = h->n_alpha;
@@ -728,6 +755,10 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
 
   LaunchParams P;
   fill_launch_params(h, P);
+  if (h->has_lattice && !(h->prm.mode == B200VR_MODE_RAYMARCH && h->prm.shading == B200VR_SHADING_NONE &&
+                           h->prm.sampler == B200VR_SAMPLER_TEX3D && !std::getenv("B200VR_KERNEL")))
+    return fail(h, B200VR_ESTATE, "render: a brick (sort-last) needs ray marching with SHADING_NONE and the tex3D sampler: "
+                                  "shadow rays and random walks leave the brick");
   const KernelChoice kc = pick_kernel(h);
   const render_kernel_t kernel = kc.fn;
   const size_t smem = kc.smem;

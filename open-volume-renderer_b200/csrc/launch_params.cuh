@@ -27,6 +27,9 @@ struct LaunchParams {
   f3 rdim;                  // 1 / dims
   aff3 otw, wto;
   f3 clip_lo, clip_hi;      // object-space clip box (unit cube unless sort-last)
+  int brick;                // sort-last: march the t lattice of the whole volume, own the samples whose midpoint is inside own_lo..own_hi
+  f3 lat_lo, lat_hi;        // WORLD-space box of the whole volume (brick only)
+  f3 own_lo, own_hi;        // WORLD-space box of this brick's own voxels (brick only)
   // ---- transfer function (global copies; staged into shared memory by every CTA) ----
   const float4* tf_color;
   const float* tf_alpha;

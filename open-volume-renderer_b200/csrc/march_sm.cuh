@@ -208,10 +208,34 @@ raymarch_sm_kernel(const __grid_constant__ LaunchParams P)
       const f3 dir = normalize3(P.cam_dir + (sx - 0.5f) * P.cam_hor + (sy - 0.5f) * P.cam_ver);
       const f3 od = xfm_vector(P.wto.l, dir);
       float tx = 0.f, t1 = FLT_MAX;
-      bool active = inside && intersect_box(tx, t1, oo, od, P.clip_lo, P.clip_hi);
+      bool active;
+      float own_exit = FLT_MAX; // sort-last brick: samples with midpoint in [b0, own_exit) are this handle's
+      float b0 = 0.f;
+      if (!P.brick) active = inside && intersect_box(tx, t1, oo, od, P.clip_lo, P.clip_hi);
+      else {
+        // Both intervals come from WORLD-space slab tests on the world ray: every rank then computes bit-identical
+        // parameters for a shared cut plane, so the bricks partition the lattice samples exactly (no sample is rendered
+        // twice or dropped), and all ranks walk the same lattice.
+        active = inside && intersect_box(tx, t1, P.cam_pos, dir, P.lat_lo, P.lat_hi);
+        active = intersect_box(b0, own_exit, P.cam_pos, dir, P.own_lo, P.own_hi) && active;
+      }
       if (inside) c_rays++;
       float ty = fminf(t1, tx + step);
       active = active && ty > tx;
+      if (P.brick && active && 0.5f * (tx + ty) < b0) { // walk the lattice up to the brick: the same running sum as the march itself
+        const float lim = fminf(b0, t1) - 5.f * step;
+        while (ty < lim) {
+          ty += step;
+          ty += step;
+          ty += step;
+          ty += step;
+        }
+        do {
+          tx = ty;
+          ty = fminf(tx + step, t1);
+        } while (ty > tx && 0.5f * (tx + ty) < b0);
+        active = ty > tx;
+      }
       const f3 od_rcp = mk3(1.f / od.x, 1.f / od.y, 1.f / od.z);
       float A = 0.f;
       f3 C = mk3(0.f), G = mk3(0.f);
@@ -261,6 +285,10 @@ raymarch_sm_kernel(const __grid_constant__ LaunchParams P)
             }
             // ---- one primary sample (raymarching, shaders_raymarching.cu:87-171) ----
             const float tm = 0.5f * (tx + ty);
+            if (!(tm < own_exit)) { // the rest of the lattice belongs to the bricks behind this one
+              active = false;
+              break;
+            }
             const f3 p = mk3(__fmaf_rn(tm, od.x, oo.x), __fmaf_rn(tm, od.y, oo.y), __fmaf_rn(tm, od.z, oo.z));
             if (SKIP) {
               if (!(tm < cell_exit)) {
