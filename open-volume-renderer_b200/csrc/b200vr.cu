@@ -9,6 +9,7 @@
 #include "raymarch.cuh"
 #include "march_sm.cuh"
 #include "march_q.cuh"
+#include "march_ring.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -75,6 +76,19 @@ struct b200vr {
   int frame_index = 0;
   bool reset = true;
   unsigned int* tile_counter = nullptr;
+  // launch order of the super tiles (build.cuh tile_order_kernel): cost of the previous frame, cost being collected, order
+  unsigned int* tile_cost[2] = { nullptr, nullptr };
+  int* tile_order = nullptr;
+  int tile_slots = 0;      // allocated slots (super tiles of the whole image)
+  int cost_cur = 0;        // tile_cost[cost_cur] is written by the next launch, tile_cost[cost_cur ^ 1] orders it
+  bool cost_valid = false; // false: no history for this image size / partition -> centre-out order
+  // deferred-shading ring of the ring kernel (march_ring.cuh), allocated on first use
+  unsigned int* ring_ctrl = nullptr;
+  unsigned int* ring_seq = nullptr;
+  float4* ring_data = nullptr;
+  int ring_cap = 0, ring_count = 0;
+  unsigned long long* acc = nullptr; // per pixel fixed-point sums (allocated with the frame)
+  float* ray_alpha = nullptr;
   Counters* counters = nullptr;
 };
 
@@ -200,6 +214,14 @@ extern "C" void b200vr_destroy(b200vr_t* h)
   cudaFree(h->tf_color);
   cudaFree(h->tf_alpha);
   cudaFree(h->tile_counter);
+  cudaFree(h->tile_cost[0]);
+  cudaFree(h->tile_cost[1]);
+  cudaFree(h->tile_order);
+  cudaFree(h->ring_ctrl);
+  cudaFree(h->ring_seq);
+  cudaFree(h->ring_data);
+  cudaFree(h->acc);
+  cudaFree(h->ray_alpha);
   cudaFree(h->counters);
   cudaFree(h->minmax);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -532,6 +554,19 @@ extern "C" int b200vr_resize(b200vr_t* h, int width, int height)
     CK(cudaMemset(h->accum, 0, n * sizeof(float4)));
     h->width = width;
     h->height = height;
+    cudaFree(h->tile_cost[0]);
+    cudaFree(h->tile_cost[1]);
+    cudaFree(h->tile_order);
+    h->tile_slots = ((width + SUPER_TILE_W - 1) / SUPER_TILE_W) * ((height + SUPER_TILE_H - 1) / SUPER_TILE_H);
+    for (int i = 0; i < 2; i++) CK(cudaMalloc(&h->tile_cost[i], (size_t)h->tile_slots * sizeof(unsigned int)));
+    CK(cudaMalloc(&h->tile_order, (size_t)h->tile_slots * sizeof(int)));
+    h->cost_valid = false;
+    cudaFree(h->acc);
+    cudaFree(h->ray_alpha);
+    CK(cudaMalloc(&h->acc, n * 3 * sizeof(unsigned long long)));
+    CK(cudaMemset(h->acc, 0, n * 3 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&h->ray_alpha, n * sizeof(float)));
+    CK(cudaMemset(h->ray_alpha, 0, n * sizeof(float)));
   }
   if (h->lookat_valid) derive_camera(h); // "camera.update() || framebuffer_size_updated", device_impl.cpp:125
   h->reset = true;
@@ -579,6 +614,7 @@ extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
 {
   if (!h) return B200VR_EINVAL;
   if (nranks < 1 || rank < 0 || rank >= nranks) return fail(h, B200VR_EINVAL, "set_tile_partition: bad rank");
+  if (rank != h->rank || nranks != h->nranks) h->cost_valid = false; // slots mean other super tiles now
   h->rank = rank;
   h->nranks = nranks;
   h->reset = true;
@@ -598,6 +634,7 @@ struct KernelChoice {
   render_kernel_t fn;
   int threads;
   size_t smem;
+  bool ring = false; // march_ring.cuh: needs the task ring, one launch per sample + resolve_kernel
 };
 
 static KernelChoice pick_kernel(const b200vr_t* h)
@@ -605,6 +642,10 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   const b200vr_params& p = h->prm;
   const char* force = std::getenv("B200VR_KERNEL");
   const bool legacy = force && std::strcmp(force, "legacy") == 0, sm = force && std::strcmp(force, "sm") == 0;
+  // Per-warp queue kernel (march_q.cuh) or queue + work-sharing rings (march_ring.cuh). Measured on C2: the whole frame on
+  // one GPU 2.29 vs 2.65 ms (the rings cost ~8 % more instructions), an eighth of its tiles 1.06-1.50 vs 0.80-1.13 ms (the
+  // heaviest warp tile alone takes ~1 ms with the queue kernel): rings when the frame is split sort-first, queue otherwise.
+  const bool q = force ? std::strcmp(force, "q") == 0 : h->nranks == 1;
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
@@ -616,9 +657,17 @@ static KernelChoice pick_kernel(const b200vr_t* h)
     if (p.shading == B200VR_SHADING_REF && !sm) {
       const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
       const bool occs = p.skip_empty && q_occ_in_smem(h->occ_words);
-      if (!p.skip_empty) k.fn = pow2 ? raymarch_q_kernel<false, true, false> : raymarch_q_kernel<false, false, false>;
-      else if (occs) k.fn = pow2 ? raymarch_q_kernel<true, true, true> : raymarch_q_kernel<true, false, true>;
-      else k.fn = pow2 ? raymarch_q_kernel<true, true, false> : raymarch_q_kernel<true, false, false>;
+      if (q) {
+        if (!p.skip_empty) k.fn = pow2 ? raymarch_q_kernel<false, true, false> : raymarch_q_kernel<false, false, false>;
+        else if (occs) k.fn = pow2 ? raymarch_q_kernel<true, true, true> : raymarch_q_kernel<true, false, true>;
+        else k.fn = pow2 ? raymarch_q_kernel<true, true, false> : raymarch_q_kernel<true, false, false>;
+      }
+      else {
+        if (!p.skip_empty) k.fn = pow2 ? raymarch_ring_kernel<false, true, false> : raymarch_ring_kernel<false, false, false>;
+        else if (occs) k.fn = pow2 ? raymarch_ring_kernel<true, true, true> : raymarch_ring_kernel<true, false, true>;
+        else k.fn = pow2 ? raymarch_ring_kernel<true, true, false> : raymarch_ring_kernel<true, false, false>;
+        k.ring = true;
+      }
       k.threads = Q_THREADS;
       k.smem = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0) + q_queue_bytes();
       return k;
@@ -737,7 +786,17 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.rank = h->rank, P.nranks = h->nranks;
   P.n_warp_tiles = owned_super_tiles(h->rank, h->nranks, P.super_w * P.super_h) * WARP_TILES_PER_SUPER;
   P.tile_counter = h->tile_counter;
+  P.tile_order = h->tile_order;
+  P.tile_cost = h->tile_cost[h->cost_cur];
   P.counters = h->counters;
+  P.ring_ctrl = h->ring_ctrl;
+  P.ring_seq = h->ring_seq;
+  P.ring_data = h->ring_data;
+  P.ring_cap = h->ring_cap;
+  P.ring_high = 0;
+  P.acc = h->acc;
+  P.ray_alpha = h->ray_alpha;
+  P.sidx = 0;
 }
 
 extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
@@ -771,15 +830,85 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   const int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
   CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
   CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
+  {
+    // launch order: owned super tiles by descending cost of the previous frame (no history: centre-out)
+    const int n_owned = P.n_warp_tiles / WARP_TILES_PER_SUPER;
+    if (!h->cost_valid) CK(cudaMemsetAsync(h->tile_cost[h->cost_cur ^ 1], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
+    // 0 (default) row-major, 1 centre-out, 2 by the previous frame's cost. Measured on C2 with the queue kernel: 2.29 / 2.52 /
+    // 2.42 ms -- launching neighbouring tiles together keeps their texels in L1/L2, and a heavy tile is itself the critical
+    // path whenever it starts (tools/partition_probe.py), so "expensive first" buys nothing.
+    const char* om = std::getenv("B200VR_TILE_ORDER");
+    const int order_mode = om ? std::atoi(om) : 0;
+    if (n_owned > 0) {
+      tile_order_kernel<<<(n_owned + 127) / 128, 128, 0, h->stream>>>(h->tile_cost[h->cost_cur ^ 1], n_owned, h->rank, h->nranks,
+                                                                       P.super_w, P.super_h, h->tile_order, order_mode);
+      CK(cudaGetLastError());
+    }
+    CK(cudaMemsetAsync(h->tile_cost[h->cost_cur], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
+    h->cost_valid = true;
+    h->cost_cur ^= 1; // P.tile_cost was taken before the flip: this launch writes it, the next one reads it
+  }
+  int launches = 0;
+  if (kc.ring && P.n_warp_tiles > 0) {
+    // one ring per CTA: high-water mark + one block in flight per warp of the CTA + slack, as a power of two
+    const char* hw = std::getenv("B200VR_RING_HIGH");
+    P.ring_high = hw ? std::max(1, std::atoi(hw)) : 4; // blocks kept ready per CTA for warps that have run out of tiles
+    int cap = 32;
+    while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
+    if (cap != h->ring_cap || grid != h->ring_count) {
+      CK(cudaStreamSynchronize(h->stream));
+      cudaFree(h->ring_ctrl);
+      cudaFree(h->ring_seq);
+      cudaFree(h->ring_data);
+      h->ring_ctrl = nullptr, h->ring_seq = nullptr, h->ring_data = nullptr, h->ring_cap = 0, h->ring_count = 0;
+      CK(cudaMalloc(&h->ring_ctrl, ring_ctrl_words(grid) * sizeof(unsigned int)));
+      CK(cudaMalloc(&h->ring_seq, (size_t)cap * grid * sizeof(unsigned int)));
+      CK(cudaMalloc(&h->ring_data, (size_t)cap * grid * RING_BLOCK_FLOAT4 * sizeof(float4)));
+      h->ring_cap = cap, h->ring_count = grid;
+      ring_init_kernel<<<64, 256, 0, h->stream>>>(h->ring_seq, cap, grid, h->ring_ctrl, (int)ring_ctrl_words(grid));
+      CK(cudaGetLastError());
+    }
+    P.ring_ctrl = h->ring_ctrl, P.ring_seq = h->ring_seq, P.ring_data = h->ring_data, P.ring_cap = h->ring_cap;
+  }
   CK(cudaEventRecord(h->ev0, h->stream));
-  if (P.n_warp_tiles > 0) {
+  if (P.n_warp_tiles > 0 && !kc.ring) {
     void* args[] = { (void*)&P };
     CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3((unsigned)kc.threads), args, smem, h->stream));
+    launches = 1;
+  }
+  else if (P.n_warp_tiles > 0) {
+    const int n_owned = P.n_warp_tiles / WARP_TILES_PER_SUPER;
+    for (int sidx = 0; sidx < P.spp; sidx++) { // one march + one resolve per sample of the pixel
+      P.sidx = sidx;
+      if (sidx > 0) CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
+      ring_start_kernel<<<(grid + 127) / 128, 128, 0, h->stream>>>(h->ring_ctrl, RING_CTRL_STRIDE, grid, warps_per_cta);
+      CK(cudaGetLastError());
+      void* args[] = { (void*)&P };
+      CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3((unsigned)kc.threads), args, smem, h->stream));
+      const size_t npx = (size_t)n_owned * SUPER_TILE_W * SUPER_TILE_H;
+      resolve_kernel<<<(unsigned)std::min<size_t>((npx + 255) / 256, (size_t)h->sm_count * 16), 256, 0, h->stream>>>(P, n_owned);
+      CK(cudaGetLastError());
+      launches += 3;
+    }
   }
   CK(cudaEventRecord(h->ev1, h->stream));
   Counters c;
   CK(cudaMemcpyAsync(&c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+  unsigned int ring_err = 0;
+  if (kc.ring && h->ring_ctrl) CK(cudaMemcpyAsync(&ring_err, h->ring_ctrl + (size_t)h->ring_count * RING_CTRL_PER_RING + RING_CTRL_STRIDE, sizeof(ring_err), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream)); // synchronous like DeviceOptix7::render (device.cpp:34-43)
+  if (ring_err) {
+    h->ring_cap = 0; // rebuilt on the next render
+    return fail(h, B200VR_ECUDA, "render: the deferred-shading ring timed out (internal error)");
+  }
+  if (B200VR_TILE_STATS && std::getenv("B200VR_DEBUG_TILES")) { // build with -DB200VR_TILE_STATS=1
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    std::fprintf(stderr, "[b200] tiles: kernel %.3f ms, longest warp tile %.0f kclk, all tiles %.0f Mclk over %d warps = %.0f kclk each\n", ms,
+                 c.tile_clocks_max * 1e-3, c.tile_clocks_sum * 1e-6, grid * warps_per_cta, c.tile_clocks_sum * 1e-3 / (grid * warps_per_cta));
+    std::fprintf(stderr, "[b200] ring: longest warp %.0f kclk, after the last tile %.0f kclk per warp, blocks published %llu, taken by draining warps %llu\n",
+                 c.warp_clocks_max * 1e-3, c.drain_clocks_sum * 1e-3 / (grid * warps_per_cta), c.blocks_published, c.blocks_stolen);
+  }
   if (stats) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
@@ -790,7 +919,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     stats->delta_samples = c.delta_samples;
     stats->rays = c.rays;
     stats->frame_index = h->frame_index;
-    stats->kernel_launches = P.n_warp_tiles > 0 ? 1 : 0;
+    stats->kernel_launches = launches;
   }
   return B200VR_OK;
 }

@@ -182,6 +182,111 @@ __global__ void occupancy_bits_kernel(const float* __restrict__ maj_pad, int n_p
   }
 }
 
+// ---- launch order of the super tiles: most expensive first ----------------------------------------------------------
+// A warp tile is a serial chain (march, shade 32 samples, march ...) that can take a large part of the whole frame
+// time; started late it becomes the tail of the launch. The owned super tiles are therefore launched in descending order of
+// the warp time they took in the previous frame (frames of an interactive session are similar); without a history (all
+// costs 0) the order is centre-out, the volume usually being in the middle of the image. Rank sort, one thread per tile.
+__global__ void tile_order_kernel(const unsigned int* __restrict__ cost, int n_owned, int rank, int nranks, int super_w, int super_h,
+                                  int* __restrict__ order, int mode)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_owned) return;
+  if (mode == 0) { // row-major, for A/B runs
+    order[i] = i;
+    return;
+  }
+  auto key = [&](int m) { // larger = earlier
+    const int s = rank + m * nranks;
+    const float dx = (float)(s % super_w) + 0.5f - 0.5f * (float)super_w, dy = (float)(s / super_w) + 0.5f - 0.5f * (float)super_h;
+    const unsigned int d = (unsigned int)fminf(4.f * (2.f * dx * 2.f * dx + dy * dy), 1048575.f); // tiles are 64 x 32 pixels
+    return ((unsigned long long)(mode == 2 ? cost[m] : 0u) << 20) | (unsigned long long)(1048575u - d);
+  };
+  const unsigned long long ki = key(i);
+  int pos = 0;
+  for (int j = 0; j < n_owned; j++) {
+    const unsigned long long kj = key(j);
+    pos += (kj > ki) || (kj == ki && j < i);
+  }
+  order[pos] = i;
+}
+
+// ---- end of a ring-kernel sample: fixed-point sums -> frame (the tail of raymarch_q_kernel, per pixel of the owned super tiles) ----
+__global__ void resolve_kernel(const LaunchParams P, int n_owned)
+{
+  const size_t n = (size_t)n_owned * SUPER_TILE_W * SUPER_TILE_H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / (SUPER_TILE_W * SUPER_TILE_H)), r = (int)(i % (SUPER_TILE_W * SUPER_TILE_H));
+    const int s = P.rank + m * P.nranks;
+    const int ix = (s % P.super_w) * SUPER_TILE_W + r % SUPER_TILE_W, iy = (s / P.super_w) * SUPER_TILE_H + r / SUPER_TILE_W;
+    if (ix >= P.width || iy >= P.height) continue;
+    const size_t pixel_index = (size_t)ix + (size_t)iy * (size_t)P.width;
+    unsigned long long* const acc = P.acc + 3 * pixel_index;
+    const unsigned long long a0 = acc[0], a1 = acc[1], a2 = acc[2];
+    acc[0] = 0ull, acc[1] = 0ull, acc[2] = 0ull; // ready for the next sample / frame
+    const float k = 1.f / 1073741824.f;
+    f3 C = mk3((float)(unsigned int)a0 * k, (float)(unsigned int)(a0 >> 32) * k, (float)(unsigned int)a1 * k);
+    f3 G = mk3((float)(unsigned int)(a1 >> 32) * k, (float)(unsigned int)a2 * k, (float)(unsigned int)(a2 >> 32) * k);
+    const float A = P.ray_alpha[pixel_index];
+    // render_raymarching (shaders_raymarching.cu:260-321): background is always 0 -> alpha_blend = C / A
+    if (!P.premultiplied) {
+      C = A > 0.f ? C / A : mk3(0.f);
+      G = A > 0.f ? G / A : mk3(0.f);
+    }
+    float4 px4 = make_float4(C.x, C.y, C.z, A);
+    float* g = P.grad + 3 * pixel_index;
+    if (P.sidx > 0) { // running sums over the samples of this pixel
+      const float4 prev = P.rgba[pixel_index];
+      px4 = make_float4(prev.x + px4.x, prev.y + px4.y, prev.z + px4.z, prev.w + px4.w);
+      G = G + mk3(g[0], g[1], g[2]);
+    }
+    if (P.sidx == P.spp - 1) {
+      const float rspp = 1.f / (float)P.spp;
+      px4 = make_float4(px4.x * rspp, px4.y * rspp, px4.z * rspp, px4.w * rspp);
+      G = G * rspp;
+      // frame write / progressive accumulation (shaders_raymarching.cu:389-406)
+      if (P.accumulate) {
+        if (P.frame_index == 1) {
+          P.accum[pixel_index] = px4;
+        }
+        else {
+          const float4 acc4 = P.accum[pixel_index];
+          const float4 sum = make_float4(acc4.x + px4.x, acc4.y + px4.y, acc4.z + px4.z, acc4.w + px4.w);
+          P.accum[pixel_index] = sum;
+          const float fi = (float)P.frame_index;
+          px4 = make_float4(sum.x / fi, sum.y / fi, sum.z / fi, sum.w / fi);
+        }
+      }
+    }
+    P.rgba[pixel_index] = px4;
+    g[0] = G.x;
+    g[1] = G.y;
+    g[2] = G.z;
+  }
+}
+
+__global__ void ring_init_kernel(unsigned int* seq, int cap, int shards, unsigned int* ctrl, int ctrl_words)
+{
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cap * shards; i += gridDim.x * blockDim.x) seq[i] = (unsigned int)(i % cap);
+  if (blockIdx.x == 0)
+    for (int i = threadIdx.x; i < ctrl_words; i += blockDim.x) ctrl[i] = 0u;
+}
+// start of a ring launch (one thread per ring = per CTA): draining warps of the previous launch may have drawn tickets beyond
+// the last published block
+__global__ void ring_start_kernel(unsigned int* ctrl, int stride, int rings, int warps_per_cta)
+{
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < rings) {
+    unsigned int* c = ctrl + (size_t)r * 3 * stride;
+    c[stride] = c[0];
+    c[2 * stride] = (unsigned int)warps_per_cta;
+  }
+  if (r == 0) {
+    ctrl[(size_t)rings * 3 * stride] = (unsigned int)(rings * warps_per_cta);
+    ctrl[(size_t)rings * 3 * stride + stride] = 0u;
+  }
+}
+
 // ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------
 // slice layout: [owned super tile m][y in 32][x in 64][rgba]; pixels outside the image are zero in the slice
 template<bool PACK>

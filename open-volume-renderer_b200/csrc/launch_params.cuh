@@ -14,9 +14,14 @@ constexpr int SUPER_TILE_W = 64;   // sort-first ownership granule: 64 x 32 pixe
 constexpr int SUPER_TILE_H = 32;
 constexpr int WARP_TILES_PER_SUPER = (SUPER_TILE_W / WARP_TILE_W) * (SUPER_TILE_H / WARP_TILE_H);
 constexpr int RENDER_THREADS = 128;
+#ifndef B200VR_TILE_STATS
+#define B200VR_TILE_STATS 0
+#endif
 
 struct Counters {
   unsigned long long primary_samples, shadow_samples, gradient_fetches, delta_samples, rays;
+  unsigned long long tile_clocks_max, tile_clocks_sum; // longest warp tile / all warp tiles, in SM clocks (B200VR_DEBUG_TILES)
+  unsigned long long drain_clocks_sum, warp_clocks_max, blocks_published, blocks_stolen; // ring kernel: after a warp's last tile
 };
 
 struct LaunchParams {
@@ -81,21 +86,42 @@ struct LaunchParams {
   int rank, nranks;         // sort-first ownership: super tile s belongs to rank s % nranks
   int n_warp_tiles;         // warp tiles this launch has to render
   unsigned int* tile_counter;
+  const int* tile_order;    // launch order of the owned super tiles: tile_order[j] = slot m (super tile rank + m * nranks)
+  unsigned int* tile_cost;  // per slot m: warp clocks / 64 spent on its warp tiles in THIS launch (orders the next one)
   Counters* counters;
+  // ---- deferred-shading ring (march_ring.cuh) ----
+  unsigned int* ring_ctrl;  // [0] head, [1] tail, [2] warps still marching, [3] error
+  unsigned int* ring_seq;   // per slot sequence number
+  float4* ring_data;        // ring_cap blocks of 64 float4 (32 tasks)
+  int ring_cap, ring_high;  // slots (power of two); fill level above which a producer shades a block before publishing
+  unsigned long long* acc;  // per pixel 3 words of fixed-point sums: (r|g), (b|Gx), (Gy|Gz)
+  float* ray_alpha;         // per pixel opacity of the sample being rendered
+  int sidx;                 // sample index of this launch (the spp loop runs on the host for the ring kernel)
 };
 
-// k-th warp tile owned by (rank, nranks) -> pixel origin. Inside a super tile the 64 warp tiles are ordered so that 16
-// consecutive ones form a 4 x 4 block of tiles (32 x 16 pixels): a CTA that takes 16 consecutive tiles works on one compact
-// screen region, i.e. on one compact bundle of primary and shadow rays (L1 / texture-cache locality).
+// k-th warp tile of this launch -> pixel origin and the slot m of its super tile in the cost / order tables. The launch walks
+// the owned super tiles in the order of P.tile_order (most expensive first, see tile_order_kernel); inside a super tile the
+// 64 warp tiles are ordered so that 16 consecutive ones form a 4 x 4 block of tiles (32 x 16 pixels).
 constexpr int TILE_CHUNK = 16;
-__host__ __device__ __forceinline__ void warp_tile_origin(int k, int rank, int nranks, int super_w, int& px, int& py)
+__device__ __forceinline__ int warp_tile_origin(const LaunchParams& P, int k, int& px, int& py)
 {
-  const int m = k / WARP_TILES_PER_SUPER, r = k % WARP_TILES_PER_SUPER;
-  const int s = rank + m * nranks;
-  const int sx = s % super_w, sy = s / super_w;
+  const int m = P.tile_order[k / WARP_TILES_PER_SUPER], r = k % WARP_TILES_PER_SUPER;
+  const int s = P.rank + m * P.nranks;
+  const int sx = s % P.super_w, sy = s / P.super_w;
   const int b = r / TILE_CHUNK, i = r % TILE_CHUNK; // block (2 x 2 per super tile), tile inside the block (4 x 4)
   px = sx * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W;
   py = sy * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
+  return m;
+}
+// a warp reports how long its tile took: next frame's launch order
+__device__ __forceinline__ void tile_cost_add(const LaunchParams& P, int m, long long t_start)
+{
+  const unsigned long long dt = (unsigned long long)(clock64() - t_start);
+  atomicAdd(P.tile_cost + m, (unsigned int)(dt >> 6));
+#if B200VR_TILE_STATS // two more atomics per tile on single words: measurably slows the launch, debugging only
+  atomicMax(&P.counters->tile_clocks_max, dt);
+  atomicAdd(&P.counters->tile_clocks_sum, dt);
+#endif
 }
 __host__ __device__ __forceinline__ int owned_super_tiles(int rank, int nranks, int n_super)
 {

@@ -139,6 +139,82 @@ __device__ __forceinline__ f3 color_global(const LaunchParams& P, float s)
   return mk3(__fmaf_rn(w, c1.x - c0.x, c0.x), __fmaf_rn(w, c1.y - c0.y, c0.y), __fmaf_rn(w, c1.z - c0.z, c0.z));
 }
 
+// Shading of one deferred sample (position p in object space, scalar s, compositing weight w): colour lookup, forward-
+// difference gradient, shadow march toward the light, Phong-less "0.5 + cos * transmittance" shading of the reference
+// (shaders_raymarching.cu:126-169, 205-229, 44-85). Returns the colour and normal-layer contributions of the sample.
+template<bool SKIP, bool POW2, bool OCCS>
+__device__ __forceinline__ void shade_task(const LaunchParams& P, unsigned int apair_base, unsigned int occ_base, f3 p, float s, float w,
+                                           unsigned int& c_shaded, unsigned int& c_shadow, f3& cC, f3& cG)
+{
+  const f3 rgb = color_global<POW2>(P, s);
+  // compute_volume_gradient_object_space (shaders_common.h:195-215): forward differences, step 1/dims
+  f3 stp = P.rdim;
+  if (p.x + stp.x > 1.f) stp.x = -stp.x;
+  if (p.y + stp.y > 1.f) stp.y = -stp.y;
+  if (p.z + stp.z > 1.f) stp.z = -stp.z;
+  const float gx = tex3D<float>(P.tex, p.x + stp.x, p.y, p.z) - s;
+  const float gy = tex3D<float>(P.tex, p.x, p.y + stp.y, p.z) - s;
+  const float gz = tex3D<float>(P.tex, p.x, p.y, p.z + stp.z) - s;
+  c_shaded++;
+  // shadow ray from the sample toward the light (__closesthit__volume_shadow + raymarching_shadow,
+  // shaders_raymarching.cu:205-229,44-85), transmittance accumulated as a sum of logs
+  // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
+  // while sample k is classified the fetch of k+1 and the majorant of k+2 are already in flight.
+  float slog = 0.f, stx, st1;
+  if (clip_shadow_p(P, p, stx, st1)) {
+    const float sstep = P.sstep;
+    // All lanes walk the fixed t lattice in lockstep (neighbouring shadow rays then fetch neighbouring texels: letting
+    // each lane run ahead to its next live sample measured 3.60 ms against 2.95 ms); a sample in an empty macrocell
+    // (alpha == 0 exactly, adds 0 to the log sum) costs the cell test only.
+    auto cell_live = [&](float tm) { // bit test in shared memory (reading the float majorants through L1TEX instead: 2.91 vs 2.61 ms)
+      return occ_bit<OCCS>(P, occ_base, pad_index_floor(P, mk3(__fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y),
+                                                               __fmaf_rn(tm, P.sh_d.z, p.z))));
+    };
+    auto fetch = [&](float tm) {
+      return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
+    };
+    auto classify = [&](float sv, float dt) {
+      c_shadow++;
+      const float a = alpha_lookup<POW2>(P, apair_base, sv);
+      // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
+      slog = __fmaf_rn(P.base * dt, lg2_fast(fmaxf(1.f - a, 0.f)), slog);
+    };
+    // Software pipeline: sample positions do not depend on fetched data (fixed t lattice), so while sample k is
+    // classified the fetch of k+1 and the macrocell test of k+2 are already in flight.
+    // intervals: current [stx, sty], next [sty, nty], the one after [nty, n2ty]
+    // (Measured alternatives on C2: batches of 4/8 independent samples per ray 3.09/3.07 ms against 2.95 ms for this
+    // pipeline; a second fetch in flight per ray 2.64 against 2.61 ms.)
+    float sty = fminf(st1, stx + sstep);
+    const float tm_c = 0.5f * (stx + sty);
+    bool live_c = !SKIP || cell_live(tm_c);
+    float s_c = 0.f;
+    if (live_c && sty > stx) s_c = fetch(tm_c);
+    float nty = fminf(sty + sstep, st1);
+    float tm_n = 0.5f * (sty + nty);
+    bool live_n = !SKIP || cell_live(tm_n);
+#pragma unroll 2
+    while (sty > stx && slog > P.log_ert) {
+      float s_n = 0.f;
+      if (live_n && nty > sty) s_n = fetch(tm_n); // prefetch; unused if the ray ends at this sample
+      const float n2ty = fminf(nty + sstep, st1);
+      const float tm_n2 = 0.5f * (nty + n2ty);
+      const bool live_n2 = !SKIP || cell_live(tm_n2);
+      if (live_c) classify(s_c, sty - stx);
+      stx = sty, sty = nty, nty = n2ty;
+      s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
+    }
+  }
+  // shading normals: v * rsqrt.approx(|v|^2) (2 ulp) instead of the reference's v / sqrt(|v|^2) -- three IEEE
+  // square roots and nine divisions per shaded sample otherwise; the zero-gradient case gives NaN -> clamp -> 0 in both
+  const f3 normal_o = -normalize3_fast(mk3(gx * rcp_fast(stp.x), gy * rcp_fast(stp.y), gz * rcp_fast(stp.z)));
+  const f3 normal_w = normalize3_fast(xfm_vector(P.wto_t, normal_o));
+  const f3 normal_c = normalize3_fast(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
+  const float cosNL = fabsf(dot3(P.light_dir, normal_w));
+  const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(slog); // light_rgb = 2; 1 - shadow.alpha = 2^slog
+  cC = clamp01(rgb * k_sh) * w; // shaders_raymarching.cu:156-165
+  cG = clamp01(normal_c) * w;
+}
+
 template<bool SKIP, bool POW2, bool OCCS>
 __global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
@@ -171,7 +247,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
-    warp_tile_origin(k, P.rank, P.nranks, P.super_w, px, py);
+    const int tile_slot = warp_tile_origin(P, k, px, py);
+    const long long tile_t0 = clock64();
     const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     const bool inside = ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
@@ -215,105 +292,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             const float4 q0 = lds_f32x4(queue_base + 32u * (unsigned)(lane)), q1 = lds_f32x4(queue_base + 32u * (unsigned)(lane) + 16u);
             const f3 p = mk3(q0.x, q0.y, q0.z);
             const float s = q0.w, w = q1.x;
-            const f3 rgb = color_global<POW2>(P, s);
-            // compute_volume_gradient_object_space (shaders_common.h:195-215): forward differences, step 1/dims
-            f3 stp = P.rdim;
-            if (p.x + stp.x > 1.f) stp.x = -stp.x;
-            if (p.y + stp.y > 1.f) stp.y = -stp.y;
-            if (p.z + stp.z > 1.f) stp.z = -stp.z;
-            const float gx = tex3D<float>(P.tex, p.x + stp.x, p.y, p.z) - s;
-            const float gy = tex3D<float>(P.tex, p.x, p.y + stp.y, p.z) - s;
-            const float gz = tex3D<float>(P.tex, p.x, p.y, p.z + stp.z) - s;
-            c_shaded++;
-            // shadow ray from the sample toward the light (__closesthit__volume_shadow + raymarching_shadow,
-            // shaders_raymarching.cu:205-229,44-85), transmittance accumulated as a sum of logs
-            // Software pipeline, two samples deep: sample positions do not depend on fetched data (fixed t lattice), so
-            // while sample k is classified the fetch of k+1 and the majorant of k+2 are already in flight.
-            float slog = 0.f, stx, st1;
-            if (clip_shadow_p(P, p, stx, st1)) {
-              const float sstep = P.sstep;
-              // All lanes walk the fixed t lattice in lockstep (neighbouring shadow rays then fetch neighbouring texels: letting
-              // each lane run ahead to its next live sample measured 3.60 ms against 2.95 ms); a sample in an empty macrocell
-              // (alpha == 0 exactly, adds 0 to the log sum) costs the cell test only.
-#ifndef B200VR_Q_OCC_BITS
-#define B200VR_Q_OCC_BITS 1
-#endif
-#ifndef B200VR_Q_DEPTH
-#define B200VR_Q_DEPTH 1
-#endif
-              const f3 ph = mk3(__fmaf_rn(p.x, P.cells_per_unit.x, -0.5f), __fmaf_rn(p.y, P.cells_per_unit.y, -0.5f),
-                                __fmaf_rn(p.z, P.cells_per_unit.z, -0.5f)); // ray origin in macrocell units - 1/2
-              auto cell_live = [&](float tm) {
-                if (B200VR_Q_OCC_BITS)
-                  return occ_bit<OCCS>(P, occ_base, pad_index_floor(P, mk3(__fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y),
-                                                                           __fmaf_rn(tm, P.sh_d.z, p.z))));
-                return __ldg(P.maj_pad + pad_index_magic(P, __fmaf_rn(tm, P.sh_dcell.x, ph.x), __fmaf_rn(tm, P.sh_dcell.y, ph.y),
-                                                         __fmaf_rn(tm, P.sh_dcell.z, ph.z))) != 0.f;
-              };
-              auto fetch = [&](float tm) {
-                return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
-              };
-              auto classify = [&](float sv, float dt) {
-                c_shadow++;
-                const float a = alpha_lookup<POW2>(P, apair_base, sv);
-                // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
-                slog = __fmaf_rn(P.base * dt, lg2_fast(fmaxf(1.f - a, 0.f)), slog);
-              };
-#if B200VR_Q_DEPTH == 1
-              // Software pipeline: sample positions do not depend on fetched data (fixed t lattice), so while sample k is
-              // classified the fetch of k+1 and the macrocell test of k+2 are already in flight.
-              // intervals: current [stx, sty], next [sty, nty], the one after [nty, n2ty]
-              // (Measured alternatives on C2: batches of 4/8 independent samples per ray 3.09/3.07 ms, this pipeline 2.95 ms.)
-              float sty = fminf(st1, stx + sstep);
-              const float tm_c = 0.5f * (stx + sty);
-              bool live_c = !SKIP || cell_live(tm_c);
-              float s_c = 0.f;
-              if (live_c && sty > stx) s_c = fetch(tm_c);
-              float nty = fminf(sty + sstep, st1);
-              float tm_n = 0.5f * (sty + nty);
-              bool live_n = !SKIP || cell_live(tm_n);
-#pragma unroll 2
-              while (sty > stx && slog > P.log_ert) {
-                float s_n = 0.f;
-                if (live_n && nty > sty) s_n = fetch(tm_n); // prefetch; unused if the ray ends at this sample
-                const float n2ty = fminf(nty + sstep, st1);
-                const float tm_n2 = 0.5f * (nty + n2ty);
-                const bool live_n2 = !SKIP || cell_live(tm_n2);
-                if (live_c) classify(s_c, sty - stx);
-                stx = sty, sty = nty, nty = n2ty;
-                s_c = s_n, live_c = live_n, live_n = live_n2, tm_n = tm_n2;
-              }
-#else
-              // two fetches in flight per ray: while sample k is classified, k+1 and k+2 are being fetched and the cell test
-              // of k+3 is issued. intervals: [t0, t1_], [t1_, t2], [t2, t3], [t3, t4]
-              float t0 = stx, t1_ = fminf(st1, t0 + sstep), t2 = fminf(st1, t1_ + sstep), t3 = fminf(st1, t2 + sstep);
-              bool live_c = !SKIP || cell_live(0.5f * (t0 + t1_));
-              bool live_n = !SKIP || cell_live(0.5f * (t1_ + t2));
-              bool live_n2 = !SKIP || cell_live(0.5f * (t2 + t3));
-              float s_c = 0.f, s_n = 0.f;
-              if (live_c && t1_ > t0) s_c = fetch(0.5f * (t0 + t1_));
-              if (live_n && t2 > t1_) s_n = fetch(0.5f * (t1_ + t2));
-#pragma unroll 2
-              while (t1_ > t0 && slog > P.log_ert) {
-                float s_n2 = 0.f;
-                if (live_n2 && t3 > t2) s_n2 = fetch(0.5f * (t2 + t3));
-                const float t4 = fminf(st1, t3 + sstep);
-                const bool live_n3 = !SKIP || cell_live(0.5f * (t3 + t4));
-                if (live_c) classify(s_c, t1_ - t0);
-                t0 = t1_, t1_ = t2, t2 = t3, t3 = t4;
-                s_c = s_n, s_n = s_n2, live_c = live_n, live_n = live_n2, live_n2 = live_n3;
-              }
-#endif
-            }
-            // shading normals: v * rsqrt.approx(|v|^2) (2 ulp) instead of the reference's v / sqrt(|v|^2) -- three IEEE
-            // square roots and nine divisions per shaded sample otherwise; the zero-gradient case gives NaN -> clamp -> 0 in both
-            const f3 normal_o = -normalize3_fast(mk3(gx * rcp_fast(stp.x), gy * rcp_fast(stp.y), gz * rcp_fast(stp.z)));
-            const f3 normal_w = normalize3_fast(xfm_vector(P.wto_t, normal_o));
-            const f3 normal_c = normalize3_fast(xfm_vector(P.wtc, normal_w)); // wtc = transpose(inverse(world_to_camera.l))
-            const float cosNL = fabsf(dot3(P.light_dir, normal_w));
-            const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(slog); // light_rgb = 2; 1 - shadow.alpha = 2^slog
-            cC = clamp01(rgb * k_sh) * w; // shaders_raymarching.cu:156-165
-            cG = clamp01(normal_c) * w;
+            shade_task<SKIP, POW2, OCCS>(P, apair_base, occ_base, p, s, w, c_shaded, c_shadow, cC, cG);
           }
           __syncwarp();
           if (lane < n) {
@@ -454,6 +433,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
         g[2] = G.z;
       }
     }
+    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
   }
 
   // executed-sample counters: one atomic set per warp

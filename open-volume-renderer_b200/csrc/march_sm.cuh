@@ -188,7 +188,8 @@ raymarch_sm_kernel(const __grid_constant__ LaunchParams P)
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
-    warp_tile_origin(k, P.rank, P.nranks, P.super_w, px, py);
+    const int tile_slot = warp_tile_origin(P, k, px, py);
+    const long long tile_t0 = clock64();
     const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     const bool inside = ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
@@ -400,6 +401,7 @@ raymarch_sm_kernel(const __grid_constant__ LaunchParams P)
     n_shadow += __reduce_add_sync(0xffffffffu, c_shadow);
     n_gradient += __reduce_add_sync(0xffffffffu, 3u * c_shaded);
     n_rays += __reduce_add_sync(0xffffffffu, c_rays);
+    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
   }
 
   if (lane == 0) { // one atomic set per warp

@@ -126,7 +126,8 @@ pathtrace_kernel(const __grid_constant__ LaunchParams P)
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
-    warp_tile_origin(k, P.rank, P.nranks, P.super_w, px, py);
+    const int tile_slot = warp_tile_origin(P, k, px, py);
+    const long long tile_t0 = clock64();
     const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     unsigned int samples = 0, rays = 0;
     if (ix < P.width && iy < P.height) {
@@ -197,6 +198,7 @@ pathtrace_kernel(const __grid_constant__ LaunchParams P)
     }
     n_delta += __reduce_add_sync(0xffffffffu, samples);
     n_rays += __reduce_add_sync(0xffffffffu, rays);
+    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
   }
   if (lane == 0) {
     atomicAdd(&P.counters->delta_samples, n_delta);

@@ -198,7 +198,8 @@ raymarch_kernel(const __grid_constant__ LaunchParams P)
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
     int px, py;
-    warp_tile_origin(k, P.rank, P.nranks, P.super_w, px, py);
+    const int tile_slot = warp_tile_origin(P, k, px, py);
+    const long long tile_t0 = clock64();
     const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     RayStats st = { 0u, 0u, 0u };
     unsigned int rays = 0;
@@ -264,6 +265,7 @@ raymarch_kernel(const __grid_constant__ LaunchParams P)
     n_shadow += __reduce_add_sync(0xffffffffu, st.shadow);
     n_gradient += __reduce_add_sync(0xffffffffu, st.gradient);
     n_rays += __reduce_add_sync(0xffffffffu, rays);
+    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
   }
 
   if (lane == 0) { // one atomic set per warp

@@ -222,12 +222,25 @@ def test_path_tracing_matches_oracle_statistically():
 
 
 def test_sort_first_tiles_reassemble_bit_exact():
+    """Partitioned launches use the work-sharing ring kernel (integer per-pixel sums: independent of who shades what and in
+    which order), the undivided frame the queue kernel (float sums in march order). Against the ring kernel on the whole
+    frame the reassembled tiles are bit-identical; against the queue kernel they differ by summation rounding only."""
     import torch
     W, H = 200, 120
     sc = S.noise_scene(48, tf="sparse", camera="oblique")
     r = make_renderer(sc, W, H)
     r.render()
-    full = r.download()[0]
+    full_q = r.download()[0].copy()
+    os.environ["B200VR_KERNEL"] = "ring"
+    try:
+        r.render()
+        full = r.download()[0].copy()
+        r.render()
+        assert np.array_equal(r.download()[0].view(np.uint32), full.view(np.uint32))   # deterministic run to run
+    finally:
+        del os.environ["B200VR_KERNEL"]
+    # 30-bit fixed-point contributions, then C / A: pixels with a tiny opacity amplify the 2^-31 quantisation
+    assert max_abs(full, full_q) < 1e-4
     L = capi.lib()
     nranks = 3
     slices = []
@@ -245,6 +258,30 @@ def test_sort_first_tiles_reassemble_bit_exact():
     got = disp.download()[0]
     assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
     r.close(), disp.close()
+
+
+@pytest.mark.parametrize("spp,accumulate", [(1, False), (3, True)])
+def test_ring_kernel_matches_queue_kernel(spp, accumulate):
+    """Same frames through both shading kernels: samples, counters and images agree (images up to summation rounding),
+    also with several samples per pixel and progressive accumulation (host-side sample loop + resolve_kernel)."""
+    W, H = 192, 108
+    sc = S.noise_scene(64, tf="sparse", camera="oblique")
+    frames = {}
+    for kern in ("q", "ring"):
+        os.environ["B200VR_KERNEL"] = kern
+        try:
+            r = make_renderer(sc, W, H, spp=spp, accumulate=accumulate)
+            for _ in range(3 if accumulate else 1):
+                r.render()
+            frames[kern] = (r.download(), dict(r.last_stats))
+            r.close()
+        finally:
+            del os.environ["B200VR_KERNEL"]
+    (a_rgba, a_grad), a_st = frames["q"]
+    (b_rgba, b_grad), b_st = frames["ring"]
+    for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
+        assert a_st[k] == b_st[k], k
+    assert max_abs(a_rgba, b_rgba) < 1e-4 and max_abs(a_grad, b_grad) < 1e-4   # 2^-31 quantisation / tiny pixel opacity
 
 
 def test_sort_last_bricks_composite_to_the_full_image():
