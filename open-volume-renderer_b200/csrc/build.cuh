@@ -200,6 +200,11 @@ __global__ void tile_order_kernel(const unsigned int* __restrict__ cost, int n_o
     const int s = rank + m * nranks;
     const float dx = (float)(s % super_w) + 0.5f - 0.5f * (float)super_w, dy = (float)(s / super_w) + 0.5f - 0.5f * (float)super_h;
     const unsigned int d = (unsigned int)fminf(4.f * (2.f * dx * 2.f * dx + dy * dy), 1048575.f); // tiles are 64 x 32 pixels
+    if (mode == 3) { // Z-order over the super-tile grid: the tiles in flight form a compact block of the image
+      unsigned int x = (unsigned int)(s % super_w), y = (unsigned int)(s / super_w), z = 0u;
+      for (int b = 0; b < 10; b++) z |= ((x >> b) & 1u) << (2 * b) | ((y >> b) & 1u) << (2 * b + 1);
+      return (unsigned long long)(1048575u - z);
+    }
     return ((unsigned long long)(mode == 2 ? cost[m] : 0u) << 20) | (unsigned long long)(1048575u - d);
   };
   const unsigned long long ki = key(i);

@@ -28,7 +28,10 @@ constexpr int Q_SLOT_FLOATS = 8;               // task: p.xyz, s, w, -, -, -   r
 // dynamic shared memory: [alpha pairs (n_alpha + 1) x float2][macrocell occupancy bits][task queues, one per warp]
 // (the alpha pairs sit at offset 0 so that the hot lookup is a plain LDS [i * 8 + base]; the colour table is read once
 // per shaded sample and stays in global memory / L1)
-constexpr int Q_OCC_SMEM_WORDS = 3072; // occupancy bit masks up to 12 KB (padded grids up to 46^3 cells) are staged per CTA
+#ifndef B200VR_Q_OCC_SMEM_WORDS
+#define B200VR_Q_OCC_SMEM_WORDS 3072
+#endif
+constexpr int Q_OCC_SMEM_WORDS = B200VR_Q_OCC_SMEM_WORDS; // occupancy bit masks up to 12 KB (padded grids up to 46^3 cells) are staged per CTA
 __host__ __device__ __forceinline__ size_t q_alpha_bytes(int n_alpha) { return (sizeof(float2) * (size_t)(n_alpha + 1) + 15) & ~(size_t)15; }
 __host__ __device__ __forceinline__ size_t q_occ_bytes(int occ_words) { return (sizeof(unsigned int) * (size_t)occ_words + 15) & ~(size_t)15; }
 __host__ __device__ __forceinline__ size_t q_queue_bytes() { return sizeof(float) * Q_SLOT_FLOATS * Q_SLOTS * (Q_THREADS / 32); }
