@@ -398,7 +398,7 @@ def main():
     elif args.sampler == "manual":
         kernel_name = "raymarch_kernel"
     else:   # pick_kernel in csrc/b200vr.cu
-        kernel_name = "raymarch_q_kernel" if wl["shading"] == "ref" else "raymarch_sm_kernel"
+        kernel_name = ("raymarch_ring_kernel" if world > 1 else "raymarch_q_kernel") if wl["shading"] == "ref" else "raymarch_ns_kernel"
     # dram__bytes_read.sum + dram__bytes_write.sum of that kernel for this workload, from the committed `ncu --set full` capture
     traffic, traffic_src = None, None
     try:

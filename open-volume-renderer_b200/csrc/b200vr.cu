@@ -10,6 +10,7 @@
 #include "march_sm.cuh"
 #include "march_q.cuh"
 #include "march_ring.cuh"
+#include "march_ns.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -672,6 +673,16 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       k.smem = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0) + q_queue_bytes();
       return k;
     }
+    if (p.shading == B200VR_SHADING_NONE && !sm) { // lean classification + compositing kernel (march_ns.cuh)
+      const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
+      const bool occs = p.skip_empty && q_occ_in_smem(h->occ_words);
+      if (!p.skip_empty) k.fn = pow2 ? raymarch_ns_kernel<false, true, false> : raymarch_ns_kernel<false, false, false>;
+      else if (occs) k.fn = pow2 ? raymarch_ns_kernel<true, true, true> : raymarch_ns_kernel<true, false, true>;
+      else k.fn = pow2 ? raymarch_ns_kernel<true, true, false> : raymarch_ns_kernel<true, false, false>;
+      k.threads = NS_THREADS;
+      k.smem = ns_shared_bytes(h->n_color, h->n_alpha, occs ? h->occ_words : 0);
+      return k;
+    }
     k.smem = tf_fast_shared_bytes(h->n_color, h->n_alpha);
     if (p.shading == B200VR_SHADING_REF)
       k.fn = p.skip_empty ? raymarch_sm_kernel<SHADING_REF, true> : raymarch_sm_kernel<SHADING_REF, false>;
@@ -815,7 +826,8 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   LaunchParams P;
   fill_launch_params(h, P);
   if (h->has_lattice && !(h->prm.mode == B200VR_MODE_RAYMARCH && h->prm.shading == B200VR_SHADING_NONE &&
-                           h->prm.sampler == B200VR_SAMPLER_TEX3D && !std::getenv("B200VR_KERNEL")))
+                           h->prm.sampler == B200VR_SAMPLER_TEX3D &&
+                           (!std::getenv("B200VR_KERNEL") || std::strcmp(std::getenv("B200VR_KERNEL"), "sm") == 0)))
     return fail(h, B200VR_ESTATE, "render: a brick (sort-last) needs ray marching with SHADING_NONE and the tex3D sampler: "
                                   "shadow rays and random walks leave the brick");
   const KernelChoice kc = pick_kernel(h);
