@@ -441,3 +441,56 @@ def test_multi_gpu_paths_over_nccl():
     res = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("{")][-1])
     print(res)
     assert res["sort_first_bit_identical"] and res["sort_last_ok"]
+
+
+EDGE_CASES = [
+    # name, dims, TF resolution, spacing, shading, forced kernel
+    ("ragged-dims-ref", (70, 45, 33), 1024, (1.0, 1.0, 1.0), capi.SHADING_REF, None),
+    ("ragged-dims-none", (70, 45, 33), 1024, (1.0, 1.0, 1.0), capi.SHADING_NONE, None),
+    ("tf-100-entries-ref", (48, 48, 48), 100, (1.0, 1.0, 1.0), capi.SHADING_REF, None),       # generic (non 2^m) table path
+    ("tf-100-entries-none", (48, 48, 48), 100, (1.0, 1.0, 1.0), capi.SHADING_NONE, None),
+    ("anisotropic-ref", (40, 64, 24), 256, (1.0, 0.5, 2.0), capi.SHADING_REF, None),
+    ("ring-kernel-ref", (64, 40, 56), 1024, (1.0, 1.0, 1.0), capi.SHADING_REF, "ring"),
+]
+
+
+@pytest.mark.parametrize("case", EDGE_CASES, ids=[c[0] for c in EDGE_CASES])
+def test_raymarch_edge_cases_match_oracle(case):
+    name, dims, n_tf, spacing, shading, kern = case
+    W, H = 176, 112
+    sc = S.noise_scene(max(dims), tf="sparse", camera="oblique", dims=dims)
+    sc.tfn = S.make_tfn("sparse", n=n_tf, value_range=(1.0, -1.0))
+    sc.volume.grid_spacing = spacing
+    ext = np.array(dims, np.float64) * np.array(spacing)
+    sc.camera = ovr_b200.Camera(tuple(ext / 2 + ext.max() * np.array([1.0, 0.7, 1.4])), tuple(ext / 2), (0.0, 1.0, 0.0), 45.0)
+    if kern:
+        os.environ["B200VR_KERNEL"] = kern
+    try:
+        r = make_renderer(sc, W, H, shading=shading)
+        r.render()
+        rgba, grad = r.download()
+    finally:
+        if kern:
+            del os.environ["B200VR_KERNEL"]
+    d = oracle_desc(sc, W, H, shading=shading, volume=device_volume(r, dims))
+    o_rgba, o_grad, o_cnt = pyoracle.OracleScene(d, skip_empty=True).render_march()
+    assert (o_rgba[..., 3] > 0).mean() > 0.03
+    e, p, eg = max_abs(rgba, o_rgba), psnr(rgba, o_rgba), max_abs(grad, o_grad)
+    print(f"{name}: max-abs {e:.2e} psnr {p:.1f} dB grad max-abs {eg:.2e}")
+    assert e <= TOL and p >= 45.0 and eg <= 4 * TOL
+    assert r.last_stats["rays"] == W * H
+    r.close()
+
+
+def test_all_transparent_transfer_function_gives_an_empty_frame():
+    """Nothing to composite: every macrocell is empty, every ray skips through, the frame is exactly zero."""
+    W, H = 128, 80
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    sc.tfn = ovr_b200.TransferFunction(sc.tfn.color, np.zeros(256, np.float32), (1.0, -1.0))
+    for shading in (capi.SHADING_REF, capi.SHADING_NONE):
+        r = make_renderer(sc, W, H, shading=shading)
+        r.render()
+        rgba, grad = r.download()
+        assert not rgba.any() and not grad.any()
+        assert r.last_stats["primary_samples"] == 0 and r.last_stats["shadow_samples"] == 0 and r.last_stats["rays"] == W * H
+        r.close()
