@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--workload", default="C2")
     ap.add_argument("--sampler", default="tex3d", choices=["tex3d", "manual"])
     ap.add_argument("--no-skip", action="store_true")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="sort-last compositing: fused peer-memory blend or NCCL send/recv")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-stride", type=int, default=0, help="pixel stride of the CPU sample (0 = auto)")
     return ap.parse_args()
@@ -245,19 +246,25 @@ def run_b200(args):
 
     if sortlast:
         D.setup_brick_renderer(r, brick)
-        swap = D.SortLast(rank, world, full_scene.volume.dims, W * H, handle_renderer=r)
+        # exchange fused into the blend over NVLink peer mappings (--exchange nccl: the send/recv schedule)
+        p2p = world > 1 and args.exchange == "p2p"
+        swap = (D.SortLastP2P(rank, world, full_scene.volume.dims, W * H, r) if p2p else
+                D.SortLast(rank, world, full_scene.volume.dims, W * H, handle_renderer=r))
 
         def step():
             eye = r.params["camera"].get().frm   # visibility order follows the committed camera
             # all pixels against this rank's brick -> premultiplied layer; binary swap; display rank un-premultiplies
             r.render()
             launches[0] += r.last_stats["kernel_launches"]
-            img = D.frame_tensor(r)
             n0 = swap.launches
-            out = swap.composite(img, eye)
+            if p2p:
+                out = swap.composite(eye)
+            else:
+                out = swap.composite(D.frame_tensor(r), eye)
+                out = out.data_ptr() if out is not None else None
             launches[0] += swap.launches - n0
             if out is not None:
-                r._ck(L.b200vr_finalize_premultiplied(r.handle, C.c_void_p(out.data_ptr()), W * H))
+                r._ck(L.b200vr_finalize_premultiplied(r.handle, C.c_void_p(out), W * H))
                 launches[0] += 1
             return r.last_stats
     else:
@@ -420,7 +427,7 @@ def main():
             "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": workload_name(args, wl), "sampler": args.sampler, "skip_empty": not args.no_skip,
-                       "parallelism": (f"sort-last x{world}: one {n}^3 brick per GPU, binary swap over NCCL" if wl.get("sortlast") else
+                       "parallelism": (f"sort-last x{world}: one {n}^3 brick per GPU, binary swap, " + ("blend reads the partner over NVLink peer memory" if args.exchange == "p2p" else "NCCL send/recv") if wl.get("sortlast") else
                                        f"sort-first x{world}" if world > 1 else "1 GPU"),
                        "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                        "samples_per_frame": ctx["samples"] / args.steps, "fetches_per_frame": ctx["fetches"] / args.steps},

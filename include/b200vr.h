@@ -166,6 +166,17 @@ int b200vr_unpack_tiles(b200vr_t* h, const float* slice_dev, int rank, int nrank
 int b200vr_composite_over(b200vr_t* h, const float* front_dev, const float* back_dev, float* out_dev,
                           int64_t n_pixels);
 int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64_t n_pixels);
+/* fused sort-last exchange over NVLink (one process per GPU): a rank exports its two rgba frame buffers as CUDA IPC handles
+ * (64 bytes each, sent to the peers by any means), opens the peers' handles and passes the resulting device pointers as
+ * `back_dev` / `front_dev` of b200vr_composite_over or as `src_dev` of b200vr_copy_device: the blend then reads the
+ * partner's half image straight through the peer mapping, no staging copy, no send/recv. Handles stay valid until the next
+ * b200vr_resize of the exporting handle. On a caller-provided stream (b200vr_set_stream) composite / finalize / copy are
+ * stream-ordered and do not block the host. */
+int b200vr_ipc_export_frame(b200vr_t* h, int buffer /* 0 | 1 */, unsigned char handle_out[64]);
+int b200vr_ipc_open(b200vr_t* h, const unsigned char handle[64], void** dev_ptr_out);
+int b200vr_ipc_close(b200vr_t* h, void* dev_ptr);
+int b200vr_current_buffer(b200vr_t* h); /* index of the buffer b200vr_map returns */
+int b200vr_copy_device(b200vr_t* h, void* dst_dev, const void* src_dev, int64_t bytes);
 
 #ifdef __cplusplus
 }

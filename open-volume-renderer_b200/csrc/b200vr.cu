@@ -1027,7 +1027,52 @@ extern "C" int b200vr_composite_over(b200vr_t* h, const float* front_dev, const 
   composite_over_kernel<<<grid_for((size_t)n_pixels, 256, h->sm_count), 256, 0, h->stream>>>(
     (const float4*)front_dev, (const float4*)back_dev, (float4*)out_dev, (size_t)n_pixels);
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(h->stream));
+  if (h->stream == h->own_stream) CK(cudaStreamSynchronize(h->stream)); // on a caller's stream the call is stream-ordered
+  return B200VR_OK;
+}
+
+// ---- peer access for the fused sort-last exchange: one process per GPU, frames shared through CUDA IPC ----
+extern "C" int b200vr_ipc_export_frame(b200vr_t* h, int buffer, unsigned char handle_out[64])
+{
+  if (!h || !handle_out || buffer < 0 || buffer > 1) return B200VR_EINVAL;
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "ipc_export_frame: framebuffer size not set");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  CK(cudaSetDevice(h->device));
+  cudaIpcMemHandle_t mh;
+  CK(cudaIpcGetMemHandle(&mh, h->rgba[buffer]));
+  std::memcpy(handle_out, &mh, 64);
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_ipc_open(b200vr_t* h, const unsigned char handle[64], void** dev_ptr_out)
+{
+  if (!h || !handle || !dev_ptr_out) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  cudaIpcMemHandle_t mh;
+  std::memcpy(&mh, handle, 64);
+  CK(cudaIpcOpenMemHandle(dev_ptr_out, mh, cudaIpcMemLazyEnablePeerAccess));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_ipc_close(b200vr_t* h, void* dev_ptr)
+{
+  if (!h || !dev_ptr) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaIpcCloseMemHandle(dev_ptr));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_current_buffer(b200vr_t* h)
+{
+  return h ? h->current : -1;
+}
+
+extern "C" int b200vr_copy_device(b200vr_t* h, void* dst_dev, const void* src_dev, int64_t bytes)
+{
+  if (!h || !dst_dev || !src_dev || bytes < 0) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(dst_dev, src_dev, (size_t)bytes, cudaMemcpyDeviceToDevice, h->stream)); // UVA: src may be a peer's memory
+  if (h->stream == h->own_stream) CK(cudaStreamSynchronize(h->stream));
   return B200VR_OK;
 }
 
@@ -1038,7 +1083,7 @@ extern "C" int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64
   CK(cudaSetDevice(h->device));
   finalize_premultiplied_kernel<<<grid_for((size_t)n_pixels, 256, h->sm_count), 256, 0, h->stream>>>((float4*)rgba_dev, (size_t)n_pixels);
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(h->stream));
+  if (h->stream == h->own_stream) CK(cudaStreamSynchronize(h->stream));
   return B200VR_OK;
 }
 

@@ -318,3 +318,69 @@ def frame_tensor(renderer):
     import torch
     fb = renderer.mapframe()
     return torch.as_tensor(_DevicePtr(fb.rgba[0], fb.rgba[1] // 4), device="cuda")
+
+
+class SortLastP2P:
+    """Binary swap with the exchange FUSED into the blend: every rank maps its peers' frame buffers (CUDA IPC, NVLink peer
+    access) and `b200vr_composite_over` reads the partner's half image straight out of the partner's memory while it blends
+    -- no send/recv, no staging buffer. Round b: rank keeps one half of its current pixel range and writes
+    keep = front OVER back there, `back` or `front` being the partner's pixels of the same range; the partner does the
+    same on the other half, so nobody writes what somebody else reads within a round. Rounds, the final pull of the N
+    strips by the display rank and the next frame's render are separated by barriers (stream-ordered: the NCCL barrier is
+    enqueued behind the blends on each rank's stream). All calls are on the caller's stream (b200vr_set_stream)."""
+
+    def __init__(self, rank, world, dims, n_pixels, renderer, group=None, dst=0, grid_spacing=(1.0, 1.0, 1.0),
+                 grid_origin=(0.0, 0.0, 0.0), align=32):
+        import torch.distributed as dist
+        from . import _capi as capi
+        self.rank, self.world, self.dims, self.n = rank, world, tuple(dims), n_pixels
+        self.r, self.group, self.dst = renderer, group, dst
+        self.L = capi.lib()
+        self.kw = dict(grid_spacing=grid_spacing, grid_origin=grid_origin)
+        self.plan, self.mine = binary_swap_plan(rank, world, n_pixels, align)
+        self.ranges = final_ranges(world, n_pixels, align)
+        self.launches = 0
+        # exchange the IPC handles of both frame buffers, open everybody else's
+        mine = []
+        for b in (0, 1):
+            buf = (C.c_ubyte * 64)()
+            renderer._ck(self.L.b200vr_ipc_export_frame(renderer.handle, b, buf))
+            mine.append(bytes(buf))
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine, group=group)
+        self.peer = {}          # (rank, buffer) -> device pointer in THIS process
+        for k in range(world):
+            if k == rank:
+                continue
+            for b in (0, 1):
+                p = C.c_void_p()
+                h = (C.c_ubyte * 64).from_buffer_copy(everyone[k][b])
+                renderer._ck(self.L.b200vr_ipc_open(renderer.handle, h, C.byref(p)))
+                self.peer[(k, b)] = p.value
+
+    def close(self):
+        for p in self.peer.values():
+            self.L.b200vr_ipc_close(self.r.handle, C.c_void_p(p))
+        self.peer = {}
+
+    def composite(self, eye):
+        """In place on the renderer's current frame buffer; after the call rank `dst` holds the premultiplied frame."""
+        import torch.distributed as dist
+        r, L = self.r, self.L
+        cur = int(L.b200vr_current_buffer(r.handle))
+        own = r.mapframe().rgba[0]
+        for b, (partner, keep, _send) in enumerate(self.plan):
+            dist.barrier(group=self.group)   # the partner's pixels of this round are final (render / previous round)
+            off, n = keep[0] * 16, keep[1] - keep[0]
+            mine, theirs = own + off, self.peer[(partner, cur)] + off
+            front, back = (mine, theirs) if in_front(eye, self.dims, self.world, b, self.rank, **self.kw) else (theirs, mine)
+            r._ck(L.b200vr_composite_over(r.handle, C.c_void_p(front), C.c_void_p(back), C.c_void_p(mine), n))
+            self.launches += 1
+        dist.barrier(group=self.group)
+        if self.rank == self.dst:            # pull the other ranks' strips over NVLink
+            for k, (lo, hi) in enumerate(self.ranges):
+                if k != self.rank and hi > lo:
+                    r._ck(L.b200vr_copy_device(r.handle, C.c_void_p(own + lo * 16), C.c_void_p(self.peer[(k, cur)] + lo * 16), (hi - lo) * 16))
+                    self.launches += 1
+        dist.barrier(group=self.group)       # nobody renders the next frame into a buffer that is still being read
+        return own if self.rank == self.dst else None

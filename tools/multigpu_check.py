@@ -1,8 +1,8 @@
 """Run under torchrun with N >= 2 GPUs (one rank per GPU, NCCL): checks both multi-GPU paths against a single-GPU render
 of the same scene on rank 0 and prints one JSON line.
 
-  sort-first  gathered frame must be BIT-IDENTICAL to the single-GPU frame of the same (ring) kernel, and within 1e-4 of the
-              queue kernel's frame (summation order / fixed-point rounding)
+  sort-first  gathered frame must be BIT-IDENTICAL to the single-GPU frame of the same (ring) kernel, and within 1e-3 of the
+              queue kernel's frame (2^-31 fixed-point contributions, amplified by 1 / A at nearly transparent pixels)
   sort-last   N brick volumes (own voxels + ghosts), global sample lattice, binary swap over NCCL, un-premultiplied on rank 0:
               max-abs <= 1/255 and PSNR >= 45 dB against the single-GPU render of the whole volume
 
@@ -84,12 +84,24 @@ def main():
         out["sort_last_psnr_db"] = float("inf") if mse == 0 else float(10 * np.log10(1.0 / mse))
         out["sort_last_ok"] = bool(err <= 1.0 / 255.0 and out["sort_last_psnr_db"] >= 45.0)
         out["composite_launches"] = swap.launches
+    # the same frame through the fused peer-memory exchange must be bit-identical to the NCCL schedule
+    b.render()
+    p2p = D.SortLastP2P(rank, world, full.volume.dims, W * H, b)
+    ptr = p2p.composite(full.camera.frm)
+    if rank == 0:
+        b._ck(L.b200vr_finalize_premultiplied(b.handle, C.c_void_p(ptr), W * H))
+        torch.cuda.synchronize()
+        got2 = b.download(want_grad=False)[0]
+        out["sort_last_p2p_equals_nccl"] = bool(np.array_equal(got2.view(np.uint32), got.view(np.uint32)))
+    dist.barrier()
+    p2p.close()
     b.close()
     dist.barrier()
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
-    if rank == 0 and not (out["sort_first_bit_identical"] and out["sort_first_vs_queue_kernel_max_abs"] < 1e-4 and out["sort_last_ok"]):
+    if rank == 0 and not (out["sort_first_bit_identical"] and out["sort_first_vs_queue_kernel_max_abs"] < 1e-3 and out["sort_last_ok"] and
+                          out["sort_last_p2p_equals_nccl"]):
         sys.exit(1)
 
 
