@@ -415,7 +415,9 @@ def main():
             traffic, traffic_src = t["dram_bytes_per_launch"], t["source"]
     except (OSError, ValueError):
         pass
-    roofline = {"bound": "tex", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if peak else None,
+    hbm_frac_alg = hbm_ach / pk["hbm_gbs"]
+    roofline = {"achieved_tex": ach / peak if peak else None, "achieved_hbm": hbm_frac_alg,   # fractions of both roofs
+                "bound": "tex", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if peak else None,
                 "traffic": traffic, "traffic_source": traffic_src, "kernel": kernel_name,
                 "note": "texture/L1 sampling roofline: 32 B x executed trilinear fetches / mean kernel time (CUDA events on the launch "
                         "stream); peak = best b200vr_bench_fetch rate x 32 B measured in this run",
