@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--workload", default="C2")
     ap.add_argument("--sampler", default="tex3d", choices=["tex3d", "manual"])
     ap.add_argument("--no-skip", action="store_true")
-    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="sort-last compositing: fused peer-memory blend or NCCL send/recv")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="multi-GPU exchange: fused over NVLink peer memory (sort-first: stores into rank 0's frame; sort-last: blend reads the partner) or NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-stride", type=int, default=0, help="pixel stride of the CPU sample (0 = auto)")
     return ap.parse_args()
@@ -269,7 +269,8 @@ def run_b200(args):
             return r.last_stats
     else:
         # sort-first: own tiles rendered, dense slices gathered on rank 0 (one exchange step)
-        sf = D.SortFirst(r, rank, world)
+        # --exchange p2p: tiles rendered straight into rank 0's frame over NVLink peer memory; nccl: pack + gather + unpack
+        sf = D.SortFirstP2P(r, rank, world) if (world > 1 and args.exchange == "p2p") else D.SortFirst(r, rank, world)
 
         def step():
             n0 = sf.launches
@@ -430,7 +431,8 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(args, wl), "sampler": args.sampler, "skip_empty": not args.no_skip,
                        "parallelism": (f"sort-last x{world}: one {n}^3 brick per GPU, binary swap, " + ("blend reads the partner over NVLink peer memory" if args.exchange == "p2p" else "NCCL send/recv") if wl.get("sortlast") else
-                                       f"sort-first x{world}" if world > 1 else "1 GPU"),
+                                       f"sort-first x{world}, " + ("tiles stored straight into rank 0's frame over NVLink peer memory" if args.exchange == "p2p"
+                                                                   else "NCCL gather of tile slices") if world > 1 else "1 GPU"),
                        "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                        "samples_per_frame": ctx["samples"] / args.steps, "fetches_per_frame": ctx["fetches"] / args.steps},
             "clocks": ctx["clk"], "e2e": e2e, "gpu_launches": ctx["gpu_launches"], "roofline": roofline}

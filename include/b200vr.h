@@ -172,10 +172,14 @@ int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64_t n_pixels
  * partner's half image straight through the peer mapping, no staging copy, no send/recv. Handles stay valid until the next
  * b200vr_resize of the exporting handle. On a caller-provided stream (b200vr_set_stream) composite / finalize / copy are
  * stream-ordered and do not block the host. */
-int b200vr_ipc_export_frame(b200vr_t* h, int buffer /* 0 | 1 */, unsigned char handle_out[64]);
+int b200vr_ipc_export_frame(b200vr_t* h, int buffer /* 0 | 1: rgba, 2 | 3: grad */, unsigned char handle_out[64]);
 int b200vr_ipc_open(b200vr_t* h, const unsigned char handle[64], void** dev_ptr_out);
 int b200vr_ipc_close(b200vr_t* h, void* dev_ptr);
 int b200vr_current_buffer(b200vr_t* h); /* index of the buffer b200vr_map returns */
+/* fused sort-first exchange: render the owned tiles straight into these buffers (W*H float4 and W*H*3 float, normally the
+ * display rank's frame opened with b200vr_ipc_open) -- the kernel's own pixel stores are the transfer, there is no pack /
+ * gather / unpack step. Both NULL: back to the handle's own double buffer. */
+int b200vr_set_frame_target(b200vr_t* h, float* rgba_dev_or_null, float* grad_dev_or_null);
 int b200vr_copy_device(b200vr_t* h, void* dst_dev, const void* src_dev, int64_t bytes);
 
 #ifdef __cplusplus

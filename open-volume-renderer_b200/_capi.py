@@ -73,6 +73,7 @@ SYMBOLS = {
     "b200vr_ipc_open": (C.c_int, [_P, _P, _P]),
     "b200vr_ipc_close": (C.c_int, [_P, _P]),
     "b200vr_current_buffer": (C.c_int, [_P]),
+    "b200vr_set_frame_target": (C.c_int, [_P, _P, _P]),
     "b200vr_copy_device": (C.c_int, [_P, _P, _P, C.c_int64]),
     "b200vr_tile_slice_floats": (C.c_int64, [_P, C.c_int, C.c_int]),
     "b200vr_pack_tiles": (C.c_int, [_P, _P]),

@@ -82,6 +82,8 @@ struct b200vr {
   int* tile_order = nullptr;
   int tile_slots = 0;      // allocated slots (super tiles of the whole image)
   int cost_cur = 0;        // tile_cost[cost_cur] is written by the next launch, tile_cost[cost_cur ^ 1] orders it
+  float4* target_rgba = nullptr; // sort-first over peer memory: render into these buffers (the display rank's) instead of own
+  float* target_grad = nullptr;
   bool cost_valid = false; // false: no history for this image size / partition -> centre-out order
   // deferred-shading ring of the ring kernel (march_ring.cuh), allocated on first use
   unsigned int* ring_ctrl = nullptr;
@@ -783,8 +785,8 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.wto_t = transposed(P.wto.l);
   P.light_ambient = h->prm.light_ambient;
   P.max_num_scatters = h->prm.max_num_scatters;
-  P.rgba = h->rgba[h->current];
-  P.grad = h->grad[h->current];
+  P.rgba = h->target_rgba ? h->target_rgba : h->rgba[h->current];
+  P.grad = h->target_grad ? h->target_grad : h->grad[h->current];
   P.accum = h->accum;
   P.width = h->width, P.height = h->height;
   P.rw = 1.f / (float)h->width, P.rh = 1.f / (float)h->height;
@@ -1034,12 +1036,12 @@ extern "C" int b200vr_composite_over(b200vr_t* h, const float* front_dev, const 
 // ---- peer access for the fused sort-last exchange: one process per GPU, frames shared through CUDA IPC ----
 extern "C" int b200vr_ipc_export_frame(b200vr_t* h, int buffer, unsigned char handle_out[64])
 {
-  if (!h || !handle_out || buffer < 0 || buffer > 1) return B200VR_EINVAL;
+  if (!h || !handle_out || buffer < 0 || buffer > 3) return B200VR_EINVAL;
   if (h->width <= 0) return fail(h, B200VR_ESTATE, "ipc_export_frame: framebuffer size not set");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
   CK(cudaSetDevice(h->device));
   cudaIpcMemHandle_t mh;
-  CK(cudaIpcGetMemHandle(&mh, h->rgba[buffer]));
+  CK(cudaIpcGetMemHandle(&mh, buffer < 2 ? (void*)h->rgba[buffer] : (void*)h->grad[buffer - 2]));
   std::memcpy(handle_out, &mh, 64);
   return B200VR_OK;
 }
@@ -1059,6 +1061,15 @@ extern "C" int b200vr_ipc_close(b200vr_t* h, void* dev_ptr)
   if (!h || !dev_ptr) return B200VR_EINVAL;
   CK(cudaSetDevice(h->device));
   CK(cudaIpcCloseMemHandle(dev_ptr));
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_frame_target(b200vr_t* h, float* rgba_dev, float* grad_dev)
+{
+  if (!h || ((rgba_dev == nullptr) != (grad_dev == nullptr))) return B200VR_EINVAL;
+  h->target_rgba = (float4*)rgba_dev;
+  h->target_grad = grad_dev;
+  h->reset = true;
   return B200VR_OK;
 }
 

@@ -394,3 +394,56 @@ class SortLastP2P:
                     self.launches += 1
         self._barrier()       # nobody renders the next frame into a buffer that is still being read
         return own if self.rank == self.dst else None
+
+
+class SortFirstP2P:
+    """Sort-first with the exchange fused into the render kernel: every rank opens the display rank's frame buffers (CUDA
+    IPC, NVLink peer access) and renders its tiles STRAIGHT INTO THEM (b200vr_set_frame_target) -- the kernel's pixel stores
+    are the transfer; there is no pack / gather / unpack. One stream-ordered one-word all-reduce per frame tells the
+    display rank that all tiles have landed. Ranks must call swap() in lockstep (they share the display rank's buffer index)."""
+
+    def __init__(self, renderer, rank, world, dst=0, group=None):
+        import torch
+        import torch.distributed as dist
+        from . import _capi as capi
+        self.r, self.rank, self.world, self.dst, self.group = renderer, rank, world, dst, group
+        self.L = capi.lib()
+        renderer._ck(self.L.b200vr_set_tile_partition(renderer.handle, rank, world))
+        self.launches = 0
+        self._tok = torch.zeros(1, dtype=torch.float32, device="cuda") if world > 1 else None
+        self.remote = {}
+        if world > 1:
+            handles = [None]
+            if rank == dst:
+                hs = []
+                for b in range(4):
+                    buf = (C.c_ubyte * 64)()
+                    renderer._ck(self.L.b200vr_ipc_export_frame(renderer.handle, b, buf))
+                    hs.append(bytes(buf))
+                handles = [hs]
+            dist.broadcast_object_list(handles, src=dst, group=group)
+            if rank != dst:
+                for b in range(4):
+                    p = C.c_void_p()
+                    h = (C.c_ubyte * 64).from_buffer_copy(handles[0][b])
+                    renderer._ck(self.L.b200vr_ipc_open(renderer.handle, h, C.byref(p)))
+                    self.remote[b] = p.value
+
+    def close(self):
+        if self.remote:
+            self.r._ck(self.L.b200vr_set_frame_target(self.r.handle, None, None))
+            for p in self.remote.values():
+                self.L.b200vr_ipc_close(self.r.handle, C.c_void_p(p))
+            self.remote = {}
+
+    def step(self):
+        import torch.distributed as dist
+        r, L = self.r, self.L
+        if self.remote:
+            cur = int(L.b200vr_current_buffer(r.handle))
+            r._ck(L.b200vr_set_frame_target(r.handle, C.c_void_p(self.remote[cur]), C.c_void_p(self.remote[2 + cur])))
+        r.render()
+        self.launches += r.last_stats["kernel_launches"]
+        if self.world > 1:
+            dist.all_reduce(self._tok, group=self.group)   # stream-ordered: every rank's tiles are in the display rank's frame
+        return r.last_stats

@@ -58,6 +58,19 @@ def main():
         got = r.download(want_grad=False)[0]
         out["sort_first_bit_identical"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
         out["sort_first_vs_queue_kernel_max_abs"] = float(np.abs(got - want_q).max())
+    # the same through the fused exchange: every rank stores its tiles straight into rank 0's frame
+    dist.barrier()
+    r._ck(L.b200vr_resize(r.handle, W + 64, H))   # reallocate: a fresh zeroed frame on every rank
+    r._ck(L.b200vr_resize(r.handle, W, H))
+    fp = D.SortFirstP2P(r, rank, world)
+    fp.step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:
+        got = r.download(want_grad=False)[0]
+        out["sort_first_p2p_bit_identical"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+    fp.close()
+    dist.barrier()
     r.close()
 
     # ---- sort-last ----
@@ -100,7 +113,7 @@ def main():
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
-    if rank == 0 and not (out["sort_first_bit_identical"] and out["sort_first_vs_queue_kernel_max_abs"] < 1e-3 and out["sort_last_ok"] and
+    if rank == 0 and not (out["sort_first_bit_identical"] and out["sort_first_p2p_bit_identical"] and out["sort_first_vs_queue_kernel_max_abs"] < 1e-3 and out["sort_last_ok"] and
                           out["sort_last_p2p_equals_nccl"]):
         sys.exit(1)
 
