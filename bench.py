@@ -241,7 +241,7 @@ def run_b200(args):
     r.init(scene, scene.camera)
     r.commit()
     stream = torch.cuda.current_stream()
-    r._ck(L.b200vr_set_stream(r.handle, C.c_void_p(stream.cuda_stream)))
+    r.use_stream(stream.cuda_stream)   # kernels ordered with the NCCL collectives / barriers of the exchange
     launches = [0]
 
     if sortlast:

@@ -75,6 +75,8 @@ void b200vr_destroy(b200vr_t* h);
 const char* b200vr_last_error(const b200vr_t* h); /* h may be NULL: error of the last failed create */
 void b200vr_default_params(b200vr_params* p);
 /* launch on a caller-owned cudaStream_t (framebuffer_stream, device_impl.cpp:102-111); NULL restores the private stream */
+/* NULL selects the handle's own non-blocking stream again. The legacy default stream has the handle 0 = NULL: pass
+ * cudaStreamLegacy ((cudaStream_t)0x1) to run on it (this is what torch.cuda.current_stream() is unless a stream context is active). */
 int b200vr_set_stream(b200vr_t* h, void* cuda_stream);
 
 /* volume: replaces StructuredRegularVolume::load_from_array3d_scalar (volume.cpp:181-257) =

@@ -248,6 +248,13 @@ class MainRenderer:
         self.last_stats = st.as_dict()
         self.variance = 0.0
 
+    def use_stream(self, cuda_stream_handle):
+        """Run every kernel / copy of this device on the given CUDA stream (e.g. torch.cuda.current_stream().cuda_stream), so
+        that they are ordered with the caller's own work (NCCL collectives, peer copies). Handle 0 is the legacy default
+        stream, which the C ABI wants spelled cudaStreamLegacy (0x1): NULL means "the device's own stream" there."""
+        h = int(cuda_stream_handle)
+        self._ck(capi.lib().b200vr_set_stream(self._h, C.c_void_p(h if h != 0 else 1)))
+
     def swap(self):
         self._ck(capi.lib().b200vr_swap(self._h))
 

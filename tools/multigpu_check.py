@@ -38,7 +38,7 @@ def main():
         r.set_fbsize((W, H))
         r.init(scene, scene.camera)
         r.commit()
-        r._ck(L.b200vr_set_stream(r.handle, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        r.use_stream(torch.cuda.current_stream().cuda_stream)   # ordered with the NCCL collectives
         return r
 
     # ---- sort-first (gradient + shadow shading, the queue kernel) ----
