@@ -146,6 +146,21 @@ int b200vr_set_brick(b200vr_t* h, const float own_lo_or_null[3], const float own
 /* sort-first: render only the image tiles owned by `rank` of `nranks` (64x32-pixel tiles, round robin) */
 int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks);
 
+/* sparse (foveated) sampling: replaces MainRenderer::set_sparse_sampling / set_focus as the optix7 device consumes them
+ * (device_impl.cpp:176-183) and generate_sparse_sampling_mask_d + stream compaction (ovr/common/generate_mask.cu:55-124,
+ * device_impl.cpp:327-341). While enabled, every b200vr_render keeps pixel (x, y) with probability
+ * p = (1 - base_noise) * exp(-0.5 * (fx^2 + fy^2) / focus_scale^2) + base_noise, fx = x/W - cx, fy = (y/H - cy) / (W/H),
+ * decided against noise[(y % tile_xy), (x % tile_xy), frame_index % tile_t] (blue_noise.h:81-101), renders only the kept
+ * pixels (compute_screen_position method 3, shaders_common.h:437-449) and, when not accumulating, clears both frame
+ * buffers first (device_impl.cpp:234-239). Single-device mode: refused with a tile partition, brick or frame target. */
+int b200vr_set_sparse_sampling(b200vr_t* h, int enable, const float focus_center[2], float focus_scale, float base_noise);
+/* noise table, tile_xy * tile_xy * tile_t floats laid out [y][x][t] like the reference's embedded stbn_128x128x64 /
+ * blue_64x64x64 tables (blue_noise.h:60-101; data/noise/blue_64x64x64.bin). NULL: built-in 128x128x64 white-noise table. */
+int b200vr_set_sparse_noise(b200vr_t* h, const float* table_or_null, int tile_xy, int tile_t);
+/* pixel list of the last sparse frame: returns its length (or a negative error); xy_out (may be NULL) receives (x, y) int32
+ * pairs in launch order -- image-tile order, not the reference's row-major order; the set is the reference's */
+int64_t b200vr_get_sparse_samples(b200vr_t* h, int32_t* xy_out_or_null, int64_t capacity_pairs);
+
 /* replaces Impl::render (device_impl.cpp:199-269): one synchronous frame; stats may be NULL */
 int b200vr_render(b200vr_t* h, b200vr_stats* stats);
 /* replaces Impl::mapframe / swap (device_impl.cpp:102-111,271-281): device pointers of the current buffer

@@ -11,6 +11,7 @@
 #include "march_q.cuh"
 #include "march_ring.cuh"
 #include "march_ns.cuh"
+#include "sparse.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -93,6 +94,16 @@ struct b200vr {
   unsigned long long* acc = nullptr; // per pixel fixed-point sums (allocated with the frame)
   float* ray_alpha = nullptr;
   Counters* counters = nullptr;
+  // sparse (foveated) sampling, sparse.cuh (device_impl.cpp:180-183,236-238,327-341)
+  bool sparse = false;
+  float focus_x = 0.5f, focus_y = 0.5f, focus_scale = 0.06f, base_noise = 0.07f; // apps/main_app.cpp:122-124
+  float* sp_noise = nullptr;
+  int sp_tile_xy = 0, sp_tile_t = 0;
+  int2* sp_xy = nullptr;           // compacted pixel list of the last sparse frame
+  unsigned int* sp_blocks = nullptr; // per 1024-entry block: count, then exclusive offset
+  unsigned int* sp_count = nullptr;
+  int sp_alloc_px = 0;             // pixels sp_xy was allocated for
+  int sp_last_count = -1;          // entries of sp_xy after the last sparse render (-1: none yet)
 };
 
 #define CK(call)                                                                                   \
@@ -205,6 +216,9 @@ static void free_frame(b200vr_t* h)
   }
   cudaFree(h->accum);
   h->accum = nullptr;
+  cudaFree(h->sp_xy);
+  cudaFree(h->sp_blocks);
+  h->sp_xy = nullptr, h->sp_blocks = nullptr, h->sp_alloc_px = 0, h->sp_last_count = -1;
 }
 
 extern "C" void b200vr_destroy(b200vr_t* h)
@@ -227,6 +241,8 @@ extern "C" void b200vr_destroy(b200vr_t* h)
   cudaFree(h->ray_alpha);
   cudaFree(h->counters);
   cudaFree(h->minmax);
+  cudaFree(h->sp_noise);
+  cudaFree(h->sp_count);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -812,6 +828,106 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.sidx = 0;
 }
 
+// createSparseSamples (device_impl.cpp:327-341) + generate_sparse_sampling_mask_d (generate_mask.cu:100-124): mask, compaction,
+// and the frame clear that goes with a sparse frame (device_impl.cpp:234-239). Needs the pixel count on the host to size the
+// launch, like the reference (thrust::remove returns the new end): one 4-byte read-back.
+static int build_sparse_list(b200vr_t* h, LaunchParams& P, int& launches)
+{
+  const int npx = h->width * h->height;
+  if (!h->sp_noise) { // no table supplied: built-in white noise, 128 x 128 x 64 like the reference's STBN table
+    const int n = 128 * 128 * 64;
+    CK(cudaMalloc(&h->sp_noise, (size_t)n * sizeof(float)));
+    sparse_default_noise_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(h->sp_noise, n, 1337u); // generate_mask.cu:35
+    CK(cudaGetLastError());
+    h->sp_tile_xy = 128, h->sp_tile_t = 64;
+    launches++;
+  }
+  SparseParams S;
+  S.noise = h->sp_noise;
+  S.tile_xy = h->sp_tile_xy, S.tile_t = h->sp_tile_t;
+  S.width = h->width, S.height = h->height;
+  S.super_w = P.super_w;
+  S.n_entries = P.super_w * P.super_h * WARP_TILES_PER_SUPER * 32;
+  S.frame_index = h->frame_index; // already incremented (device_impl.cpp:241,252)
+  S.mean_x = h->focus_x, S.mean_y = h->focus_y;
+  S.sigma_rcp2 = 1.f / (h->focus_scale * h->focus_scale); // generate_mask.cu:92
+  S.base_noise = h->base_noise;
+  const int n_blocks = (S.n_entries + SPARSE_BLOCK - 1) / SPARSE_BLOCK;
+  if (h->sp_alloc_px != npx) {
+    cudaFree(h->sp_xy);
+    cudaFree(h->sp_blocks);
+    h->sp_xy = nullptr, h->sp_blocks = nullptr, h->sp_alloc_px = 0;
+    CK(cudaMalloc(&h->sp_xy, (size_t)npx * sizeof(int2)));
+    CK(cudaMalloc(&h->sp_blocks, (size_t)n_blocks * sizeof(unsigned int)));
+    h->sp_alloc_px = npx;
+  }
+  if (!h->sp_count) CK(cudaMalloc(&h->sp_count, sizeof(unsigned int)));
+  sparse_count_kernel<<<n_blocks, SPARSE_BLOCK, 0, h->stream>>>(S, h->sp_blocks);
+  sparse_scan_kernel<<<1, 1024, 0, h->stream>>>(h->sp_blocks, n_blocks, h->sp_count);
+  sparse_scatter_kernel<<<n_blocks, SPARSE_BLOCK, 0, h->stream>>>(S, h->sp_blocks, h->sp_xy);
+  CK(cudaGetLastError());
+  launches += 3;
+  unsigned int count = 0;
+  CK(cudaMemcpyAsync(&count, h->sp_count, sizeof(count), cudaMemcpyDeviceToHost, h->stream));
+  if (!h->prm.accumulate) { // "in non-sparse sampling mode, the entire frame will be re-written anyway": clear both buffers
+    for (int i = 0; i < 2; i++) {
+      CK(cudaMemsetAsync(h->rgba[i], 0, (size_t)npx * sizeof(float4), h->stream));
+      CK(cudaMemsetAsync(h->grad[i], 0, (size_t)npx * 3 * sizeof(float), h->stream));
+    }
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  h->sp_last_count = (int)count;
+  P.sparse_xy = h->sp_xy;
+  P.sparse_count = (int)count;
+  P.n_warp_tiles = ((int)count + 31) / 32;
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_sparse_sampling(b200vr_t* h, int enable, const float focus_center[2], float focus_scale, float base_noise)
+{
+  if (!h) return B200VR_EINVAL;
+  if (enable) {
+    if (!focus_center) return fail(h, B200VR_EINVAL, "set_sparse_sampling: focus_center is NULL");
+    if (!(focus_scale > 0.f)) return fail(h, B200VR_EINVAL, "set_sparse_sampling: focus_scale must be positive");
+    h->focus_x = focus_center[0], h->focus_y = focus_center[1];
+    h->focus_scale = focus_scale;
+    h->base_noise = base_noise;
+  }
+  h->sparse = enable != 0;
+  h->reset = true; // framebuffer_reset on every focus / sparse change (device_impl.cpp:154-183)
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_sparse_noise(b200vr_t* h, const float* table, int tile_xy, int tile_t)
+{
+  if (!h) return B200VR_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  cudaFree(h->sp_noise);
+  h->sp_noise = nullptr, h->sp_tile_xy = h->sp_tile_t = 0;
+  if (!table) return B200VR_OK; // back to the built-in table
+  if (tile_xy <= 0 || tile_t <= 0 || (size_t)tile_xy * tile_xy * tile_t > (size_t)1 << 28)
+    return fail(h, B200VR_EINVAL, "set_sparse_noise: bad table size");
+  const size_t n = (size_t)tile_xy * tile_xy * tile_t;
+  CK(cudaMalloc(&h->sp_noise, n * sizeof(float)));
+  CK(cudaMemcpy(h->sp_noise, table, n * sizeof(float), cudaMemcpyHostToDevice));
+  h->sp_tile_xy = tile_xy, h->sp_tile_t = tile_t;
+  return B200VR_OK;
+}
+
+extern "C" int64_t b200vr_get_sparse_samples(b200vr_t* h, int32_t* xy_out, int64_t capacity)
+{
+  if (!h) return B200VR_EINVAL;
+  if (h->sp_last_count < 0) return fail(h, B200VR_ESTATE, "get_sparse_samples: no sparse frame rendered yet");
+  if (xy_out) {
+    if (capacity < h->sp_last_count) return fail(h, B200VR_EINVAL, "get_sparse_samples: capacity too small");
+    if (cudaSetDevice(h->device) != cudaSuccess ||
+        cudaMemcpy(xy_out, h->sp_xy, (size_t)h->sp_last_count * sizeof(int2), cudaMemcpyDeviceToHost) != cudaSuccess)
+      return fail(h, B200VR_ECUDA, "get_sparse_samples: copy failed");
+  }
+  return h->sp_last_count;
+}
+
 extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
 {
   if (!h) return B200VR_EINVAL;
@@ -833,6 +949,13 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     return fail(h, B200VR_ESTATE, "render: a brick (sort-last) needs ray marching with SHADING_NONE and the tex3D sampler: "
                                   "shadow rays and random walks leave the brick");
   const KernelChoice kc = pick_kernel(h);
+  int sparse_launches = 0;
+  if (h->sparse) {
+    if (kc.ring || h->nranks != 1 || h->has_lattice || h->target_rgba)
+      return fail(h, B200VR_ESTATE, "render: sparse sampling is a single-device mode (no tile partition, brick or frame target)");
+    const int rc = build_sparse_list(h, P, sparse_launches);
+    if (rc != B200VR_OK) return rc;
+  }
   const render_kernel_t kernel = kc.fn;
   const size_t smem = kc.smem;
   if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -933,7 +1056,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     stats->delta_samples = c.delta_samples;
     stats->rays = c.rays;
     stats->frame_index = h->frame_index;
-    stats->kernel_launches = launches;
+    stats->kernel_launches = launches + sparse_launches;
   }
   return B200VR_OK;
 }

@@ -89,6 +89,9 @@ struct LaunchParams {
   const int* tile_order;    // launch order of the owned super tiles: tile_order[j] = slot m (super tile rank + m * nranks)
   unsigned int* tile_cost;  // per slot m: warp clocks / 64 spent on its warp tiles in THIS launch (orders the next one)
   Counters* counters;
+  // ---- sparse (foveated) sampling, sparse.cuh: when set, warp tile k renders list entries 32k .. 32k+31 ----
+  const int2* sparse_xy;    // compacted pixel coordinates (xs_and_ys, shaders_common.h:437-449); nullptr = whole image
+  int sparse_count;
   // ---- deferred-shading ring (march_ring.cuh) ----
   unsigned int* ring_ctrl;  // [0] head, [1] tail, [2] warps still marching, [3] error
   unsigned int* ring_seq;   // per slot sequence number
@@ -113,9 +116,26 @@ __device__ __forceinline__ int warp_tile_origin(const LaunchParams& P, int k, in
   py = sy * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
   return m;
 }
+// pixel of this lane in the k-th warp tile of the launch; returns the cost-table slot of the tile (-1: none). Dense frames:
+// 8x4 pixels at warp_tile_origin; sparse sampling: the lane's entry of the compacted list (compute_screen_position method 3,
+// shaders_common.h:437-449). Warp-uniform branch on a launch constant.
+__device__ __forceinline__ int warp_tile_pixel(const LaunchParams& P, int k, int lane, int& ix, int& iy)
+{
+  if (P.sparse_xy != nullptr) {
+    const int e = k * 32 + lane;
+    const int2 c = e < P.sparse_count ? __ldg(P.sparse_xy + e) : make_int2(P.width, 0); // x = width: outside the image
+    ix = c.x, iy = c.y;
+    return -1;
+  }
+  int px, py;
+  const int m = warp_tile_origin(P, k, px, py);
+  ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
+  return m;
+}
 // a warp reports how long its tile took: next frame's launch order
 __device__ __forceinline__ void tile_cost_add(const LaunchParams& P, int m, long long t_start)
 {
+  if (m < 0) return; // sparse sampling: no tile history
   const unsigned long long dt = (unsigned long long)(clock64() - t_start);
   atomicAdd(P.tile_cost + m, (unsigned int)(dt >> 6));
 #if B200VR_TILE_STATS // two more atomics per tile on single words: measurably slows the launch, debugging only

@@ -249,10 +249,9 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
     if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
-    int px, py;
-    const int tile_slot = warp_tile_origin(P, k, px, py);
+    int ix, iy;
+    const int tile_slot = warp_tile_pixel(P, k, lane, ix, iy);
     const long long tile_t0 = clock64();
-    const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     const bool inside = ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
     // per-pixel sums over the spp loop are kept in the frame itself (same thread reads and writes its own pixel) and the

@@ -197,10 +197,9 @@ raymarch_kernel(const __grid_constant__ LaunchParams P)
     if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
     k = __shfl_sync(0xffffffffu, k, 0);
     if (k >= P.n_warp_tiles) break;
-    int px, py;
-    const int tile_slot = warp_tile_origin(P, k, px, py);
+    int ix, iy;
+    const int tile_slot = warp_tile_pixel(P, k, lane, ix, iy);
     const long long tile_t0 = clock64();
-    const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
     RayStats st = { 0u, 0u, 0u };
     unsigned int rays = 0;
     if (ix < P.width && iy < P.height) {

@@ -9,6 +9,7 @@
 #include <ovr/common/dylink/ObjectFactory.h>
 
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
 #include <string>
@@ -50,6 +51,10 @@ struct DeviceB200::Impl {
   bool initialized = false;
   bool prm_dirty = false;
   vec2i fbsize = vec2i(0, 0);
+  // sparse sampling state (defaults of apps/main_app.cpp:122-126)
+  vec2f focus_center = vec2f(0.5f, 0.5f);
+  float focus_scale = 0.06f, base_noise = 0.07f;
+  bool sparse_sampling = false, noise_loaded = false;
 #ifndef OVR_BUILD_CUDA_DEVICES
   std::vector<float> host_rgba, host_grad; // host executable built without CUDA buffers: frames are handed out on the CPU
 #endif
@@ -94,6 +99,28 @@ struct DeviceB200::Impl {
     prm_dirty = true;
   }
 
+  // The reference embeds its noise table at build time (noise_files.h generated from stbn_128x128x64.bin, which the
+  // repository does not ship; ovr/CMakeLists.txt:60-75). Here OVR_B200_NOISE_FILE names a raw little-endian f32 table laid
+  // out [y][x][t] with t = 64 (blue_noise.h:39,95-99), e.g. data/noise/blue_64x64x64.bin; unset = the built-in table.
+  void load_noise_table()
+  {
+    noise_loaded = true;
+    const char* path = std::getenv("OVR_B200_NOISE_FILE");
+    if (!path || !*path) return;
+    std::FILE* f = std::fopen(path, "rb");
+    if (!f) throw std::runtime_error(std::string("b200: cannot open noise table ") + path);
+    std::vector<float> table;
+    float buf[4096];
+    size_t n;
+    while ((n = std::fread(buf, sizeof(float), 4096, f)) > 0) table.insert(table.end(), buf, buf + n);
+    std::fclose(f);
+    int tile = 0;
+    while ((size_t)(tile + 1) * (tile + 1) * 64 <= table.size()) tile++;
+    if (tile == 0 || (size_t)tile * tile * 64 != table.size())
+      throw std::runtime_error(std::string("b200: noise table is not tile x tile x 64 floats: ") + path);
+    check(b200vr_set_sparse_noise(handle, table.data(), tile, 64), "set_sparse_noise");
+  }
+
   void swap() { check(b200vr_swap(handle), "swap"); }
 
   // Impl::commit (device_impl.cpp:113-197): only changed parameters are applied; every change resets the accumulation
@@ -135,12 +162,18 @@ struct DeviceB200::Impl {
       prm.sampling_rate = pp.volume_sampling_rate.get();
       prm_dirty = true;
     }
-    // sparse sampling / focus / lights / materials: accepted and ignored, like the optix7 device ignores scene lights
-    // and materials; sparse sampling is a "next" row
-    pp.focus_center.update();
-    pp.focus_scale.update();
-    pp.base_noise.update();
-    pp.sparse_sampling.update();
+    // sparse (foveated) sampling, device_impl.cpp:154-183; lights / materials are accepted and ignored like the optix7
+    // device ignores them
+    bool sparse_dirty = false;
+    if (pp.focus_center.update()) focus_center = pp.focus_center.ref(), sparse_dirty = true;
+    if (pp.focus_scale.update()) focus_scale = pp.focus_scale.ref(), sparse_dirty = true;
+    if (pp.base_noise.update()) base_noise = pp.base_noise.ref(), sparse_dirty = true;
+    if (pp.sparse_sampling.update()) sparse_sampling = pp.sparse_sampling.ref(), sparse_dirty = true;
+    if (sparse_dirty) {
+      if (sparse_sampling && !noise_loaded) load_noise_table();
+      const float fc[2] = { focus_center.x, focus_center.y };
+      check(b200vr_set_sparse_sampling(handle, sparse_sampling ? 1 : 0, fc, focus_scale, base_noise), "set_sparse_sampling");
+    }
     if (prm_dirty) {
       check(b200vr_set_params(handle, &prm), "set_params");
       prm_dirty = false;

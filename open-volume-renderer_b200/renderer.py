@@ -82,6 +82,8 @@ class MainRenderer:
         self.sampler = capi.SAMPLER_TEX3D
         self.skip_empty = True
         self.premultiplied = False
+        # sparse sampling state as the device holds it (defaults of apps/main_app.cpp:122-126)
+        self._focus_center, self._focus_scale, self._base_noise, self._sparse = (0.5, 0.5), 0.06, 0.07, False
 
     # ---- thread-safe setters (ovr/renderer.h:135-248) ----
     def set_fbsize(self, fbsize):
@@ -219,9 +221,16 @@ class MainRenderer:
             self._ck(L.b200vr_set_transfer_function(self._h, c.ctypes.data_as(C.POINTER(C.c_float)), len(c) // 3,
                                                     o.ctypes.data_as(C.POINTER(C.c_float)), len(o) // 2, r[0], r[1]))
         dirty = False
-        for name in ("focus_center", "focus_scale", "base_noise", "sparse_sampling"):
-            if P[name].update():
-                dirty = True  # accepted; sparse sampling is out of scope -> full frames are rendered
+        sparse_dirty = False
+        for name, attr in (("focus_center", "_focus_center"), ("focus_scale", "_focus_scale"), ("base_noise", "_base_noise"),
+                           ("sparse_sampling", "_sparse")):
+            if P[name].update():  # device_impl.cpp:154-183
+                setattr(self, attr, P[name].ref())
+                sparse_dirty = True
+        if sparse_dirty:
+            fc = (C.c_float * 2)(float(self._focus_center[0]), float(self._focus_center[1]))
+            self._ck(L.b200vr_set_sparse_sampling(self._h, 1 if self._sparse else 0, fc, C.c_float(self._focus_scale),
+                                                  C.c_float(self._base_noise)))
         if P["sample_per_pixel"].update():
             self._spp, dirty = P["sample_per_pixel"].ref(), True
         if P["path_tracing"].update():
@@ -276,6 +285,28 @@ class MainRenderer:
         self._ck(capi.lib().b200vr_download(self._h, rgba.ctypes.data_as(C.c_void_p),
                                             grad.ctypes.data_as(C.c_void_p) if want_grad else None))
         return rgba, grad
+
+    def set_sparse_noise(self, table, tile_xy, tile_t):
+        """Device option: the [y][x][t] noise table the sparse-sampling mask is thresholded against (the reference embeds
+        one at build time, blue_noise.h:60-78); None restores the built-in table."""
+        if table is None:
+            self._ck(capi.lib().b200vr_set_sparse_noise(self._h, None, 0, 0))
+            return
+        t = np.ascontiguousarray(table, np.float32).ravel()
+        if t.size != tile_xy * tile_xy * tile_t:
+            raise RuntimeError("[b200] noise table size does not match tile_xy^2 * tile_t")
+        self._ck(capi.lib().b200vr_set_sparse_noise(self._h, t.ctypes.data_as(C.c_void_p), tile_xy, tile_t))
+
+    def sparse_samples(self):
+        """(n, 2) int32 array of the pixels (x, y) the last sparse frame rendered (xs_and_ys, device_impl.cpp:332-340)."""
+        L = capi.lib()
+        n = int(L.b200vr_get_sparse_samples(self._h, None, 0))
+        if n < 0:
+            self._ck(n)
+        out = np.empty((n, 2), np.int32)
+        if n and L.b200vr_get_sparse_samples(self._h, out.ctypes.data_as(C.c_void_p), n) != n:
+            self._ck(capi.ECUDA)
+        return out
 
     @property
     def handle(self):

@@ -111,3 +111,25 @@ extern "C" void ovr_oracle_noise(int32_t n, uint32_t seed, const int32_t org[3],
     }
   });
 }
+
+// Sparse (foveated) sampling mask: generate_blue_noise_kernel (ovr/common/random/blue_noise.h:81-101) followed by
+// generate_sparse_samples (ovr/common/generate_mask.cu:55-86). keep[i] = 1 when pixel i = x + y * width is rendered;
+// p_out (may be NULL) receives the acceptance probability, margin information for the tests: the reference evaluates
+// exp() with the device's approximate __expf and contracted multiply-adds, so a pixel whose noise value lies within a few
+// ulp of p can legitimately fall on either side on the GPU.
+extern "C" void ovr_oracle_sparse_mask(int width, int height, int frame_index, const float* noise, int tile_xy, int tile_t,
+                                       const float mean[2], float sigma, float base_noise, uint8_t* keep, float* p_out)
+{
+  const float sigma_rcp2 = 1.f / (sigma * sigma); // generate_mask.cu:92
+  const float aspect = (float)width / (float)height;
+  for (int y = 0; y < height; y++)
+    for (int x = 0; x < width; x++) {
+      const size_t i = (size_t)x + (size_t)y * (size_t)width;
+      const float d = noise[((size_t)(y % tile_xy) * tile_xy + (size_t)(x % tile_xy)) * tile_t + (size_t)(frame_index % tile_t)];
+      const float fx = (float)x / (float)width - mean[0];
+      const float fy = ((float)y / (float)height - mean[1]) / aspect;
+      const float p = (1.0f - base_noise) * std::exp(-0.5f * (fx * fx + fy * fy) * sigma_rcp2) + base_noise;
+      keep[i] = d < p ? 1 : 0;
+      if (p_out) p_out[i] = p;
+    }
+}

@@ -108,6 +108,9 @@ void ovr_oracle_tex1d(const float* table, int n, int channels, int filter_mode, 
 void ovr_oracle_noise(int32_t n, uint32_t seed, const int32_t org[3], const int32_t bdims[3], float* out,
                       int num_threads);
 void ovr_oracle_xfm(const float m[12], const float v[3], float* out24); /* gdt transforms, layout of ref_xfm */
+/* sparse-sampling mask (generate_mask.cu:55-86 + blue_noise.h:81-101): keep[x + y*width] in {0,1}, p_out optional */
+void ovr_oracle_sparse_mask(int width, int height, int frame_index, const float* noise, int tile_xy, int tile_t,
+                            const float mean[2], float sigma, float base_noise, uint8_t* keep, float* p_out);
 int ovr_oracle_hardware_threads(void);
 
 #ifdef __cplusplus

@@ -101,6 +101,29 @@ def noise(n, seed=1337, org=(0, 0, 0), bdims=None, threads=0):
     return out
 
 
+def sparse_mask(width, height, frame_index, noise_table, tile_xy, tile_t, mean, sigma, base_noise):
+    """(keep, p): boolean (H, W) mask of the pixels a sparse frame renders and their acceptance probability."""
+    t = np.ascontiguousarray(noise_table, np.float32).ravel()
+    assert t.size == tile_xy * tile_xy * tile_t
+    keep = np.zeros((height, width), np.uint8)
+    p = np.zeros((height, width), np.float32)
+    m = (C.c_float * 2)(float(mean[0]), float(mean[1]))
+    lib().ovr_oracle_sparse_mask(width, height, int(frame_index), _fp(t), tile_xy, tile_t, m, C.c_float(sigma),
+                                 C.c_float(base_noise), _p(keep), _fp(p))
+    return keep.astype(bool), p
+
+
+def ref_sparse_mask(width, height, frame_index, noise_table, tile_xy, mean, sigma, base_noise):
+    """The reference's own two kernels run on the host (oracle/_ref; the table's time extent is the reference's 64)."""
+    L = ref_kat_lib()
+    t = np.ascontiguousarray(noise_table, np.float32).ravel().copy()
+    assert t.size == tile_xy * tile_xy * 64
+    xy = np.zeros((height * width, 2), np.int32)
+    m = (C.c_float * 2)(float(mean[0]), float(mean[1]))
+    L.ref_sparse_mask(width, height, int(frame_index), _fp(t), tile_xy, m, C.c_float(sigma), C.c_float(base_noise), _p(xy))
+    return xy
+
+
 def macrocell_dims(dims):
     mc = _i3()
     lib().ovr_oracle_macrocell_dims(_i3(*dims), mc)

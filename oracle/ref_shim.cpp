@@ -4,6 +4,8 @@
 //   ovr/devices/optix7/accel/dda.h          dda::DDAIter, dda::dda3
 //   ovr/common/random/random.h              random::RandomTEA
 //   extern/gdt/gdt/math/{vec,mat}.h         normalize, xfmPoint/Vector/Normal, affine inverse
+//   ovr/common/generate_mask.cu:55-86       generate_sparse_samples  } kernel bodies cut out at build time and run as
+//   ovr/common/random/blue_noise.h:81-101   generate_blue_noise_kernel } host loops (threadIdx/blockIdx are plain structs here)
 // tests/golden/make_golden.py drives it to produce the fixtures that pin the oracle.
 #include <cuda_runtime.h> // float2 / make_float2 for random.h (host-side CUDA headers only)
 #include <dda.h>
@@ -81,4 +83,41 @@ extern "C" void ref_xfm(const float m[12], const float v[3], float* out)
   out[12] = inv.l.vx.x, out[13] = inv.l.vy.x, out[14] = inv.l.vz.x, out[15] = inv.p.x;
   out[16] = inv.l.vx.y, out[17] = inv.l.vy.y, out[18] = inv.l.vz.y, out[19] = inv.p.y;
   out[20] = inv.l.vx.z, out[21] = inv.l.vy.z, out[22] = inv.l.vz.z, out[23] = inv.p.z;
+}
+
+// ---- sparse-sampling mask: the reference's two kernels, executed one "thread" at a time on the host ----
+#include <cassert>
+#include <cmath>
+#include <vector>
+namespace ref_mask {
+struct Idx { size_t x; };
+static Idx threadIdx, blockIdx, blockDim;
+static int tile_xy = 128;
+static inline float __expf(float x) { return std::exp(x); } // the device intrinsic is approximate; see the tolerance in the tests
+#define __restrict__
+#define OVR_NOISE_TILE_SIZE_XY ref_mask::tile_xy
+#define OVR_NOISE_TILE_SIZE_T 64
+static void
+#include <sparse_samples_extract.h>
+template<typename T> static void
+#include <blue_noise_extract.h>
+} // namespace ref_mask
+
+// generate_sparse_sampling_mask_d (generate_mask.cu:100-124) without the compaction: xy[2i], xy[2i+1] = pixel or -1
+extern "C" void ref_sparse_mask(int width, int height, int frame_index, float* noise, int tile_xy, const float mean[2],
+                                float sigma, float base_noise, int32_t* xy)
+{
+  using namespace ref_mask;
+  ref_mask::tile_xy = tile_xy;
+  const size_t n = (size_t)width * height;
+  std::vector<float> dist(n);
+  blockIdx.x = 0, blockDim.x = 0;
+  for (size_t i = 0; i < n; i++) {
+    threadIdx.x = i;
+    generate_blue_noise_kernel<float>((uint32_t)n, noise, dist.data(), (uint32_t)height, (uint32_t)width, frame_index);
+  }
+  for (size_t i = 0; i < n; i++) {
+    threadIdx.x = i;
+    generate_sparse_samples(n, xy, dist.data(), vec2i(width, height), 1, vec2f(mean[0], mean[1]), 1.f / (sigma * sigma), base_noise);
+  }
 }

@@ -6,7 +6,9 @@ where /root/reference exists):
   scene_vorts1.npz  the bundled scene data/configs/scene_vorts1.json (BASELINE config C1): camera, sample distance,
                     scalar mapping range, 1024-entry alpha array, colour controls
 
-Usage: python tests/golden/make_golden.py
+  sparse_mask.npz   sparse-sampling masks from the reference's own mask kernels run on the host (same shim)
+
+Usage: python tests/golden/make_golden.py [sparse]
 """
 import base64
 import ctypes as C
@@ -20,6 +22,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 from oracle import pyoracle  # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from helpers import sparse_noise_table  # noqa: E402
 
 REF = "/root/reference"
 
@@ -114,5 +118,36 @@ def main():
     print("wrote scene_vorts1.npz: alpha", alpha.shape, "max", alpha.max())
 
 
+SPARSE_CASES = [  # (width, height, frame_index, tile_xy, focus centre, focus scale, base noise)
+    (160, 96, 1, 16, (0.5, 0.5), 0.06, 0.07),     # the defaults of apps/main_app.cpp:122-124
+    (257, 131, 7, 16, (0.3, 0.7), 0.15, 0.01),
+    (320, 200, 64, 64, (0.9, 0.1), 0.5, 0.2),     # frame_index wraps the 64 time slices
+    (64, 64, 129, 64, (0.5, 0.5), 1.0, 1.0),      # base noise 1: p = 1 everywhere -> the noise value 1.0 alone is rejected
+    (96, 128, 3, 16, (1.5, -0.5), 0.05, 0.0),     # focus outside the image, no base noise: almost empty
+]
+
+
+def make_sparse():
+    """sparse_mask.npz: masks produced by the reference's generate_blue_noise_kernel + generate_sparse_samples (cut out of
+    ovr/common/random/blue_noise.h and ovr/common/generate_mask.cu and run on the host by oracle/ref_shim.cpp)."""
+    pyoracle.build()
+    assert pyoracle.ref_kat_lib() is not None, "oracle/_ref/libovr_ref_kat.so missing (needs /root/reference)"
+    out = {"n": np.int32(len(SPARSE_CASES))}
+    for k, (w, h, fi, tile, mean, sigma, base) in enumerate(SPARSE_CASES):
+        xy = pyoracle.ref_sparse_mask(w, h, fi, sparse_noise_table(tile), tile, mean, sigma, base)
+        keep = xy[:, 0] >= 0
+        idx = np.nonzero(keep)[0]
+        assert np.array_equal(xy[idx, 0], idx % w) and np.array_equal(xy[idx, 1], idx // w) and (xy[~keep] == -1).all()
+        out[f"case{k}"] = np.array([w, h, fi, tile], np.int32)
+        out[f"case{k}_f"] = np.array([mean[0], mean[1], sigma, base], np.float32)
+        out[f"case{k}_keep"] = np.packbits(keep)
+        print(f"sparse case {k}: {keep.sum()} of {w * h} pixels kept")
+    np.savez_compressed(os.path.join(HERE, "sparse_mask.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "sparse":
+        make_sparse()
+    else:
+        main()
+        make_sparse()

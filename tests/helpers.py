@@ -41,3 +41,11 @@ def psnr(a, b, peak=1.0):
 
 def max_abs(a, b):
     return float(np.max(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))))
+
+
+def sparse_noise_table(tile_xy, seed=1337):
+    """Synthetic stand-in for the reference's embedded noise tables (blue_noise.h:60-78): values on the same 8-bit grid
+    k / 255, laid out [y][x][t] with 64 time slices. tests/golden/make_golden.py feeds the same tables to the reference's
+    mask kernels."""
+    k = np.random.default_rng(seed + tile_xy).integers(0, 256, size=tile_xy * tile_xy * 64, dtype=np.uint32)
+    return (k.astype(np.float32) / np.float32(255.0)).astype(np.float32)

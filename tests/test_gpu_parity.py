@@ -494,3 +494,136 @@ def test_all_transparent_transfer_function_gives_an_empty_frame():
         assert not rgba.any() and not grad.any()
         assert r.last_stats["primary_samples"] == 0 and r.last_stats["shadow_samples"] == 0 and r.last_stats["rays"] == W * H
         r.close()
+
+
+# ---- sparse (foveated) sampling: SURVEY 8f-f3 ----
+def _mask_from_list(xy, w, h):
+    assert ((xy[:, 0] >= 0) & (xy[:, 0] < w) & (xy[:, 1] >= 0) & (xy[:, 1] < h)).all()
+    flat = xy[:, 0].astype(np.int64) + xy[:, 1].astype(np.int64) * w
+    assert len(np.unique(flat)) == len(flat), "a pixel is listed twice"
+    m = np.zeros(w * h, bool)
+    m[flat] = True
+    return m.reshape(h, w)
+
+
+def _check_mask_against_oracle(got, want, p, table, tile, fi, w, h):
+    """The device evaluates exp() with the approximate ex2 unit and fused multiply-adds (like the reference's kernel, which
+    uses __expf); the oracle uses the host's expf. A pixel may differ only where its noise value is within 4e-6 of p."""
+    diff = got != want
+    if diff.any():
+        ys, xs = np.nonzero(diff)
+        d = table.reshape(tile, tile, 64)[ys % tile, xs % tile, fi % 64]
+        assert (np.abs(d - p[ys, xs]) <= 4e-6).all()
+        assert diff.sum() <= max(4, w * h // 2000)
+
+
+SPARSE_GPU_CASES = [
+    # name, shading, path tracing, sampler
+    ("ref-queue", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
+    ("none-lean", capi.SHADING_NONE, False, capi.SAMPLER_TEX3D),
+    ("ref-manual", capi.SHADING_REF, False, capi.SAMPLER_MANUAL),
+    ("path", capi.SHADING_REF, True, capi.SAMPLER_TEX3D),
+]
+
+
+@pytest.mark.parametrize("case", SPARSE_GPU_CASES, ids=[c[0] for c in SPARSE_GPU_CASES])
+def test_sparse_sampling_renders_exactly_the_masked_pixels(case):
+    """Sparse frame == dense frame at the kept pixels (bit for bit: same per-pixel code, same screen position) and 0
+    elsewhere (device_impl.cpp:236-238); kept set == the reference's mask (oracle pinned by tests/golden/sparse_mask.npz)."""
+    from helpers import sparse_noise_table
+    name, shading, path, sampler = case
+    W, H, tile = 203, 117, 16  # ragged: not multiples of the 8x4 / 64x32 tiles
+    sc = S.noise_scene(48, tf="pt" if path else "sparse", camera="front" if path else "oblique")
+    rd = make_renderer(sc, W, H, shading=shading, sampler=sampler, path=path)
+    rd.render()
+    dense_rgba, dense_grad = rd.download()
+    rd.close()
+    table = sparse_noise_table(tile)
+    r = make_renderer(sc, W, H, shading=shading, sampler=sampler, path=path)
+    r.set_sparse_noise(table, tile, 64)
+    focus, scale, base = (0.4, 0.55), 0.2, 0.05
+    r.set_focus(focus, scale, base)
+    r.set_sparse_sampling(True)
+    r.commit()
+    r.render()
+    assert r.last_stats["frame_index"] == 1  # same frame index as the dense frame: same RNG streams for path tracing
+    rgba, grad = r.download()
+    xy = r.sparse_samples()
+    got = _mask_from_list(xy, W, H)
+    want, p = pyoracle.sparse_mask(W, H, 1, table, tile, 64, focus, scale, base)
+    _check_mask_against_oracle(got, want, p, table, tile, 1, W, H)
+    assert 0.05 < got.mean() < 0.9 and r.last_stats["rays"] == got.sum()
+    assert np.array_equal(rgba[got].view(np.uint32), dense_rgba[got].view(np.uint32))
+    assert (rgba[~got] == 0).all() and (dense_rgba[got][:, 3] > 0).any()
+    if not path:
+        assert np.array_equal(grad[got].view(np.uint32), dense_grad[got].view(np.uint32))
+        assert (grad[~got] == 0).all()
+    # next sparse frame: another time slice of the noise table, another pixel set
+    r.render()
+    got2 = _mask_from_list(r.sparse_samples(), W, H)
+    want2, p2 = pyoracle.sparse_mask(W, H, 2, table, tile, 64, focus, scale, base)
+    _check_mask_against_oracle(got2, want2, p2, table, tile, 2, W, H)
+    assert (got2 != got).any()
+    # back to dense frames: the whole image again (ray marching with 1 spp draws no random numbers: identical to frame 1)
+    r.set_sparse_sampling(False)
+    r.commit()
+    r.render()
+    again, _ = r.download()
+    if not path:
+        assert np.array_equal(again.view(np.uint32), dense_rgba.view(np.uint32))
+    else:
+        assert (again[..., 3] > 0).mean() > 0.5 * (dense_rgba[..., 3] > 0).mean()
+    r.close()
+
+
+def test_sparse_sampling_golden_cases_and_frame_index():
+    """The five golden cases of the reference's mask kernels (incl. the empty list and p == 1), through the C ABI; the noise
+    time slice follows frame_index, which advances by one per render (device_impl.cpp:241)."""
+    from helpers import sparse_noise_table
+    M = np.load(os.path.join(os.path.dirname(__file__), "golden", "sparse_mask.npz"))
+    sc = S.noise_scene(32, tf="ramp", camera="oblique")
+    for k in range(int(M["n"])):
+        w, h, fi, tile = [int(v) for v in M[f"case{k}"]]
+        cx, cy, sigma, base = [float(v) for v in M[f"case{k}_f"]]
+        want = np.unpackbits(M[f"case{k}_keep"])[: w * h].astype(bool).reshape(h, w)
+        table = sparse_noise_table(tile)
+        r = make_renderer(sc, w, h, shading=capi.SHADING_NONE)
+        r.set_sparse_noise(table, tile, 64)
+        r.set_focus((cx, cy), sigma, base)
+        r.set_sparse_sampling(True)
+        r.commit()
+        for _ in range(fi):  # frame_index advances by one per render (device_impl.cpp:241)
+            r.render()
+        assert r.last_stats["frame_index"] == fi
+        got = _mask_from_list(r.sparse_samples(), w, h)
+        _, p = pyoracle.sparse_mask(w, h, fi, table, tile, 64, (cx, cy), sigma, base)
+        _check_mask_against_oracle(got, want, p, table, tile, fi, w, h)
+        assert r.last_stats["rays"] == got.sum()
+        if got.sum() == 0:
+            assert r.last_stats["kernel_launches"] <= 4  # mask kernels only, no render launch
+        r.close()
+
+
+def test_sparse_sampling_default_table_and_refusals():
+    sc = S.noise_scene(32, tf="ramp", camera="oblique")
+    r = make_renderer(sc, 128, 64, shading=capi.SHADING_NONE)
+    with pytest.raises(RuntimeError):
+        r.sparse_samples()  # no sparse frame yet
+    r.set_focus((0.5, 0.5), 0.06, 0.07)
+    r.set_sparse_sampling(True)
+    r.commit()
+    r.render()  # built-in table
+    n1 = len(r.sparse_samples())
+    assert 0 < n1 < 128 * 64 // 2
+    rgba, _ = r.download()
+    got = _mask_from_list(r.sparse_samples(), 128, 64)
+    assert (rgba[~got] == 0).all() and (rgba[got][:, 3] > 0).any()
+    # a tile partition (sort-first) and sparse sampling do not combine
+    r._ck(capi.lib().b200vr_set_tile_partition(r.handle, 0, 2))
+    with pytest.raises(RuntimeError):
+        r.render()
+    r._ck(capi.lib().b200vr_set_tile_partition(r.handle, 0, 1))
+    with pytest.raises(RuntimeError):
+        r.set_focus((0.5, 0.5), 0.0, 0.07)  # focus_scale must be positive
+        r.commit()
+    r.close()

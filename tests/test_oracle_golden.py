@@ -80,3 +80,21 @@ def test_oracle_tap_weights_match_captured_b200_weights():
         got = np.round(pyoracle.sample_volume(vol, pts, pyoracle.FILTER_HW).astype(np.float64) * 256).astype(np.int64)
         assert np.array_equal(got, want[:, t]), f"tap {t}"
     assert (want.sum(axis=1) == 256).all()
+
+
+def test_sparse_mask_matches_reference_kernels():
+    """ovr_oracle_sparse_mask against masks made by the reference's own generate_blue_noise_kernel + generate_sparse_samples
+    (tests/golden/sparse_mask.npz, generator: make_golden.py sparse). Both run exp() on the host: bit-exact."""
+    from helpers import sparse_noise_table
+    M = np.load(os.path.join(os.path.dirname(__file__), "golden", "sparse_mask.npz"))
+    assert int(M["n"]) >= 5
+    kept = []
+    for k in range(int(M["n"])):
+        w, h, fi, tile = [int(v) for v in M[f"case{k}"]]
+        cx, cy, sigma, base = [float(v) for v in M[f"case{k}_f"]]
+        want = np.unpackbits(M[f"case{k}_keep"])[: w * h].astype(bool).reshape(h, w)
+        keep, p = pyoracle.sparse_mask(w, h, fi, sparse_noise_table(tile), tile, 64, (cx, cy), sigma, base)
+        assert np.array_equal(keep, want), f"case {k}"
+        assert (p >= min(base, 1.0) - 1e-6).all() and (p <= 1.0 + 1e-6).all()
+        kept.append(int(keep.sum()))
+    assert kept[4] == 0 and 0 < kept[0] < 160 * 96 // 4  # empty list edge case; default focus keeps a small fraction
