@@ -240,6 +240,10 @@ def run_b200(args):
     r.set_frame_accumulation(wl["mode"] == "pathtrace")
     r.init(scene, scene.camera)
     r.commit()
+    if wl.get("sparse"):
+        r.set_focus((0.5, 0.5), 0.06, 0.07)
+        r.set_sparse_sampling(True)
+        r.commit()
     stream = torch.cuda.current_stream()
     r.use_stream(stream.cuda_stream)   # kernels ordered with the NCCL collectives / barriers of the exchange
     launches = [0]

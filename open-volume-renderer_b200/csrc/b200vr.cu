@@ -962,6 +962,8 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kernel, kc.threads, smem));
   if (per_sm < 1) return fail(h, B200VR_ECUDA, "render: kernel does not fit on an SM");
+  if (const char* cap = std::getenv("B200VR_MAX_CTAS_PER_SM")) // experiments: fewer warps in flight = shorter reuse distance in L2
+    per_sm = std::max(1, std::min(per_sm, std::atoi(cap)));
   const int warps_per_cta = kc.threads / 32;
   const int want = (P.n_warp_tiles + warps_per_cta - 1) / warps_per_cta;
   const int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs

@@ -136,6 +136,8 @@ WORKLOADS = {
     # name: (volume edge, width, height, tf preset, camera, sampling rate, mode, shading)
     "C2": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref"),
     "C2-noshade": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none"),
+    # C2 with sparse (foveated) sampling at the GUI's default focus (apps/main_app.cpp:122-124): ~9 % of the pixels per frame
+    "C2-sparse": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref", sparse=True),
     "C3": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref"),
     "C4": dict(n=1024, width=1920, height=1080, tf="pt", camera="front", rate=1.0, mode="pathtrace", shading="ref"),
     # sort-last: `n` is the edge of ONE brick; N ranks render a (grid * n)^3-ish volume, 4K frame, no shading
