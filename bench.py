@@ -92,10 +92,21 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def workload_scene(name):
+def workload_scene(name, cuda_device=None):
     import ovr_b200
-    w = dict(ovr_b200.scenes.WORKLOADS[name])
-    scene = ovr_b200.scenes.noise_scene(w["n"], tf=w["tf"], camera=w["camera"], rate=w["rate"])
+    S = ovr_b200.scenes
+    w = dict(S.WORKLOADS[name])
+    scene = S.noise_scene(w["n"], tf=w["tf"], camera=w["camera"], rate=w["rate"])
+    if w.get("dtype") == "u8" and cuda_device is not None:
+        # typed workload: the device generates noise(n), the host quantises it to 8 bits and hands it back as a u8 volume
+        r0 = ovr_b200.create_renderer("b200", cuda_device)
+        r0.set_fbsize((8, 8))
+        r0.init(scene, scene.camera)
+        vol = np.empty((w["n"],) * 3, np.float32)
+        r0._ck(ovr_b200.capi.lib().b200vr_download_volume(r0.handle, vol.ctypes.data_as(C.c_void_p)))
+        r0.close()
+        data = np.rint(vol * np.float32(255.0)).astype(np.uint8)
+        scene = S.Scene(S.Volume(data), S.make_tfn(w["tf"], value_range=(1.0, -1.0)), scene.camera, w["rate"])
     return w, scene
 
 
@@ -218,7 +229,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = capi.lib()
     from ovr_b200 import distributed as D
-    wl, scene = workload_scene(args.workload)
+    wl, scene = workload_scene(args.workload, local_rank)
     W, H = wl["width"], wl["height"]
     sortlast = bool(wl.get("sortlast"))
     brick = None

@@ -43,6 +43,7 @@ struct b200vr {
   float data_lo = 0.f, data_hi = 0.f; // original_value_range (volume.cpp:187-189)
   bool has_volume = false;
   int vol_type = B200VR_TYPE_FLOAT; // texture element type as the reference would hold it (array.cpp:322-351)
+  bool tex_native8 = false;         // the 3-D array holds the original 8-bit voxels (cudaReadModeNormalizedFloat)
   // macrocells
   i3 mc = { 0, 0, 0 };
   float2* ranges = nullptr;
@@ -257,14 +258,24 @@ static int rebuild_majorants(b200vr_t* h);
 
 // h->lin holds nx*ny*nz fp32 voxels: build the 3-D array + texture (array.cpp:287-309, cuda_buffer.h:248-331) and the
 // macrocell ranges / global range (sp_singlemc.cu:99-120, array.cpp:27-66)
-static int finish_volume(b200vr_t* h, const float obj_to_world[12])
+// native8: device copy of the original 8-bit voxels (or nullptr). The reference keeps 8-bit volumes as 8-bit 3-D arrays read
+// through cudaReadModeNormalizedFloat (array.cpp:300-306); so does this device: a 32-byte sector of the texture then holds four
+// times as many texels, which is what the L1TEX tag stage (4 sectors/clk/SM, the limiter of the march kernels, DESIGN.md
+// section 5) and HBM see. B200VR_TEX_NATIVE8=0 forces the fp32 array (A/B runs). The fp32 copy `lin` is kept either way.
+static int finish_volume(b200vr_t* h, const float obj_to_world[12], const void* native8 = nullptr, bool native8_signed = false)
 {
-  const cudaChannelFormatDesc desc = cudaCreateChannelDesc<float>();
+  if (const char* e = std::getenv("B200VR_TEX_NATIVE8"))
+    if (std::atoi(e) == 0) native8 = nullptr;
+  const cudaChannelFormatDesc desc = !native8 ? cudaCreateChannelDesc<float>()
+                                     : native8_signed ? cudaCreateChannelDesc<signed char>() : cudaCreateChannelDesc<unsigned char>();
   const cudaExtent ext = make_cudaExtent((size_t)h->nx, (size_t)h->ny, (size_t)h->nz);
   CK(cudaMalloc3DArray(&h->array, &desc, ext));
   cudaMemcpy3DParms cp;
   std::memset(&cp, 0, sizeof(cp));
-  cp.srcPtr = make_cudaPitchedPtr(h->lin, (size_t)h->nx * sizeof(float), (size_t)h->nx, (size_t)h->ny);
+  if (native8)
+    cp.srcPtr = make_cudaPitchedPtr(const_cast<void*>(native8), (size_t)h->nx, (size_t)h->nx, (size_t)h->ny);
+  else
+    cp.srcPtr = make_cudaPitchedPtr(h->lin, (size_t)h->nx * sizeof(float), (size_t)h->nx, (size_t)h->ny);
   cp.dstArray = h->array;
   cp.extent = ext;
   cp.kind = cudaMemcpyDeviceToDevice;
@@ -277,9 +288,10 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12])
   std::memset(&td, 0, sizeof(td));
   td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
   td.filterMode = cudaFilterModeLinear;
-  td.readMode = cudaReadModeElementType;
+  td.readMode = native8 ? cudaReadModeNormalizedFloat : cudaReadModeElementType;
   td.normalizedCoords = 1;
   CK(cudaCreateTextureObject(&h->tex, &rd, &td, nullptr));
+  h->tex_native8 = native8 != nullptr;
 
   h->otw = from_3x4(obj_to_world);
   h->wto = inverse(h->otw);
@@ -318,8 +330,9 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12])
   return B200VR_OK;
 }
 
+// keep != nullptr: the device copy of the typed voxels is handed back (*keep, *owned says whether the caller frees it)
 template<typename T>
-static int upload_typed(b200vr_t* h, const void* voxels, size_t n, int on_device)
+static int upload_typed(b200vr_t* h, const void* voxels, size_t n, int on_device, const void** keep = nullptr, bool* owned = nullptr)
 {
   const T* src = (const T*)voxels;
   T* staged = nullptr;
@@ -331,7 +344,11 @@ static int upload_typed(b200vr_t* h, const void* voxels, size_t n, int on_device
   convert_kernel<T><<<grid_for(n, 256, h->sm_count), 256, 0, h->stream>>>(h->lin, src, n);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));
-  if (staged) CK(cudaFree(staged));
+  if (keep) {
+    *keep = src;
+    *owned = staged != nullptr;
+  }
+  else if (staged) CK(cudaFree(staged));
   return B200VR_OK;
 }
 
@@ -346,6 +363,8 @@ extern "C" int b200vr_set_volume(b200vr_t* h, const void* voxels, int type, int 
   const size_t n = (size_t)nx * ny * nz;
   CK(cudaMalloc(&h->lin, n * sizeof(float)));
   int rc = B200VR_OK;
+  const void* native8 = nullptr;
+  bool native8_owned = false;
   // 16-bit integers and doubles are converted to plain floats by the reference; 8/32-bit integers stay normalised
   h->vol_type = (type == B200VR_TYPE_UINT16 || type == B200VR_TYPE_INT16 || type == B200VR_TYPE_DOUBLE) ? B200VR_TYPE_FLOAT : type;
   switch (type) {
@@ -353,8 +372,8 @@ extern "C" int b200vr_set_volume(b200vr_t* h, const void* voxels, int type, int 
     CK(cudaMemcpyAsync(h->lin, voxels, n * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
                        h->stream));
     break;
-  case B200VR_TYPE_UINT8: rc = upload_typed<uint8_t>(h, voxels, n, on_device); break;
-  case B200VR_TYPE_INT8: rc = upload_typed<int8_t>(h, voxels, n, on_device); break;
+  case B200VR_TYPE_UINT8: rc = upload_typed<uint8_t>(h, voxels, n, on_device, &native8, &native8_owned); break;
+  case B200VR_TYPE_INT8: rc = upload_typed<int8_t>(h, voxels, n, on_device, &native8, &native8_owned); break;
   case B200VR_TYPE_UINT16: rc = upload_typed<uint16_t>(h, voxels, n, on_device); break;
   case B200VR_TYPE_INT16: rc = upload_typed<int16_t>(h, voxels, n, on_device); break;
   case B200VR_TYPE_UINT32: rc = upload_typed<uint32_t>(h, voxels, n, on_device); break;
@@ -363,7 +382,9 @@ extern "C" int b200vr_set_volume(b200vr_t* h, const void* voxels, int type, int 
   default: return fail(h, B200VR_EINVAL, "set_volume: unknown value type"); // array.cpp:347
   }
   if (rc != B200VR_OK) return rc;
-  return finish_volume(h, obj_to_world);
+  rc = finish_volume(h, obj_to_world, native8, type == B200VR_TYPE_INT8); // synchronises the stream before it returns
+  if (native8_owned) cudaFree(const_cast<void*>(native8));
+  return rc;
 }
 
 extern "C" int b200vr_set_volume_noise(b200vr_t* h, uint32_t seed, const int32_t org[3], int nx, int ny, int nz,

@@ -205,6 +205,10 @@ __global__ void tile_order_kernel(const unsigned int* __restrict__ cost, int n_o
       for (int b = 0; b < 10; b++) z |= ((x >> b) & 1u) << (2 * b) | ((y >> b) & 1u) << (2 * b + 1);
       return (unsigned long long)(1048575u - z);
     }
+    if (mode == 4 || mode == 5) { // column-major (4: bottom-up, 5: top-down): tiles in flight form a vertical strip of the image
+      const unsigned int x = (unsigned int)(s % super_w), y = (unsigned int)(s / super_w);
+      return (unsigned long long)(1048575u - (x * (unsigned int)super_h + (mode == 4 ? y : (unsigned int)super_h - 1u - y)));
+    }
     return ((unsigned long long)(mode == 2 ? cost[m] : 0u) << 20) | (unsigned long long)(1048575u - d);
   };
   const unsigned long long ki = key(i);

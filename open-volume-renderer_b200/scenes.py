@@ -138,6 +138,9 @@ WORKLOADS = {
     "C2-noshade": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none"),
     # C2 with sparse (foveated) sampling at the GUI's default focus (apps/main_app.cpp:122-124): ~9 % of the pixels per frame
     "C2-sparse": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref", sparse=True),
+    # C2 on 8-bit data (the bundled engine / teapot / bonsai scenes are UNSIGNED_BYTE): noise(512) quantised to u8, kept as an
+    # 8-bit 3-D array like the reference does (array.cpp:300-306); B200VR_TEX_NATIVE8=0 renders the same voxels from an fp32 array
+    "C2-u8": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref", dtype="u8"),
     "C3": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref"),
     "C4": dict(n=1024, width=1920, height=1080, tf="pt", camera="front", rate=1.0, mode="pathtrace", shading="ref"),
     # sort-last: `n` is the edge of ONE brick; N ranks render a (grid * n)^3-ish volume, 4K frame, no shading

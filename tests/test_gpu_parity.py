@@ -627,3 +627,47 @@ def test_sparse_sampling_default_table_and_refusals():
         r.set_focus((0.5, 0.5), 0.0, 0.07)  # focus_scale must be positive
         r.commit()
     r.close()
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int8])
+def test_native_8bit_texture_matches_the_fp32_array(dtype):
+    """8-bit volumes are kept as 8-bit 3-D arrays read through cudaReadModeNormalizedFloat, like the reference does
+    (array.cpp:300-306). Same voxels rendered from an fp32 array (B200VR_TEX_NATIVE8=0) and by the oracle: the unit converts
+    the texels itself, so the two device paths may differ in the last bits, far inside the 1/255 tolerance."""
+    base = pyoracle.noise(40, 5)
+    if dtype == np.uint8:
+        data = np.rint(base * 255).astype(np.uint8)
+        as_f32 = data.astype(np.float32) / np.float32(255)
+    else:
+        data = np.rint(base * 254 - 127).astype(np.int8)
+        as_f32 = np.maximum(data.astype(np.float32) / np.float32(127), np.float32(-1))
+    sc = S.Scene(S.Volume(data), S.make_tfn("sparse", value_range=(1.0, -1.0)), S.camera_preset("oblique", (40, 40, 40)))
+    frames = {}
+    for native in ("1", "0"):
+        os.environ["B200VR_TEX_NATIVE8"] = native
+        try:
+            r = make_renderer(sc, 160, 96)
+            r.render()
+            frames[native] = r.download()
+            pts = np.random.default_rng(3).uniform(-0.05, 1.05, (4096, 3)).astype(np.float32)
+            frames["probe" + native] = probe(r, pts, capi.SAMPLER_TEX3D, want_rgba=False)[0]
+            assert np.array_equal(device_volume(r, (40, 40, 40)), as_f32)
+            r.close()
+        finally:
+            del os.environ["B200VR_TEX_NATIVE8"]
+    sc_f = S.Scene(S.Volume(as_f32), sc.tfn, sc.camera)
+    o = pyoracle.OracleScene(oracle_desc(sc_f, 160, 96, tf_range=(float(as_f32.min()), float(as_f32.max()))), skip_empty=True).render_march()[0]
+    # The 8-bit filter path of the unit is less precise than the fp32 one (fetches differ by ~1e-5, printed below). A pixel whose
+    # only samples sit within that distance of the TF's opacity threshold gets A ~ 1e-5 on one path and exactly 0 on the other;
+    # alpha_blend's C / A (shaders_common.h:329-337) then turns an invisible difference into a full-scale colour. The native
+    # frame is therefore compared as displayed, colour * A over the black background; the fp32-array frame as stored.
+    def displayed(f):
+        return np.concatenate([f[..., :3] * f[..., 3:4], f[..., 3:4]], axis=-1)
+
+    e_native, e_f32 = max_abs(displayed(frames["1"][0]), displayed(o)), max_abs(frames["0"][0], o)
+    d_probe = float(np.abs(frames["probe1"] - frames["probe0"]).max())
+    print(f"{np.dtype(dtype).name}: native-8 vs oracle {e_native:.2e}, fp32 array vs oracle {e_f32:.2e}, native vs fp32 frame "
+          f"{max_abs(frames['1'][0], frames['0'][0]):.2e}, fetches {d_probe:.2e}")
+    assert (o[..., 3] > 0).mean() > 0.05
+    assert e_native <= TOL and e_f32 <= TOL and psnr(displayed(frames["1"][0]), displayed(o)) >= 45.0
+    assert d_probe <= 2.0 ** -12  # texel conversion + filter arithmetic of the 8-bit path: well below one 8-bit grey level
