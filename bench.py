@@ -451,6 +451,21 @@ def main():
                        "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                        "samples_per_frame": ctx["samples"] / args.steps, "fetches_per_frame": ctx["fetches"] / args.steps},
             "clocks": ctx["clk"], "e2e": e2e, "gpu_launches": ctx["gpu_launches"], "roofline": roofline}
+    if world == 1 and not wl.get("sortlast") and not wl.get("sparse") and not args.no_skip:
+        # Msamples/s is reported twice -- `value` counts the samples this device executed; the reference-
+        # equivalent figure counts the samples the reference's unskipped algorithm takes for the same frame (one extra frame
+        # with empty-space skipping off: the image is bit-identical, only the counters differ), over the same frame time
+        r.set_camera(ctx["scene"].camera)
+        r.commit()
+        r.skip_empty = False
+        r.apply_device_options()
+        r.render()
+        st = r.last_stats
+        s_ref = st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
+        r.skip_empty = True
+        r.apply_device_options()
+        line["config"]["samples_per_frame_reference_equivalent"] = s_ref
+        line["value_reference_equivalent"] = s_ref / (ctx["t_ms"] / args.steps * 1e-3) / 1e6
     if world == 1 and not args.no_cpu_baseline and n <= 1024:   # the CPU port needs the whole volume on the host
         from oracle import pyoracle
         vol = np.empty((n, n, n), np.float32)
