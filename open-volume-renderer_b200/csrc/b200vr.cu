@@ -685,7 +685,11 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   // Per-warp queue kernel (march_q.cuh) or queue + work-sharing rings (march_ring.cuh). Measured on C2: the whole frame on
   // one GPU 2.29 vs 2.65 ms (the rings cost ~8 % more instructions), an eighth of its tiles 1.06-1.50 vs 0.80-1.13 ms (the
   // heaviest warp tile alone takes ~1 ms with the queue kernel): rings when the frame is split sort-first, queue otherwise.
-  const bool q = force ? std::strcmp(force, "q") == 0 : h->nranks == 1;
+  // Sparse (foveated) frames keep the heavy tiles around the focus and drop most of the light ones: the launch is as long as
+  // its heaviest warp tile with the queue kernel (C2-sparse 1.59 ms for a quarter of the samples), so they take the rings too.
+  // Not while accumulating: resolve_kernel rewrites every pixel, the reference leaves unsampled pixels untouched then.
+  const bool sparse_ring = h->sparse && !p.accumulate;
+  const bool q = force ? std::strcmp(force, "q") == 0 : (h->nranks == 1 && !sparse_ring);
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
@@ -972,7 +976,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   const KernelChoice kc = pick_kernel(h);
   int sparse_launches = 0;
   if (h->sparse) {
-    if (kc.ring || h->nranks != 1 || h->has_lattice || h->target_rgba)
+    if ((kc.ring && h->prm.accumulate) || h->nranks != 1 || h->has_lattice || h->target_rgba)
       return fail(h, B200VR_ESTATE, "render: sparse sampling is a single-device mode (no tile partition, brick or frame target)");
     const int rc = build_sparse_list(h, P, sparse_launches);
     if (rc != B200VR_OK) return rc;
@@ -987,7 +991,8 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     per_sm = std::max(1, std::min(per_sm, std::atoi(cap)));
   const int warps_per_cta = kc.threads / 32;
   const int want = (P.n_warp_tiles + warps_per_cta - 1) / warps_per_cta;
-  const int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
+  int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
+  if (kc.ring && P.sparse_xy) grid = h->sm_count * per_sm;      // few tiles, all heavy: warps without a tile shade published blocks
   CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
   CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
   {
@@ -1037,8 +1042,10 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     launches = 1;
   }
   else if (P.n_warp_tiles > 0) {
-    const int n_owned = P.n_warp_tiles / WARP_TILES_PER_SUPER;
+    // sparse frame: the list covers the image, resolve_kernel rewrites every pixel (unsampled ones: sums 0, opacity 0 -> 0)
+    const int n_owned = P.sparse_xy ? P.super_w * P.super_h : P.n_warp_tiles / WARP_TILES_PER_SUPER;
     for (int sidx = 0; sidx < P.spp; sidx++) { // one march + one resolve per sample of the pixel
+      if (P.sparse_xy) CK(cudaMemsetAsync(h->ray_alpha, 0, (size_t)h->width * h->height * sizeof(float), h->stream));
       P.sidx = sidx;
       if (sidx > 0) CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
       ring_start_kernel<<<(grid + 127) / 128, 128, 0, h->stream>>>(h->ring_ctrl, RING_CTRL_STRIDE, grid, warps_per_cta);

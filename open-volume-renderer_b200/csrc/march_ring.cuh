@@ -128,10 +128,9 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
         }
         continue;
       }
-      int px, py;
-      tile_slot = warp_tile_origin(P, k, px, py);
+      int ix, iy;
+      tile_slot = warp_tile_pixel(P, k, lane, ix, iy);
       tile_t0 = clock64();
-      const int ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
       inside = ix < P.width && iy < P.height;
       pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
       // ---- ray generation + clip (shaders_common.h:400-404, shaders_raymarching.cu:351-362, shaders_common.h:156-184) ----

@@ -518,7 +518,8 @@ def _check_mask_against_oracle(got, want, p, table, tile, fi, w, h):
 
 
 SPARSE_GPU_CASES = [
-    # name, shading, path tracing, sampler
+    # name, shading, path tracing, sampler  ("ref-ring": the default for shaded sparse frames; "ref-queue": B200VR_KERNEL=q)
+    ("ref-ring", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
     ("ref-queue", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
     ("none-lean", capi.SHADING_NONE, False, capi.SAMPLER_TEX3D),
     ("ref-manual", capi.SHADING_REF, False, capi.SAMPLER_MANUAL),
@@ -534,6 +535,19 @@ def test_sparse_sampling_renders_exactly_the_masked_pixels(case):
     name, shading, path, sampler = case
     W, H, tile = 203, 117, 16  # ragged: not multiples of the 8x4 / 64x32 tiles
     sc = S.noise_scene(48, tf="pt" if path else "sparse", camera="front" if path else "oblique")
+    # shaded sparse frames go through the work-sharing ring kernel (fixed-point per-pixel sums: bit-identical for any split of
+    # the work, within 1e-3 of the queue kernel); the dense frame to compare with comes from the same kernel
+    force = {"ref-ring": "ring", "ref-queue": "q"}.get(name)
+    if force:
+        os.environ["B200VR_KERNEL"] = force
+    try:
+        _sparse_case_body(name, shading, path, sampler, W, H, tile, sc)
+    finally:
+        os.environ.pop("B200VR_KERNEL", None)
+
+
+def _sparse_case_body(name, shading, path, sampler, W, H, tile, sc):
+    from helpers import sparse_noise_table
     rd = make_renderer(sc, W, H, shading=shading, sampler=sampler, path=path)
     rd.render()
     dense_rgba, dense_grad = rd.download()
