@@ -209,6 +209,12 @@ __global__ void tile_order_kernel(const unsigned int* __restrict__ cost, int n_o
       const unsigned int x = (unsigned int)(s % super_w), y = (unsigned int)(s / super_w);
       return (unsigned long long)(1048575u - (x * (unsigned int)super_h + (mode == 4 ? y : (unsigned int)super_h - 1u - y)));
     }
+    if (mode == 6) { // whole rows of super tiles, middle row first, then alternating outwards: row-major locality inside a row,
+                     // the (usually heavy) middle of the image no longer starts halfway through the launch
+      const int x = s % super_w, y = s / super_w, mid = super_h / 2;
+      const int d2 = y >= mid ? 2 * (y - mid) : 2 * (mid - y) - 1;
+      return (unsigned long long)(1048575u - (unsigned int)(d2 * super_w + x));
+    }
     return ((unsigned long long)(mode == 2 ? cost[m] : 0u) << 20) | (unsigned long long)(1048575u - d);
   };
   const unsigned long long ki = key(i);

@@ -52,3 +52,22 @@ def test_scene_geometry():
     v = S.Volume(np.zeros((4, 6, 8), np.uint8), grid_origin=(1, 2, 3), grid_spacing=(2, 2, 2))
     assert v.dims == (8, 6, 4)
     assert np.array_equal(v.obj_to_world(), np.array([16, 0, 0, 1, 0, 12, 0, 2, 0, 0, 8, 3], np.float32))
+
+
+def test_sparse_enumeration_visits_every_pixel_once():
+    """sparse.cuh lists the kept pixels in the order the render kernels walk the image (super tile -> 2 x 2 blocks of 4 x 4 warp
+    tiles -> 8 x 4 pixels), not row-major: same arithmetic as sparse_entry_pixel, checked to be a bijection onto the image plus
+    padding beyond the right / top edge, with the 32 entries of a warp tile forming one 8 x 4 block."""
+    for (w, h) in [(203, 117), (1920, 1080), (64, 32), (7, 3)]:
+        sw, sh = super_tiles(w, h)
+        e = np.arange(sw * sh * 2048)
+        s, r = e // 2048, e % 2048
+        t, lane = r >> 5, r & 31
+        b, i = t // 16, t % 16
+        x = (s % sw) * 64 + ((b & 1) * 4 + (i & 3)) * 8 + (lane & 7)
+        y = (s // sw) * 32 + ((b >> 1) * 4 + (i >> 2)) * 4 + lane // 8
+        inside = (x < w) & (y < h)
+        flat = (x + y * w)[inside]
+        assert len(flat) == w * h and len(np.unique(flat)) == w * h
+        xt, yt = x.reshape(-1, 32), y.reshape(-1, 32)
+        assert (xt.max(1) - xt.min(1) == 7).all() and (yt.max(1) - yt.min(1) == 3).all()
