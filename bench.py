@@ -411,10 +411,25 @@ def main():
     p_fetch, fetch_rows = measure_fetch_peak(r, capi, r.sampler)
     pk = peaks()
     n = wl["n"]
+    r_dims = tuple(int(v) for v in (ctx["scene"].volume.dims if world == 1 or not wl.get("sortlast") else (n, n, n)))
+    if wl.get("sortlast"):
+        r_dims = (n, n, n)   # this rank's brick
     kernel_s = ctx["kernel_ms"] * 1e-3
     ach = 32.0 * ctx["fetches"] / world / kernel_s / 1e9 if kernel_s > 0 else 0.0   # per GPU: rank-max kernel time
     peak = 32.0 * p_fetch / 1e9
-    hbm_bytes = 4.0 * n ** 3 + 12.0 * ((n + 15) // 16) ** 3 + 28.0 * wl["width"] * wl["height"]
+    # compulsory HBM bytes per frame: 4 B x voxels of the macrocells a fetch can touch + 12 B per macrocell + the
+    # frame stores. With skipping on, only cells whose majorant is not 0 are ever fetched from (a superset of the cells the
+    # rays reach before they terminate); the whole volume is the bound without skipping.
+    mcd = (C.c_int32 * 3)()
+    r._ck(capi.lib().b200vr_get_macrocells(r.handle, mcd, None, None))
+    n_cells = mcd[0] * mcd[1] * mcd[2]
+    maj = np.empty(n_cells, np.float32)
+    r._ck(capi.lib().b200vr_get_macrocells(r.handle, mcd, None, maj.ctypes.data_as(C.c_void_p)))
+    live_cells = int(np.count_nonzero(maj)) if not args.no_skip else n_cells
+    vox_per_cell = (r_dims[0] * r_dims[1] * r_dims[2]) / n_cells
+    frame_bytes = (28.0 + (32.0 if wl["mode"] != "raymarch" else 0.0)) * wl["width"] * wl["height"]
+    hbm_bytes_whole = 4.0 * r_dims[0] * r_dims[1] * r_dims[2] + 12.0 * n_cells + frame_bytes
+    hbm_bytes = 4.0 * vox_per_cell * live_cells + 12.0 * n_cells + frame_bytes
     hbm_ach = hbm_bytes * args.steps / kernel_s / 1e9 if kernel_s > 0 else 0.0
     if wl["mode"] != "raymarch":
         kernel_name = "pathtrace_kernel"
@@ -439,7 +454,8 @@ def main():
                         "stream); peak = best b200vr_bench_fetch rate x 32 B measured in this run",
                 "kernel_ms_per_launch": ctx["kernel_ms"] / args.steps, "fetch_bench": fetch_rows,
                 "hbm": {"achieved": hbm_ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_ach / pk["hbm_gbs"],
-                        "bytes_per_launch_upper_bound": hbm_bytes, "peak_source": pk["source"]}}
+                        "bytes_per_launch": hbm_bytes, "live_macrocells": live_cells, "macrocells": n_cells,
+                        "bytes_per_launch_whole_volume": hbm_bytes_whole, "peak_source": pk["source"]}}
     line = {"metric": METRIC, "value": ctx["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ctx["t_ms"] / args.steps, "higher_is_better": True, "scaling": "weak" if wl.get("sortlast") else "strong",
             "vs_baseline": None, "dtype": "f32",

@@ -142,6 +142,8 @@ WORKLOADS = {
     # 8-bit 3-D array like the reference does (array.cpp:300-306); B200VR_TEX_NATIVE8=0 renders the same voxels from an fp32 array
     "C2-u8": dict(n=512, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref", dtype="u8"),
     "C3": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref"),
+    "C3-u8": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref", dtype="u8"),
+    "C3-noshade": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none"),
     "C4": dict(n=1024, width=1920, height=1080, tf="pt", camera="front", rate=1.0, mode="pathtrace", shading="ref"),
     # sort-last: `n` is the edge of ONE brick; N ranks render a (grid * n)^3-ish volume, 4K frame, no shading
     "C5": dict(n=2048, width=3840, height=2160, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none", sortlast=True),
