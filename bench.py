@@ -428,8 +428,10 @@ def main():
     live_cells = int(np.count_nonzero(maj)) if not args.no_skip else n_cells
     vox_per_cell = (r_dims[0] * r_dims[1] * r_dims[2]) / n_cells
     frame_bytes = (28.0 + (32.0 if wl["mode"] != "raymarch" else 0.0)) * wl["width"] * wl["height"]
-    hbm_bytes_whole = 4.0 * r_dims[0] * r_dims[1] * r_dims[2] + 12.0 * n_cells + frame_bytes
-    hbm_bytes = 4.0 * vox_per_cell * live_cells + 12.0 * n_cells + frame_bytes
+    # bytes per voxel in the 3-D array the kernels fetch from: 8-bit volumes stay 8-bit (B200VR_TEX_NATIVE8=0: fp32 array)
+    bpv = 1.0 if wl.get("dtype") == "u8" and os.environ.get("B200VR_TEX_NATIVE8", "1") != "0" else 4.0
+    hbm_bytes_whole = bpv * r_dims[0] * r_dims[1] * r_dims[2] + 12.0 * n_cells + frame_bytes
+    hbm_bytes = bpv * vox_per_cell * live_cells + 12.0 * n_cells + frame_bytes
     hbm_ach = hbm_bytes * args.steps / kernel_s / 1e9 if kernel_s > 0 else 0.0
     if wl["mode"] != "raymarch":
         kernel_name = "pathtrace_kernel"
