@@ -61,8 +61,28 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
+        self.nvml_rows, self._stop, self._thr = [], False, None
+
+    def _nvml_loop(self):
+        # NVML in-process: a sample every ~2 ms, so that even a 30 ms timed region (8 GPUs, 25 frames) is covered;
+        # the nvidia-smi process below stays as the second source (its first line arrives after ~100 ms)
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+            while not self._stop:
+                sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
+                bits = N.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(N, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.nvml_rows.append((float(sm), float(mx), int(bits)))
+                time.sleep(0.002)
+        except Exception:
+            pass
 
     def start(self):
+        self._thr = threading.Thread(target=self._nvml_loop, daemon=True)
+        self._thr.start()
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -75,11 +95,22 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        self._stop = True
+        if self._thr is not None:
+            self._thr.join(timeout=1.0)
+        sm, mx, reasons = [], [], set()
+        for a, b, bits in self.nvml_rows:   # nvml.h: HwSlowdown 0x8, SwPowerCap 0x4, SwThermalSlowdown 0x20, HwThermalSlowdown 0x40
+            sm.append(a), mx.append(b)
+            for name, bit in (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)):
+                if bits & bit:
+                    reasons.add(name)
         if self.proc is None:
+            if sm:
+                return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                        "source": "nvml"}
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        sm, mx, reasons = [], [], set()
         for r in self.rows:
             try:
                 sm.append(float(r[0])), mx.append(float(r[1]))
@@ -353,19 +384,30 @@ def run_e2e(ctx, args):
 
     copy_stream = torch.cuda.Stream()
 
+    phases = [0.0] * 5   # host seconds per phase, printed with B200VR_BENCH_DEBUG=1
+
     def e2e_step(k):
         # the GUI loop of apps/main_app.cpp:244-263: commit -> mapframe (frame k-1) -> swap -> render (frame k). The
         # device->host copy of frame k-1 runs on its own stream while frame k renders into the other buffer; both are
         # complete before the step returns. (Under sort-first, rank 0 copies the gathered frame.)
+        t = [time.perf_counter()]
         r.set_camera(orbit_camera(scene, k, args.steps))
         r.set_transfer_function(c, o, tuple(tfn.value_range))
+        t.append(time.perf_counter())
         r.commit()
+        t.append(time.perf_counter())
         if rank == 0:
             r._ck(L.b200vr_download_async(r.handle, C.c_void_p(rgba_host.data_ptr()), C.c_void_p(grad_host.data_ptr()),
                                           C.c_void_p(copy_stream.cuda_stream)))
         r.swap()
+        t.append(time.perf_counter())
         st = ctx["step"]()
+        t.append(time.perf_counter())
         copy_stream.synchronize()
+        t.append(time.perf_counter())
+        for i in range(5):
+            phases[i] += t[i + 1] - t[i]
+        phases.append(st["ms"])
         return st
 
     for k in range(max(1, min(args.warmup, 3))):
@@ -383,6 +425,10 @@ def run_e2e(ctx, args):
     ev1.record(ctx["stream"])
     ctx["barrier"]()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    if os.environ.get("B200VR_BENCH_DEBUG") and rank == 0:
+        n_calls = args.steps + max(1, min(args.warmup, 3))
+        print("[bench] e2e host ms per step: setters %.3f commit %.3f copy-enqueue+swap %.3f render %.3f copy-wait %.3f" %
+              tuple(1e3 * p / n_calls for p in phases[:5]), "kernel ms (device events) %.3f" % (sum(phases[5:]) / n_calls), file=sys.stderr)
     t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
     s = torch.tensor([samples], dtype=torch.float64, device="cuda")
     if world > 1:
