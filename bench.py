@@ -61,7 +61,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
-        self.nvml_rows, self._stop, self._thr = [], False, None
+        self.nvml_rows, self._stop, self._thr, self.nvml_error = [], False, None, None
 
     def _nvml_loop(self):
         # NVML in-process: a sample every ~2 ms, so that even a 30 ms timed region (8 GPUs, 25 frames) is covered;
@@ -73,12 +73,14 @@ class ClockSampler:
             mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
             while not self._stop:
                 sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
-                bits = N.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(N, "nvmlDeviceGetCurrentClocksEventReasons") \
-                    else N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                try:
+                    bits = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                except Exception:
+                    bits = 0
                 self.nvml_rows.append((float(sm), float(mx), int(bits)))
                 time.sleep(0.002)
-        except Exception:
-            pass
+        except Exception as e:
+            self.nvml_error = repr(e)
 
     def start(self):
         self._thr = threading.Thread(target=self._nvml_loop, daemon=True)
