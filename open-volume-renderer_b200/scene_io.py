@@ -57,10 +57,45 @@ def write_vidi3d_scene(json_path, data, alpha, color_controls, camera, sample_di
     return json_path
 
 
+def _strip_json_comments(text):
+    """The reference parses with nlohmann's ignore_comments (json::parse(text, nullptr, true, true),
+    serializer_vidi3d.cpp:417): // and /* */ comments outside strings are skipped. Two bundled configs rely on it."""
+    out, i, n, in_str = [], 0, len(text), False
+    while i < n:
+        c = text[i]
+        if in_str:
+            out.append(c)
+            if c == "\\" and i + 1 < n:
+                out.append(text[i + 1])
+                i += 1
+            elif c == '"':
+                in_str = False
+        elif c == '"':
+            in_str = True
+            out.append(c)
+        elif c == "/" and i + 1 < n and text[i + 1] == "/":
+            while i < n and text[i] != "\n":
+                i += 1
+            continue
+        elif c == "/" and i + 1 < n and text[i + 1] == "*":
+            j = text.find("*/", i + 2)
+            i = n if j < 0 else j + 2
+            out.append(" ")
+            continue
+        else:
+            out.append(c)
+        i += 1
+    return "".join(out)
+
+
+def load_json_with_comments(json_path):
+    with open(json_path) as f:
+        return json.loads(_strip_json_comments(f.read()))
+
+
 def read_vidi3d_scene(json_path, payload=None):
     """-> scenes.Scene. `payload` overrides the raw file (bundled configs reference blobs that are not shipped)."""
-    with open(json_path) as f:
-        root = json.load(f)
+    root = load_json_with_comments(json_path)
     ds, view = root["dataSource"][0], root["view"]
     dims = ds["dimensions"]
     nx, ny, nz = int(dims["x"]), int(dims["y"]), int(dims["z"])
