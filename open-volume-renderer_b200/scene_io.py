@@ -93,6 +93,47 @@ def load_json_with_comments(json_path):
         return json.loads(_strip_json_comments(f.read()))
 
 
+def transfer_function_table(jt):
+    """tfn::loadTransferFunction + updateColorMap (extern/tfn/core.h:711-760, 598-634, 344-378, 652-685) restated: the RGBA
+    table create_scene_tfn reads (serializer_vidi3d.cpp:210-221). `jt` is the "transferFunction" object. Entry i:
+    colour from the colour controls at (i + 0.5) / n; alpha = max(alphaArray[i], every Gaussian object at (i + 0.5) / n
+    clamped to [0, 1], the opacity-control polyline at i / (n - 1)). Returns (color [n, 4] with w = 1, alpha [n])."""
+    f32 = np.float32
+    n = int(jt.get("resolution", 1024))
+    alpha = None
+    aa = jt.get("alphaArray")
+    if aa and "data" in aa and aa.get("encoding") == "BASE64":
+        alpha = np.frombuffer(base64.b64decode(aa["data"]), "<f4").astype(f32).copy()
+        n = len(alpha)
+    if alpha is None:
+        alpha = np.zeros(n, f32)
+    controls = [(float(c["position"]), (float(c["color"]["r"]), float(c["color"]["g"]), float(c["color"]["b"])))
+                for c in jt.get("colorControls", []) if "position" in c and "color" in c]
+    color = rasterize_color_controls(controls or [(0.0, (0.0, 0.0, 0.0))], n)
+    x = (np.arange(n, dtype=f32) + f32(0.5)) * (f32(1.0) / f32(n))
+    for g in jt.get("gaussianObjects", []):
+        if not all(k in g for k in ("mean", "sigma", "heightFactor")):
+            continue
+        mean, sigma, hf = f32(g["mean"]), f32(g["sigma"]), f32(g["heightFactor"])
+        diff = x - mean
+        val = hf / (sigma * np.sqrt(f32(2.0) * f32(np.pi))) * np.exp(-(diff * diff) / (f32(2.0) * sigma * sigma))
+        alpha = np.maximum(alpha, np.clip(val.astype(f32), f32(0), f32(1)))
+    oc = sorted(((float(c["position"]["x"]), float(c["position"]["y"])) for c in jt.get("opacityControl", []) if "position" in c),
+                key=lambda c: c[0])
+    if oc:
+        px, py = np.array([c[0] for c in oc], f32), np.array([c[1] for c in oc], f32)
+        value = np.arange(n, dtype=np.float64) / np.float64(n - 1)
+        ub = np.searchsorted(px, value.astype(f32), side="right")
+        lo, hi = np.clip(ub - 1, 0, len(oc) - 1), np.clip(ub, 0, len(oc) - 1)
+        span = np.abs(px[hi].astype(np.float64) - px[lo].astype(np.float64))
+        w = (np.abs(value - px[lo].astype(np.float64)) / np.where(span > 0, span, 1.0)).astype(f32)
+        a = (py[lo] + w * (py[hi] - py[lo])).astype(f32)
+        a[ub <= 0] = py[0]
+        a[ub >= len(oc)] = py[-1]
+        alpha = np.maximum(alpha, a)
+    return color, alpha.astype(f32)
+
+
 def read_vidi3d_scene(json_path, payload=None):
     """-> scenes.Scene. `payload` overrides the raw file (bundled configs reference blobs that are not shipped)."""
     root = load_json_with_comments(json_path)
@@ -114,10 +155,7 @@ def read_vidi3d_scene(json_path, payload=None):
         vol.grid_spacing = _xyz(ds["scales"])
     jv = view["volume"]
     jt = jv["transferFunction"]
-    alpha = np.frombuffer(base64.b64decode(jt["alphaArray"]["data"]), "<f4").astype(np.float32).copy()
-    controls = sorted(((float(c["position"]), (float(c["color"]["r"]), float(c["color"]["g"]), float(c["color"]["b"])))
-                       for c in jt.get("colorControls", [])), key=lambda c: c[0])
-    color = rasterize_color_controls(controls or [(0.0, (0.0, 0.0, 0.0))], len(alpha))
+    color, alpha = transfer_function_table(jt)
     if alpha[0] < 0.01:      # serializer_vidi3d.cpp:222-223
         alpha[0] = 0.0
     if alpha[-1] < 0.01:

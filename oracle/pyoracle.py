@@ -76,6 +76,20 @@ def ref_kat_lib():
     return L
 
 
+def ref_tfn_table(tfn_json_text, capacity=8192):
+    """The reference's own tfn::loadTransferFunction (oracle/_ref/libovr_ref_tfn.so, built where /root/reference exists):
+    (N, 4) float32 RGBA table of a VIDI3D "transferFunction" object; None when the library is not there."""
+    so = os.path.join(_HERE, "_ref", "libovr_ref_tfn.so")
+    if not os.path.exists(so):
+        return None
+    L = C.CDLL(so)
+    L.ref_tfn_table.restype = C.c_int
+    out = np.zeros((capacity, 4), np.float32)
+    n = L.ref_tfn_table(tfn_json_text.encode(), out.ctypes.data_as(C.POINTER(C.c_float)), capacity)
+    assert n > 0
+    return out[:n].copy()
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 

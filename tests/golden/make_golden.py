@@ -8,7 +8,9 @@ where /root/reference exists):
 
   sparse_mask.npz   sparse-sampling masks from the reference's own mask kernels run on the host (same shim)
 
-Usage: python tests/golden/make_golden.py [sparse]
+  tfn_tables.npz    RGBA tables of every bundled scene's transfer function from the reference's tfn::loadTransferFunction
+
+Usage: python tests/golden/make_golden.py [sparse|tfn]
 """
 import base64
 import ctypes as C
@@ -145,9 +147,39 @@ def make_sparse():
     np.savez_compressed(os.path.join(HERE, "sparse_mask.npz"), **out)
 
 
+def make_tfn():
+    """tfn_tables.npz: for every bundled data/configs/*.json its "transferFunction" object (text) and the RGBA table the
+    reference's tfn::loadTransferFunction builds from it (alpha array, colour controls, Gaussian objects, opacity controls),
+    plus two synthetic objects that exercise opacityControl and a missing alphaArray."""
+    import glob
+    from ovr_b200 import scene_io
+    pyoracle.build()
+    out, names = {}, []
+    cases = [(os.path.basename(p)[:-5], scene_io.load_json_with_comments(p)["view"]["volume"]["transferFunction"])
+             for p in sorted(glob.glob(os.path.join(REF, "data/configs/*.json")))]
+    cases.append(("synthetic_opacity_controls", {
+        "resolution": 256, "colorControls": [{"position": 0.2, "color": {"r": 1, "g": 0, "b": 0}},
+                                             {"position": 0.9, "color": {"r": 0, "g": 0.5, "b": 1}}],
+        "opacityControl": [{"position": {"x": 0.1, "y": 0.0}}, {"position": {"x": 0.5, "y": 0.8}}, {"position": {"x": 0.75, "y": 0.1}}],
+        "gaussianObjects": [{"mean": 0.3, "sigma": 0.02, "heightFactor": 0.03}]}))
+    cases.append(("synthetic_no_controls", {"resolution": 64, "gaussianObjects": [{"mean": 0.5, "sigma": 0.1, "heightFactor": 0.1}]}))
+    for name, tf in cases:
+        text = json.dumps(tf)
+        table = pyoracle.ref_tfn_table(text)
+        assert table is not None, "oracle/_ref/libovr_ref_tfn.so missing (needs /root/reference)"
+        names.append(name)
+        out[name + "_json"], out[name + "_table"] = np.array(text), table
+        print(f"tfn {name}: resolution {len(table)}, alpha max {table[:, 3].max():.4f}")
+    out["names"] = np.array(names)
+    np.savez_compressed(os.path.join(HERE, "tfn_tables.npz"), **out)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
+    elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
+        make_tfn()
     else:
         main()
         make_sparse()
+        make_tfn()

@@ -98,3 +98,28 @@ def test_sparse_mask_matches_reference_kernels():
         assert (p >= min(base, 1.0) - 1e-6).all() and (p <= 1.0 + 1e-6).all()
         kept.append(int(keep.sum()))
     assert kept[4] == 0 and 0 < kept[0] < 160 * 96 // 4  # empty list edge case; default focus keeps a small fraction
+
+
+def test_scene_file_transfer_functions_match_the_reference_loader():
+    """scene_io.transfer_function_table against tests/golden/tfn_tables.npz: the RGBA tables the reference's own
+    tfn::loadTransferFunction (extern/tfn/core.h, compiled on the host by oracle/ref_tfn_shim.cpp) builds for every bundled
+    scene config plus two synthetic objects (opacity controls, no alpha array). Alpha arrays and control colours are
+    bit-exact; interpolated colours and Gaussians (exp / sqrt through numpy instead of libm's float versions) to 2 ulp."""
+    import json
+
+    from ovr_b200 import scene_io
+    T = np.load(os.path.join(os.path.dirname(__file__), "golden", "tfn_tables.npz"))
+    names = [str(n) for n in T["names"]]
+    assert len(names) >= 20
+    n_gauss = 0
+    for name in names:
+        jt = json.loads(str(T[name + "_json"]))
+        want = T[name + "_table"]
+        color, alpha = scene_io.transfer_function_table(jt)
+        assert color.shape == (len(want), 4) and alpha.shape == (len(want),)
+        assert np.abs(color[:, :3] - want[:, :3]).max() <= 3e-7, name
+        assert np.abs(alpha - want[:, 3]).max() <= 3e-7, name
+        if not jt.get("gaussianObjects") and not jt.get("opacityControl"):
+            assert np.array_equal(alpha, want[:, 3]), name
+        n_gauss += bool(jt.get("gaussianObjects"))
+    assert n_gauss >= 10  # the bundled scenes that the alpha array alone does not describe
