@@ -147,6 +147,9 @@ def read_vidi3d_scene(json_path, payload=None):
         found = next((p for n in names for p in (n, os.path.join(base, n)) if os.path.exists(p)), None)
         if found is None:
             raise RuntimeError("Cannot find volume file.")  # serializer_vidi3d.cpp:188
+        offset = int(ds.get("offset", 0))
+        if os.path.getsize(found) < offset + nx * ny * nz * dtype.itemsize:
+            raise RuntimeError("File size does not match data size")  # CreateArray3DScalarFromFile, ovr/scene.cpp:207-212
         order = ">" if ds.get("endian", "LITTLE_ENDIAN") == "BIG_ENDIAN" else "<"
         payload = np.fromfile(found, dtype.newbyteorder(order), nx * ny * nz, offset=int(ds.get("offset", 0))).astype(dtype)
     data = np.ascontiguousarray(payload, dtype).reshape(nz, ny, nx)

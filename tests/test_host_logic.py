@@ -102,3 +102,35 @@ def test_every_bundled_scene_config_parses():
         if dtype.kind != "f":
             assert hi <= np.iinfo(dtype).max * 1.0001  # scalarMappingRange x type maximum (serializer_vidi3d.cpp:235-269)
     assert {"UNSIGNED_BYTE", "UNSIGNED_SHORT", "FLOAT"} <= seen
+
+
+def test_scene_file_payload_offset_endianness_and_errors(tmp_path):
+    """CreateArray3DScalarFromFile (ovr/scene.cpp:181-245): `offset` bytes are skipped, BIG_ENDIAN payloads are byte-swapped,
+    a file shorter than offset + data raises; `scales` becomes the grid spacing (serializer_vidi3d.cpp:298-301)."""
+    import json
+
+    import pytest
+    from ovr_b200 import scene_io
+    data = (np.arange(4 * 5 * 6, dtype=np.uint16) * 517 % 65521).astype(np.uint16).reshape(6, 5, 4)
+    cam = S.camera_preset("front", (4, 5, 6))
+    path = scene_io.write_vidi3d_scene(str(tmp_path / "s.json"), data, S.alpha_preset("ramp", 16), S.RAINBOW_CONTROLS, cam,
+                                       sample_distance=0.5)
+    root = json.load(open(path))
+    raw = root["dataSource"][0]["fileName"][0]
+    with open(raw, "wb") as f:
+        f.write(b"\x01" * 7 + data.astype(">u2").tobytes())
+    root["dataSource"][0].update(offset=7, endian="BIG_ENDIAN", scales={"x": 1.0, "y": 2.0, "z": 0.5})
+    json.dump(root, open(path, "w"))
+    sc = scene_io.read_vidi3d_scene(path)
+    assert np.array_equal(sc.volume.data, data) and sc.volume.data.dtype == np.uint16
+    assert tuple(sc.volume.grid_spacing) == (1.0, 2.0, 0.5) and sc.volume_sampling_rate == 2.0
+    # scalarMappingRange x type maximum, in fp32 like the serializer (serializer_vidi3d.cpp:235-269)
+    assert sc.tfn.value_range == tuple(float(np.float32(65535) * np.float32(v)) for v in (data.min(), data.max()))
+    root["dataSource"][0]["offset"] = 9
+    json.dump(root, open(path, "w"))
+    with pytest.raises(RuntimeError, match="File size does not match data size"):
+        scene_io.read_vidi3d_scene(path)
+    root["dataSource"][0]["fileName"] = ["/nonexistent/volume.raw"]
+    json.dump(root, open(path, "w"))
+    with pytest.raises(RuntimeError, match="Cannot find volume file"):
+        scene_io.read_vidi3d_scene(path)
