@@ -65,6 +65,35 @@ static bool delta_tracking(const PathCtx& c, TEA& rng, vec3 org, vec3 dir, float
   return false;
 }
 
+} // namespace ovr_oracle
+
+// Known-answer entry point for the free-path iteration alone: repeated hashit calls along one ray, taus[k] handed to call k
+// (the caller of the reference re-draws tau after every tentative collision). out[4k..] = (found, rayt, majorant, tau after).
+// Pinned against the reference's own DeltaTrackingIter<true> (oracle/ref_shim.cpp: ref_delta_hashit).
+extern "C" int ovr_oracle_delta_hashit(const float* majorants, const int32_t grid[3], const float spac_rcp[3], const float org[3],
+                                       const float dir[3], float tnear, float tfar, const float* taus, int n_taus, float* out)
+{
+  using namespace ovr_oracle;
+  ovr_oracle_scene s{};
+  s.mc_majorants = majorants;
+  PathCtx c{ s, VolumeTex{ nullptr, 0, 0, 0, 0 }, affine3{}, vec3i_t{ grid[0], grid[1], grid[2] },
+             v3(spac_rcp[0], spac_rcp[1], spac_rcp[2]) };
+  const vec3 o = v3(org[0], org[1], org[2]), d = v3(dir[0], dir[1], dir[2]);
+  DDAIter it;
+  it.init(o * c.spac_rcp, d * c.spac_rcp, tnear, tfar, c.mc);
+  float rayt = tnear, majorant = 0.f;
+  int k = 0;
+  for (; k < n_taus; k++) {
+    float tau = taus[k];
+    const bool found = hashit(c, it, o, d, tnear, tfar, rayt, majorant, tau);
+    out[4 * k] = found ? 1.f : 0.f, out[4 * k + 1] = rayt, out[4 * k + 2] = majorant, out[4 * k + 3] = tau;
+    if (!found) return k + 1;
+  }
+  return k;
+}
+
+namespace ovr_oracle {
+
 // uniform_sample_sphere (shaders_common.h:339-354); 2*M_PI*s.x is evaluated in double by the reference
 static inline vec3 uniform_sphere(float sx, float sy)
 {

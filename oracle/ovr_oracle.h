@@ -111,6 +111,9 @@ void ovr_oracle_xfm(const float m[12], const float v[3], float* out24); /* gdt t
 /* sparse-sampling mask (generate_mask.cu:55-86 + blue_noise.h:81-101): keep[x + y*width] in {0,1}, p_out optional */
 void ovr_oracle_sparse_mask(int width, int height, int frame_index, const float* noise, int tile_xy, int tile_t,
                             const float mean[2], float sigma, float base_noise, uint8_t* keep, float* p_out);
+/* free-path iteration of delta tracking alone (spatial_partition.h:56-96): see oracle_path.cpp */
+int ovr_oracle_delta_hashit(const float* majorants, const int32_t grid[3], const float spac_rcp[3], const float org[3],
+                            const float dir[3], float tnear, float tfar, const float* taus, int n_taus, float* out);
 int ovr_oracle_hardware_threads(void);
 
 #ifdef __cplusplus

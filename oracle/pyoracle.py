@@ -90,6 +90,25 @@ def ref_tfn_table(tfn_json_text, capacity=8192):
     return out[:n].copy()
 
 
+def delta_hashit(majorants, spac_rcp, org, dr, tnear, tfar, taus, use_ref=False):
+    """Free-path iteration of delta tracking along one ray (spatial_partition.h:56-96): rows (found, rayt, majorant, tau)
+    per hashit call. use_ref: the reference's own iterator from oracle/_ref (None when not built)."""
+    maj = np.ascontiguousarray(majorants, np.float32)
+    grid = _i3(maj.shape[2], maj.shape[1], maj.shape[0])
+    taus = np.ascontiguousarray(taus, np.float32)
+    out = np.zeros((len(taus), 4), np.float32)
+    if use_ref:
+        L = ref_kat_lib()
+        if L is None:
+            return None
+        fn = L.ref_delta_hashit
+    else:
+        fn = lib().ovr_oracle_delta_hashit
+    fn.restype = C.c_int
+    n = fn(_fp(maj), grid, _f3(*spac_rcp), _f3(*org), _f3(*dr), C.c_float(tnear), C.c_float(tfar), _fp(taus), len(taus), _fp(out))
+    return out[:n].copy()
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 

@@ -121,3 +121,41 @@ extern "C" void ref_sparse_mask(int width, int height, int frame_index, float* n
     generate_sparse_samples(n, xy, dist.data(), vec2i(width, height), 1, vec2f(mean[0], mean[1]), 1.f / (sigma * sigma), base_noise);
   }
 }
+
+// ---- delta tracking over the macrocell grid: the reference's DeltaTrackingIter<true> (accel/spatial_partition.h:23-96), the
+// struct and the iterator cut out at build time; RandomTEA comes from the extract above ----
+#include <cfloat>
+namespace ovr { namespace optix7 {
+struct range1f { float lower, upper; };
+constexpr float float_epsilon = std::numeric_limits<float>::epsilon(); // ovr/common/math_def.h:58
+typedef ovr::random::RandomTEA RandomTEA;
+#define __NVCC__ 1
+#include <singlemc_extract.h>
+template<>
+#include <delta_iter_extract.h>
+#undef __NVCC__
+} }
+
+// Repeated hashit calls along one ray, tau re-drawn by the caller after every tentative collision (delta_tracking,
+// shaders_pathtracing.cu:385-404): taus[k] is the free path handed to call k. out[4k..] = (found, rayt, majorant, tau after).
+extern "C" int ref_delta_hashit(const float* majorants, const int32_t grid[3], const float spac_rcp[3], const float org[3],
+                                const float dir[3], float tnear, float tfar, const float* taus, int n_taus, float* out)
+{
+  using namespace ovr::optix7;
+  DeviceSpacePartiton_SingleMC sp;
+  sp.majorants = const_cast<float*>(majorants);
+  sp.dims = vec3i(grid[0], grid[1], grid[2]);
+  sp.spac_rcp = vec3f(spac_rcp[0], spac_rcp[1], spac_rcp[2]);
+  const vec3f o(org[0], org[1], org[2]), d(dir[0], dir[1], dir[2]);
+  DeviceSpacePartiton_SingleMC::DeltaTrackingIter<true> it(sp, o, d, tnear, tfar);
+  RandomTEA rng(0, 0);
+  float rayt = tnear, majorant = 0.f;
+  int k = 0;
+  for (; k < n_taus; k++) {
+    float tau = taus[k];
+    const bool found = it.hashit(sp, o, d, tnear, tfar, rng, rayt, majorant, tau);
+    out[4 * k] = found ? 1.f : 0.f, out[4 * k + 1] = rayt, out[4 * k + 2] = majorant, out[4 * k + 3] = tau;
+    if (!found) return k + 1;
+  }
+  return k;
+}

@@ -10,7 +10,9 @@ where /root/reference exists):
 
   tfn_tables.npz    RGBA tables of every bundled scene's transfer function from the reference's tfn::loadTransferFunction
 
-Usage: python tests/golden/make_golden.py [sparse|tfn]
+  delta_hashit.npz  free-path iteration of delta tracking from the reference's own DeltaTrackingIter<true>::hashit
+
+Usage: python tests/golden/make_golden.py [sparse|tfn|delta]
 """
 import base64
 import ctypes as C
@@ -174,8 +176,51 @@ def make_tfn():
     np.savez_compressed(os.path.join(HERE, "tfn_tables.npz"), **out)
 
 
+def delta_cases():
+    """Seeded rays through random majorant grids with zero-majorant (skipped) cells; shared by the generator and the test."""
+    rng = np.random.default_rng(4242)
+    cases = []
+    for grid in [(8, 8, 8), (16, 4, 9), (3, 64, 5)]:
+        for k in range(12):
+            maj = rng.uniform(0.0, 1.5, grid[::-1]).astype(np.float32)
+            maj[rng.uniform(size=maj.shape) < (0.15 + 0.05 * k)] = 0.0          # empty cells: majorant <= epsilon
+            g = np.array(grid, np.float32)
+            spac_rcp = g                                                          # object space = unit cube
+            org = rng.uniform(-0.6, 1.6, 3).astype(np.float32)
+            tgt = rng.uniform(0.1, 0.9, 3).astype(np.float32)
+            d = tgt - org
+            if k % 4 == 3:
+                d[rng.integers(3)] = 0.0
+                org = np.clip(org, 0.05, 0.95).astype(np.float32)
+            d = (d / np.float32(np.linalg.norm(d))).astype(np.float32)
+            ok, t0, t1 = pyoracle.clip(org, d, (0, 0, 0), (1, 1, 1))
+            if not ok:
+                continue
+            taus = (-np.log(1.0 - rng.uniform(0.0, 1.0, 40)) * rng.choice([0.02, 0.2, 1.0])).astype(np.float32)
+            cases.append((maj, spac_rcp, org, d, np.float32(t0), np.float32(t1), taus))
+    return cases
+
+
+def make_delta():
+    """delta_hashit.npz: outputs of the reference's own DeltaTrackingIter<true>::hashit (oracle/ref_shim.cpp) for delta_cases()."""
+    pyoracle.build()
+    out = {}
+    cases = delta_cases()
+    n_found = 0
+    for k, (maj, sr, org, d, t0, t1, taus) in enumerate(cases):
+        rows = pyoracle.delta_hashit(maj, sr, org, d, t0, t1, taus, use_ref=True)
+        assert rows is not None, "oracle/_ref/libovr_ref_kat.so missing (needs /root/reference)"
+        out[f"case{k}"] = rows
+        n_found += int(rows[:, 0].sum())
+    out["n"] = np.int32(len(cases))
+    np.savez_compressed(os.path.join(HERE, "delta_hashit.npz"), **out)
+    print(f"wrote delta_hashit.npz: {len(cases)} rays, {n_found} tentative collisions")
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "sparse":
+    if len(sys.argv) > 1 and sys.argv[1] == "delta":
+        make_delta()
+    elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
     elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
         make_tfn()
@@ -183,3 +228,4 @@ if __name__ == "__main__":
         main()
         make_sparse()
         make_tfn()
+        make_delta()

@@ -123,3 +123,28 @@ def test_scene_file_transfer_functions_match_the_reference_loader():
             assert np.array_equal(alpha, want[:, 3]), name
         n_gauss += bool(jt.get("gaussianObjects"))
     assert n_gauss >= 10  # the bundled scenes that the alpha array alone does not describe
+
+
+def test_delta_tracking_free_path_iteration_matches_the_reference_iterator():
+    """The oracle's hashit (oracle_path.cpp) against tests/golden/delta_hashit.npz: (found, t, majorant, tau) of every call of
+    the reference's own DeltaTrackingIter<true>::hashit (accel/spatial_partition.h:56-96, cut out and compiled on the host by
+    oracle/ref_shim.cpp) along 36 seeded rays through grids with empty cells -- incl. its stale-t behaviour across skipped
+    cells. Bit-exact."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(__file__), "golden", "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    D = np.load(os.path.join(os.path.dirname(__file__), "golden", "delta_hashit.npz"))
+    cases = mg.delta_cases()
+    assert len(cases) == int(D["n"]) >= 30
+    found = skipped_cells = 0
+    for k, (maj, sr, org, d, t0, t1, taus) in enumerate(cases):
+        want = D[f"case{k}"]
+        got = pyoracle.delta_hashit(maj, sr, org, d, float(t0), float(t1), taus)
+        assert got.shape == want.shape, f"ray {k}"
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), f"ray {k}"
+        found += int(want[:, 0].sum())
+        skipped_cells += int((maj == 0).sum())
+        hits = want[want[:, 0] == 1]
+        assert (np.diff(hits[:, 1]) >= 0).all() and (hits[:, 1] >= t0).all() and (hits[:, 1] <= t1 + 1e-5).all()
+    assert found > 200 and skipped_cells > 1000
