@@ -103,6 +103,16 @@ static inline vec3 uniform_sphere(float sx, float sy)
   return v3(std::cos(phi) * sin_t, std::sin(phi) * sin_t, cos_t);
 }
 
+} // namespace ovr_oracle
+
+extern "C" void ovr_oracle_uniform_sphere(float sx, float sy, float out[3]) /* known-answer entry point */
+{
+  const ovr_oracle::vec3 v = ovr_oracle::uniform_sphere(sx, sy);
+  out[0] = v.x, out[1] = v.y, out[2] = v.z;
+}
+
+namespace ovr_oracle {
+
 // pathtracing (:477-542) for one camera ray; returns (Le, alpha)
 static void trace_path(const PathCtx& c, TEA& rng, vec3 cam_org, vec3 cam_dir, vec3& color, float& alpha,
                        ovr_oracle_counters& n)

@@ -114,6 +114,7 @@ void ovr_oracle_sparse_mask(int width, int height, int frame_index, const float*
 /* free-path iteration of delta tracking alone (spatial_partition.h:56-96): see oracle_path.cpp */
 int ovr_oracle_delta_hashit(const float* majorants, const int32_t grid[3], const float spac_rcp[3], const float org[3],
                             const float dir[3], float tnear, float tfar, const float* taus, int n_taus, float* out);
+void ovr_oracle_uniform_sphere(float sx, float sy, float out[3]); /* uniform_sample_sphere(1, s), shaders_common.h:339-354 */
 int ovr_oracle_hardware_threads(void);
 
 #ifdef __cplusplus

@@ -109,6 +109,28 @@ def delta_hashit(majorants, spac_rcp, org, dr, tnear, tfar, taus, use_ref=False)
     return out[:n].copy()
 
 
+def uniform_sphere(s, use_ref=False):
+    """uniform_sample_sphere(1, s) for rows s = (sx, sy); use_ref: the reference's own function from oracle/_ref."""
+    s = np.ascontiguousarray(s, np.float32)
+    L = ref_kat_lib() if use_ref else lib()
+    if L is None:
+        return None
+    fn = L.ref_uniform_sphere if use_ref else L.ovr_oracle_uniform_sphere
+    out = np.zeros((len(s), 3), np.float32)
+    for k in range(len(s)):
+        fn(C.c_float(float(s[k, 0])), C.c_float(float(s[k, 1])), _fp(out[k]))
+    return out
+
+
+def ref_clip(org, dr, lo, hi, t0=0.0, t1=np.finfo(np.float32).max):
+    """The reference's own intersect_box (oracle/_ref): (hit, t0, t1)."""
+    L = ref_kat_lib()
+    a, b = C.c_float(t0), C.c_float(t1)
+    L.ref_intersect_box.restype = C.c_int
+    ok = L.ref_intersect_box(_f3(*org), _f3(*dr), _f3(*lo), _f3(*hi), C.byref(a), C.byref(b))
+    return bool(ok), a.value, b.value
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 

@@ -159,3 +159,32 @@ extern "C" int ref_delta_hashit(const float* majorants, const int32_t grid[3], c
   }
   return k;
 }
+
+// ---- small shader helpers cut out of ovr/devices/optix7/shaders_common.h at build time: intersect_box (:156-184),
+// spherical_to_cartesian + uniform_sample_sphere (:339-354). __frcp_rn is the IEEE reciprocal. ----
+namespace ref_shader {
+using namespace gdt;
+constexpr float float_large = std::numeric_limits<float>::max(); // ovr/common/math_def.h:56-57
+constexpr float float_small = std::numeric_limits<float>::min();
+static inline float __frcp_rn(float x) { return 1.f / x; }
+using std::fabs;
+using std::sqrt;
+static bool
+#include <intersect_box_extract.h>
+static vec3f
+#include <spherical_extract.h>
+static vec3f
+#include <uniform_sphere_extract.h>
+} // namespace ref_shader
+
+extern "C" int ref_intersect_box(const float org[3], const float dir[3], const float lo[3], const float hi[3], float* t0, float* t1)
+{
+  return ref_shader::intersect_box(*t0, *t1, vec3f(org[0], org[1], org[2]), vec3f(dir[0], dir[1], dir[2]), vec3f(lo[0], lo[1], lo[2]),
+                                   vec3f(hi[0], hi[1], hi[2])) ? 1 : 0;
+}
+
+extern "C" void ref_uniform_sphere(float sx, float sy, float out[3])
+{
+  const vec3f v = ref_shader::uniform_sample_sphere(1.f, vec2f(sx, sy));
+  out[0] = v.x, out[1] = v.y, out[2] = v.z;
+}

@@ -12,7 +12,9 @@ where /root/reference exists):
 
   delta_hashit.npz  free-path iteration of delta tracking from the reference's own DeltaTrackingIter<true>::hashit
 
-Usage: python tests/golden/make_golden.py [sparse|tfn|delta]
+  shader_helpers.npz  intersect_box and uniform_sample_sphere from the reference's shaders_common.h
+
+Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers]
 """
 import base64
 import ctypes as C
@@ -201,6 +203,40 @@ def delta_cases():
     return cases
 
 
+def shader_helper_cases():
+    """Seeded inputs of intersect_box and uniform_sample_sphere; shared by the generator and the test."""
+    rng = np.random.default_rng(777)
+    rays = []
+    for k in range(600):
+        lo = rng.uniform(-0.2, 0.4, 3).astype(np.float32) if k % 3 else np.zeros(3, np.float32)
+        hi = (lo + rng.uniform(0.1, 1.0, 3)).astype(np.float32) if k % 3 else np.ones(3, np.float32)
+        org = rng.uniform(-2.0, 3.0, 3).astype(np.float32)
+        d = rng.normal(size=3).astype(np.float32)
+        if k % 2 == 0:                                     # aimed at the box: most of these hit
+            d = ((lo + (hi - lo) * rng.uniform(0.05, 0.95, 3)).astype(np.float32) - org).astype(np.float32)
+        if k % 5 == 0:
+            d[rng.integers(3)] = 0.0                       # |dir| < FLT_MIN on one axis
+        if k % 7 == 0:
+            d[rng.integers(3)] = np.float32(1e-39)         # denormal component: also "small"
+        if k % 11 == 0:
+            org = (lo + (hi - lo) * rng.uniform(0.1, 0.9, 3)).astype(np.float32)   # origin inside the box
+        rays.append((org, d, lo, hi))
+    s = rng.uniform(0.0, 1.0, (1500, 2)).astype(np.float32)
+    s[:8] = [[0, 0], [1, 1], [0.5, 0.5], [0.25, 0], [0, 1], [1, 0], [0.75, 0.999999], [0.999999, 0.5]]
+    return rays, s
+
+
+def make_shader_helpers():
+    """shader_helpers.npz: the reference's own intersect_box and uniform_sample_sphere (shaders_common.h:156-184,339-354)."""
+    pyoracle.build()
+    assert pyoracle.ref_kat_lib() is not None, "oracle/_ref/libovr_ref_kat.so missing (needs /root/reference)"
+    rays, s = shader_helper_cases()
+    box = np.array([[float(h), t0, t1] for h, t0, t1 in (pyoracle.ref_clip(*r) for r in rays)], np.float32)
+    sph = pyoracle.uniform_sphere(s, use_ref=True)
+    np.savez_compressed(os.path.join(HERE, "shader_helpers.npz"), box=box, sphere=sph)
+    print(f"wrote shader_helpers.npz: {int(box[:, 0].sum())} of {len(rays)} rays hit, {len(sph)} sphere samples")
+
+
 def make_delta():
     """delta_hashit.npz: outputs of the reference's own DeltaTrackingIter<true>::hashit (oracle/ref_shim.cpp) for delta_cases()."""
     pyoracle.build()
@@ -220,6 +256,8 @@ def make_delta():
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "delta":
         make_delta()
+    elif len(sys.argv) > 1 and sys.argv[1] == "helpers":
+        make_shader_helpers()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
     elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
@@ -229,3 +267,4 @@ if __name__ == "__main__":
         make_sparse()
         make_tfn()
         make_delta()
+        make_shader_helpers()

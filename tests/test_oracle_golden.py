@@ -148,3 +148,21 @@ def test_delta_tracking_free_path_iteration_matches_the_reference_iterator():
         hits = want[want[:, 0] == 1]
         assert (np.diff(hits[:, 1]) >= 0).all() and (hits[:, 1] >= t0).all() and (hits[:, 1] <= t1 + 1e-5).all()
     assert found > 200 and skipped_cells > 1000
+
+
+def test_clip_and_sphere_sampling_match_the_reference_functions():
+    """ovr_oracle_clip / the oracle's uniform_sphere against the reference's own intersect_box and uniform_sample_sphere
+    (shaders_common.h:156-184, 339-354; cut out and compiled on the host) on seeded inputs incl. zero / denormal direction
+    components and origins inside the box. Bit-exact."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(__file__), "golden", "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    H = np.load(os.path.join(os.path.dirname(__file__), "golden", "shader_helpers.npz"))
+    rays, s = mg.shader_helper_cases()
+    got = np.array([[float(h), t0, t1] for h, t0, t1 in (pyoracle.clip(*r) for r in rays)], np.float32)
+    assert np.array_equal(got.view(np.uint32), H["box"].view(np.uint32))
+    assert 100 < H["box"][:, 0].sum() < len(rays) - 100
+    sph = pyoracle.uniform_sphere(s)
+    assert np.array_equal(sph.view(np.uint32), H["sphere"].view(np.uint32))
+    assert np.allclose(np.linalg.norm(sph.astype(np.float64), axis=1), 1.0, atol=1e-6)
