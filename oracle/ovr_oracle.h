@@ -1,5 +1,8 @@
-/* TEST INFRASTRUCTURE ONLY -- CPU oracle for the B200 volume device ("parity unpinned by the reference":
- * the reference tree has no tests, golden images or known-answer vectors for this path).
+/* TEST INFRASTRUCTURE ONLY -- CPU oracle for the B200 volume device. The reference tree has no tests, golden images or
+ * known-answer vectors for this path; the oracle is pinned by outputs of the reference's own code
+ * compiled and run on the host (oracle/_ref: whole ray-marched frames from its raymarching() / raymarching_shadow(), its
+ * dda.h, RandomTEA, DeltaTrackingIter, intersect_box, uniform_sample_sphere, gdt transforms, mask kernels, tfn loader --
+ * fixtures under tests/golden/, all bit-exact) and, for the texture unit, by fetches captured on the B200.
  *
  * A CPU restatement (fp32, C++17, no CUDA) of the reference's optix7 shader arithmetic:
  *   ovr/devices/optix7/shaders_raymarching.cu:44-171,260-413      primary + shadow march, pixel finalisation
@@ -8,8 +11,8 @@
  *   ovr/devices/optix7/accel/{dda.h:30-148, spatial_partition.h:23-96, sp_singlemc.cu:10-137}
  *   ovr/common/random/random.h:146-188                            RandomTEA
  *   ovr/devices/optix7/device_impl.cpp:125-136                    camera derivation
- * Pinned by: KATs against the reference's own dda.h / RandomTEA / gdt compiled on the host (oracle/_ref,
- * oracle/ref_shim.cpp; fixtures under tests/golden/), analytic closed forms, and a GPU tex3D calibration KAT.
+ * Recipes: oracle/Makefile (target `ref`), oracle/ref_shim.cpp, oracle/ref_march_shim.cpp, oracle/ref_tfn_shim.cpp,
+ * oracle/extract_march.py, tests/golden/make_golden.py; also analytic closed forms (tests/test_oracle_analytic.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / `--impl reference` legs may load this library.
  */

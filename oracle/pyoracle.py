@@ -302,6 +302,20 @@ class OracleScene:
                                       int(premultiplied), C.byref(cnt), threads)
         return rgba, grad, cnt.as_dict()
 
+    def ref_march(self, pixels_xy):
+        """The REFERENCE's own raymarching() / raymarching_shadow() (cut out of its shader sources and compiled on the host by
+        oracle/ref_march_shim.cpp, texture fetches through this oracle's model of the unit) for the listed pixels:
+        (rgba [n, 4], grad [n, 3]); None where oracle/_ref was not built (needs /root/reference)."""
+        so = os.path.join(_HERE, "_ref", "libovr_ref_march.so")
+        if not os.path.exists(so):
+            return None
+        lib()  # liboracle.so first: the shim links against it
+        L = C.CDLL(so)
+        px = np.ascontiguousarray(pixels_xy, np.int32).reshape(-1, 2)
+        out = np.zeros((len(px), 7), np.float32)
+        L.ref_march_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        return out[:, :4].copy(), out[:, 4:].copy()
+
     def render_path(self, rect=None, stride=(1, 1), threads=0, frame_index=1):
         s = self.s
         s.frame_index = frame_index

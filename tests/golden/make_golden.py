@@ -14,7 +14,9 @@ where /root/reference exists):
 
   shader_helpers.npz  intersect_box and uniform_sample_sphere from the reference's shaders_common.h
 
-Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers]
+  ref_march.npz     whole frames from the reference's own raymarching() / raymarching_shadow() run on the host
+
+Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
 """
 import base64
 import ctypes as C
@@ -237,6 +239,39 @@ def make_shader_helpers():
     print(f"wrote shader_helpers.npz: {int(box[:, 0].sum())} of {len(rays)} rays hit, {len(sph)} sphere samples")
 
 
+MARCH_REF_CASES = [  # n, TF preset, camera preset, sampling rate, (W, H)
+    (32, "sparse", "oblique", 1.0, (48, 32)),   # step 1: opacity correction only where the running sum drifts / last step
+    (24, "ramp", "inside", 2.0, (40, 24)),      # camera inside the volume, rate 2: correction on every sample
+    (20, "ramp", "oblique", 0.7, (32, 20)),     # step > 1 voxel
+    (28, "dense", "front", 1.0, (36, 24)),      # no empty space, early ray termination
+]
+
+
+def march_ref_scene(case):
+    """OracleScene of one MARCH_REF_CASES entry (shared by the generator and the test)."""
+    import ovr_b200
+    from helpers import oracle_desc
+    n, tf, cam, rate, (w, h) = case
+    sc = ovr_b200.scenes.noise_scene(n, tf=tf, camera=cam, rate=rate)
+    return pyoracle.OracleScene(oracle_desc(sc, w, h)), w, h
+
+
+def make_march_ref():
+    """ref_march.npz: frames computed by the REFERENCE's own raymarching() / raymarching_shadow() and their helpers, cut out of
+    shaders_raymarching.cu / shaders_common.h and executed on the host (oracle/ref_march_shim.cpp), with texture fetches
+    through the oracle's model of the unit."""
+    pyoracle.build()
+    out = {"n": np.int32(len(MARCH_REF_CASES))}
+    for k, case in enumerate(MARCH_REF_CASES):
+        o, w, h = march_ref_scene(case)
+        ys, xs = np.mgrid[0:h, 0:w]
+        r = o.ref_march(np.stack([xs.ravel(), ys.ravel()], 1))
+        assert r is not None, "oracle/_ref/libovr_ref_march.so missing (needs /root/reference)"
+        out[f"rgba{k}"], out[f"grad{k}"] = r[0].reshape(h, w, 4), r[1].reshape(h, w, 3)
+        print(f"march case {k} {case}: {(out[f'rgba{k}'][..., 3] > 0).mean():.2f} of the pixels hit, max alpha {out[f'rgba{k}'][..., 3].max():.4f}")
+    np.savez_compressed(os.path.join(HERE, "ref_march.npz"), **out)
+
+
 def make_delta():
     """delta_hashit.npz: outputs of the reference's own DeltaTrackingIter<true>::hashit (oracle/ref_shim.cpp) for delta_cases()."""
     pyoracle.build()
@@ -258,6 +293,8 @@ if __name__ == "__main__":
         make_delta()
     elif len(sys.argv) > 1 and sys.argv[1] == "helpers":
         make_shader_helpers()
+    elif len(sys.argv) > 1 and sys.argv[1] == "march":
+        make_march_ref()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
     elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
@@ -268,3 +305,4 @@ if __name__ == "__main__":
         make_tfn()
         make_delta()
         make_shader_helpers()
+        make_march_ref()
