@@ -46,7 +46,8 @@ def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
     if force or not os.path.exists(so):
         subprocess.run(["make", "-C", _HERE, "liboracle.so"], check=True, capture_output=True)
-    if os.path.isdir("/root/reference/ovr") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "libovr_ref_kat.so"))):
+    refs = ("libovr_ref_kat.so", "libovr_ref_tfn.so", "libovr_ref_march.so")
+    if os.path.isdir("/root/reference/ovr") and (force or not all(os.path.exists(os.path.join(_HERE, "_ref", r)) for r in refs)):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
     return so
 
