@@ -10,9 +10,10 @@ A "step" is one frame of the workload through the hot path. One JSON line is pri
               function travel host -> device and the rgba + grad frame comes back device -> pinned host
   roofline    texture/L1 sampling roofline of the dominant kernel (32 B per executed trilinear fetch) against the
               fetch rate measured on this box by b200vr_bench_fetch, plus the HBM floor against MEASURED_PEAKS.json
-  cpu_baseline  the CPU oracle (a port of the reference's optix7 shader arithmetic) timed on the host cores on a strided
-              pixel sample of the same frame
-`--impl reference` times that CPU port alone (the reference's own devices need OptiX / OSPRay, neither installable here).
+  cpu_baseline  the reference's optix7 shader arithmetic on the host cores on a strided pixel sample of the same frame:
+              its own raymarching() / raymarching_shadow() compiled on the host (oracle/_ref, kind "reference") for shaded
+              ray marching, the CPU oracle (kind "port") for path tracing / unshaded frames or where oracle/_ref is absent
+`--impl reference` times that CPU arm alone (the reference's own devices need OptiX / OSPRay, neither installable here).
 N > 1 (torchrun): sort-first -- every rank renders the image tiles it owns of the same frame, slices are gathered to
 rank 0 over NCCL and scattered into the display frame; strong scaling.
 """
@@ -180,9 +181,25 @@ def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
     o = pyoracle.OracleScene(d, skip_empty=False, build_macrocells=(wl["mode"] == "pathtrace"))
     cores = pyoracle.hardware_threads()
 
+    # ray marching with the reference's shading: the REFERENCE's own raymarching() / raymarching_shadow() compiled on the host
+    # (oracle/_ref/libovr_ref_march.so, built where /root/reference exists and shipped with the snapshot) are what is timed;
+    # the oracle port -- pinned bit for bit against them by tests/golden/ref_march.npz -- supplies the sample count of the
+    # same pixels in an untimed pass. Path tracing and unshaded frames have no compiled reference counterpart: port.
+    W, H = wl["width"], wl["height"]
+    use_ref = (wl["mode"] != "pathtrace" and wl["shading"] == "ref" and not os.environ.get("B200VR_BENCH_CPU_PORT")
+               and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libovr_ref_march.so")))
+    ref_px, ref_cnt = None, None
+    if use_ref:
+        ys, xs = np.meshgrid(np.arange(0, H, stride), np.arange(0, W, stride), indexing="ij")
+        ref_px = np.stack([xs.ravel(), ys.ravel()], 1).astype(np.int32)
+        _, _, ref_cnt = o.render_march(stride=(stride, stride), threads=cores, frame_index=1)  # untimed: counts only
+
     def frame(fi):
         t0 = time.perf_counter()
-        if wl["mode"] == "pathtrace":
+        if use_ref:
+            o.ref_march(ref_px, threads=cores)
+            cnt = ref_cnt
+        elif wl["mode"] == "pathtrace":
             _, cnt = o.render_path(stride=(stride, stride), threads=cores, frame_index=fi)
         else:
             _, _, cnt = o.render_march(stride=(stride, stride), threads=cores, frame_index=fi)
@@ -196,9 +213,11 @@ def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
         dt, s, cnt = frame(k + 1)
         tot_t += dt
         tot_s += s
-    info = {"cores": cores, "kind": "port",
-            "sample": f"every {stride}th pixel in x and y (1/{stride * stride} of the rays) of the {wl['width']}x{wl['height']} frame, "
-                      f"reference algorithm without skipping, {steps} frame(s)", "rays": cnt["rays"], "samples_per_frame": tot_s // max(steps, 1)}
+    what = ("the reference's own raymarching()/raymarching_shadow() (shaders_raymarching.cu:43-171) compiled on the host, texture unit emulated"
+            if use_ref else "CPU port of the reference algorithm without skipping")
+    info = {"cores": cores, "kind": "reference" if use_ref else "port",
+            "sample": f"every {stride}th pixel in x and y (1/{stride * stride} of the rays) of the {W}x{H} frame, "
+                      f"{what}, {steps} frame(s)", "rays": cnt["rays"], "samples_per_frame": tot_s // max(steps, 1)}
     return tot_s / tot_t / 1e6, tot_t / steps * 1e3, info
 
 
@@ -218,8 +237,9 @@ def run_reference(args):
     v, ms, info = cpu_oracle_run(wl, scene, steps, warmup, stride)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args, wl), "note": "reference devices need OptiX/OSPRay (absent); this is the CPU port of "
-                       "the optix7 shader arithmetic on the host cores; ms_per_step is for the sampled pixel subset"},
+            "config": {"workload": workload_name(args, wl), "note": "reference devices need OptiX/OSPRay (absent); this is the optix7 device's shader arithmetic on "
+                       "the host cores (cpu_baseline.kind: the reference's own march functions compiled on the host where oracle/_ref "
+                       "exists, else the CPU port); ms_per_step is for the sampled pixel subset"},
             "cpu_baseline": dict(info, value=v, unit=UNIT),
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)

@@ -41,13 +41,24 @@ class Counters(C.Structure):
         return {k: int(getattr(self, k)) for k, _ in self._fields_}
 
 
+def _stale(target, sources):
+    """True when `target` is missing or older than any of `sources` (files under oracle/)."""
+    if not os.path.exists(target):
+        return True
+    mt = os.path.getmtime(target)
+    return any(os.path.getmtime(os.path.join(_HERE, s)) > mt for s in sources if os.path.exists(os.path.join(_HERE, s)))
+
+
 def build(force=False):
-    """Compile liboracle.so (and oracle/_ref when /root/reference is present)."""
+    """Compile liboracle.so (and oracle/_ref when /root/reference is present); rebuilt when a source is newer."""
     so = os.path.join(_HERE, "liboracle.so")
-    if force or not os.path.exists(so):
+    srcs = ("oracle_sample.cpp", "oracle_grid.cpp", "oracle_march.cpp", "oracle_path.cpp", "oracle_math.h", "oracle_internal.h",
+            "ovr_oracle.h")
+    if force or _stale(so, srcs):
         subprocess.run(["make", "-C", _HERE, "liboracle.so"], check=True, capture_output=True)
     refs = ("libovr_ref_kat.so", "libovr_ref_tfn.so", "libovr_ref_march.so")
-    if os.path.isdir("/root/reference/ovr") and (force or not all(os.path.exists(os.path.join(_HERE, "_ref", r)) for r in refs)):
+    ref_srcs = ("ref_shim.cpp", "ref_tfn_shim.cpp", "ref_march_shim.cpp", "extract_march.py", "Makefile", "liboracle.so")
+    if os.path.isdir("/root/reference/ovr") and (force or any(_stale(os.path.join(_HERE, "_ref", r), ref_srcs) for r in refs)):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
     return so
 
@@ -303,10 +314,11 @@ class OracleScene:
                                       int(premultiplied), C.byref(cnt), threads)
         return rgba, grad, cnt.as_dict()
 
-    def ref_march(self, pixels_xy):
+    def ref_march(self, pixels_xy, threads=1):
         """The REFERENCE's own raymarching() / raymarching_shadow() (cut out of its shader sources and compiled on the host by
         oracle/ref_march_shim.cpp, texture fetches through this oracle's model of the unit) for the listed pixels:
-        (rgba [n, 4], grad [n, 3]); None where oracle/_ref was not built (needs /root/reference)."""
+        (rgba [n, 4], grad [n, 3]); None where oracle/_ref was not built (needs /root/reference). threads: 1 = the plain loop,
+        0 = all hardware threads (ref_march_rays_mt, same pixels)."""
         so = os.path.join(_HERE, "_ref", "libovr_ref_march.so")
         if not os.path.exists(so):
             return None
@@ -314,7 +326,10 @@ class OracleScene:
         L = C.CDLL(so)
         px = np.ascontiguousarray(pixels_xy, np.int32).reshape(-1, 2)
         out = np.zeros((len(px), 7), np.float32)
-        L.ref_march_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        if threads == 1:
+            L.ref_march_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        else:
+            L.ref_march_rays_mt(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out), C.c_int(threads))
         return out[:, :4].copy(), out[:, 4:].copy()
 
     def render_path(self, rect=None, stride=(1, 1), threads=0, frame_index=1):

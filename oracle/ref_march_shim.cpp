@@ -18,6 +18,9 @@
 #include <cstdint>
 #include <cstring>
 #include <limits>
+#include <atomic>
+#include <thread>
+#include <vector>
 
 #include <cuda_runtime.h> // float2 / make_float2 (host-side vector types only)
 #include <gdt/math/mat.h>
@@ -44,7 +47,7 @@ struct float4 { // shadows CUDA's float4 inside this namespace: the device code 
   float x, y, z, w;
   operator vec4f() const { return vec4f(x, y, z, w); }
 };
-static int g_filter_mode = OVR_ORACLE_FILTER_HW;
+static thread_local int g_filter_mode = OVR_ORACLE_FILTER_HW; // per thread: ref_march_rays_mt runs one copy of the launch state per worker
 template<typename T> static inline T tex3D(const Tex3& t, float x, float y, float z)
 {
   const float p[3] = { x, y, z };
@@ -89,9 +92,9 @@ struct LaunchParams {
   vec3f light_directional_pos;
   int traversable = 0;
 };
-static LaunchParams optix_launch_params;
-static float g_otw[12], g_wto[12];
-static const DeviceStructuredRegularVolume* g_self = nullptr;
+static thread_local LaunchParams optix_launch_params;
+static thread_local float g_otw[12], g_wto[12];
+static thread_local const DeviceStructuredRegularVolume* g_self = nullptr;
 static inline void optixGetWorldToObjectTransformMatrix(float m[12]) { std::memcpy(m, g_wto, sizeof(g_wto)); }
 static inline void optixGetObjectToWorldTransformMatrix(float m[12]) { std::memcpy(m, g_otw, sizeof(g_otw)); }
 
@@ -215,4 +218,26 @@ extern "C" void ref_march_rays(const ovr_oracle_scene* s, const int32_t* pixels_
     float* o = out + 7 * i;
     o[0] = c.x, o[1] = c.y, o[2] = c.z, o[3] = alpha, o[4] = g.x, o[5] = g.y, o[6] = g.z;
   }
+}
+
+// The same over `threads` host threads (0: all hardware threads), pixels handed out in chunks of 64 through an atomic counter:
+// the timed CPU arm of bench.py (`--impl reference`, cpu_baseline.kind "reference"). Every worker sets up its own copy of
+// the launch state (thread_local above), so the result is ref_march_rays' pixel for pixel.
+extern "C" void ref_march_rays_mt(const ovr_oracle_scene* s, const int32_t* pixels_xy, int64_t n_pixels, float* out, int threads)
+{
+  if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
+  const int64_t chunk = 64;
+  std::atomic<int64_t> next{ 0 };
+  auto work = [&]() {
+    for (;;) {
+      const int64_t b = next.fetch_add(chunk);
+      if (b >= n_pixels) break;
+      const int64_t n = std::min(chunk, n_pixels - b);
+      ref_march_rays(s, pixels_xy + 2 * b, n, out + 7 * b);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int i = 1; i < threads; i++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
 }

@@ -192,3 +192,24 @@ def test_oracle_march_equals_the_reference_shader_code_bit_for_bit():
         o2.s.skip_empty = 1
         rgba2, grad2, _ = o2.render_march()
         assert np.array_equal(rgba2.view(np.uint32), rgba.view(np.uint32)) and np.array_equal(grad2.view(np.uint32), grad.view(np.uint32))
+
+
+def test_reference_march_shim_live_and_threaded_equals_the_golden_frames():
+    """Where oracle/_ref exists (this container; it ships prebuilt to the GPU box): the reference's own march functions run
+    live -- single loop and ref_march_rays_mt on all host threads, the timed CPU arm of `bench.py --impl reference` --
+    reproduce tests/golden/ref_march.npz bit for bit."""
+    import importlib.util
+    if not os.path.exists(os.path.join(os.path.dirname(pyoracle.__file__), "_ref", "libovr_ref_march.so")):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(__file__), "golden", "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_march.npz"))
+    for k, case in enumerate(mg.MARCH_REF_CASES[:2]):
+        o, w, h = mg.march_ref_scene(case)
+        ys, xs = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
+        px = np.stack([xs.ravel(), ys.ravel()], 1)
+        for threads in (1, 0):
+            rgba, grad = o.ref_march(px, threads=threads)
+            assert np.array_equal(rgba.reshape(h, w, 4).view(np.uint32), G[f"rgba{k}"].view(np.uint32)), (k, threads)
+            assert np.array_equal(grad.reshape(h, w, 3).view(np.uint32), G[f"grad{k}"].view(np.uint32)), (k, threads)
