@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define B200VR_ABI_VERSION 1
+#define B200VR_ABI_VERSION 2
 
 enum {
   B200VR_OK = 0,
@@ -55,6 +55,13 @@ typedef struct b200vr_params {
   int32_t premultiplied;    /* 1 = store (C, A) before the final divide (sort-last partial images) */
   float light_pos[3];       /* fixed directional light, params.h:79 */
   float light_ambient;      /* params.h:80 */
+  /* Path tracing, scattered rays. pathtracing() hands them to optixTrace already in object space
+   * (shaders_pathtracing.cu:510-513) and OptiX applies the instance's world-to-object transform to them once more before
+   * __intersection__volume (shaders_common.h:379-392) clips them, so in the reference their far end is bounded by the
+   * macrocell grid, not by the volume: where dims % 16 != 0 they go on colliding with clamp-to-edge voxels in the
+   * overhang of the last macrocells. 0 (default) = clip them against the volume as the object-space rays they are;
+   * 1 = the reference's behaviour, bit for bit (oracle/ref_march_shim.cpp runs the reference code). */
+  int32_t pt_child_instance_xfm;
 } b200vr_params;
 
 typedef struct b200vr_stats {

@@ -22,7 +22,7 @@ class Params(C.Structure):
     _fields_ = [("sampling_rate", C.c_float), ("base", C.c_float), ("spp", C.c_int32), ("mode", C.c_int32),
                 ("shading", C.c_int32), ("sampler", C.c_int32), ("skip_empty", C.c_int32), ("accumulate", C.c_int32),
                 ("max_num_scatters", C.c_int32), ("premultiplied", C.c_int32), ("light_pos", C.c_float * 3),
-                ("light_ambient", C.c_float)]
+                ("light_ambient", C.c_float), ("pt_child_instance_xfm", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -148,6 +148,7 @@ extern "C" void b200vr_default_params(b200vr_params* p)
   p->light_pos[1] = 2205.875f;
   p->light_pos[2] = -400.0267f;
   p->light_ambient = 1.f;
+  p->pt_child_instance_xfm = 0;
 }
 
 extern "C" const char* b200vr_last_error(const b200vr_t* h) { return h ? h->error.c_str() : g_create_error.c_str(); }
@@ -826,6 +827,7 @@ static void fill_launch_params(b200vr_t* h, LaunchParams& P)
   P.wto_t = transposed(P.wto.l);
   P.light_ambient = h->prm.light_ambient;
   P.max_num_scatters = h->prm.max_num_scatters;
+  P.pt_child_instance_xfm = h->prm.pt_child_instance_xfm;
   P.rgba = h->target_rgba ? h->target_rgba : h->rgba[h->current];
   P.grad = h->target_grad ? h->target_grad : h->grad[h->current];
   P.accum = h->accum;

@@ -63,6 +63,7 @@ struct LaunchParams {
   f3 light_dir;             // normalize(light_directional_pos), params.h:79
   float light_ambient;
   int max_num_scatters;
+  int pt_child_instance_xfm; // b200vr_params::pt_child_instance_xfm
   // ---- kernel-wide constants derived on the host so that they are plain constant-bank operands in the kernels ----
   f3 cam_oo;                // camera position in object space: xfmPoint(wto, cam_pos)
   f3 sh_d, sh_rcp;          // shadow-ray direction in object space wto.l * light_dir, and __frcp_rn of it

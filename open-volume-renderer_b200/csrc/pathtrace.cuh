@@ -168,7 +168,12 @@ pathtrace_kernel(const __grid_constant__ LaunchParams P)
             scatter_index += 1;
             t0 = 0.f;
             t1 = FLT_MAX;
-            if (!intersect_box(t0, t1, org, dir, mk3(0.f), mk3(1.f))) break;
+            // q14: under OptiX the scattered ray passes through the instance transform again before the clip; the walk
+            // itself runs along the ray as handed over, inside the clip's t range
+            if (P.pt_child_instance_xfm) {
+              if (!intersect_box(t0, t1, xfm_point(P.wto, org), xfm_vector(P.wto.l, dir), mk3(0.f), mk3(1.f))) break;
+            }
+            else if (!intersect_box(t0, t1, org, dir, mk3(0.f), mk3(1.f))) break;
           }
           le = terminal;
           for (int i = depth - 1; i >= 0; i--) le = stack[i] * le;

@@ -1,4 +1,4 @@
-"""TEST INFRASTRUCTURE ONLY -- cuts the reference's ray-marching functions out of its shader sources into the git-ignored
+"""TEST INFRASTRUCTURE ONLY -- cuts the reference's ray-marching and path-tracing functions out of its shader sources into the git-ignored
 oracle/_ref/ directory, one file per function (name line + body, without the `inline __device__ <type>` line above it), so
 that oracle/ref_march_shim.cpp can compile them as host code. Nothing is copied into the repository.
 
@@ -10,6 +10,8 @@ import sys
 REF, OUT = sys.argv[1], sys.argv[2]
 COMMON = "ovr/devices/optix7/shaders_common.h"
 MARCH = "ovr/devices/optix7/shaders_raymarching.cu"
+PATH = "ovr/devices/optix7/shaders_pathtracing.cu"
+SPART = "ovr/devices/optix7/accel/spatial_partition.h"
 
 # (source, first line regex, last line regex, output file)
 ITEMS = [
@@ -30,6 +32,12 @@ ITEMS = [
     (COMMON, r"^sample_transfer_function\(", r"^\}", "m_sample_tf.h"),
     (MARCH, r"^raymarching_shadow\(", r"^\}", "m_raymarching_shadow.h"),
     (MARCH, r"^raymarching\(", r"^\}", "m_raymarching.h"),
+    # delta-tracking path tracer (ref_march_shim.cpp, namespace pt)
+    (COMMON, r"^struct PathTracingPayload \{", r"^\};", "p_payload.h"),
+    (SPART, r"^  DeviceSpacePartiton_SingleMC::iter\(", r"^  \}", "p_sp_iter.h"),
+    (PATH, r"^delta_tracking\(const DeviceStructuredRegularVolume& self,", r"^\}", "p_delta_tracking.h"),
+    (PATH, r"^pathtracing\(const DeviceStructuredRegularVolume& self,", r"^\}", "p_pathtracing.h"),
+    (PATH, r"^render_pathtracing\(vec3f org,", r"^\}", "p_render_pathtracing.h"),
 ]
 
 os.makedirs(OUT, exist_ok=True)

@@ -148,7 +148,12 @@ static void trace_path(const PathCtx& c, TEA& rng, vec3 cam_org, vec3 cam_dir, v
     scatter_index += 1; // child payload starts at scatter_index + 1
     t0 = 0.f;
     t1 = float_large;
-    if (!intersect_box(t0, t1, org, dir, v3(0.f), v3(1.f))) break; // child misses: its colour stays 0
+    if (c.s.pt_child_instance_xfm) {
+      // q14: OptiX carries the (already object-space) scattered ray through the instance transform once more before the clip;
+      // the march itself runs along the ray as passed (optixGetWorldRayOrigin / Direction), with the clip's t range
+      if (!intersect_box(t0, t1, xfmPoint(c.wto, org), xfmVector(c.wto.l, dir), v3(0.f), v3(1.f))) break;
+    }
+    else if (!intersect_box(t0, t1, org, dir, v3(0.f), v3(1.f))) break; // child misses: its colour stays 0
   }
   vec3 le = terminal;
   for (int i = depth - 1; i >= 0; i--) le = stack[i] * le; // Le = albedo * child.color, inside out

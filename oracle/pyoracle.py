@@ -30,6 +30,7 @@ class Scene(C.Structure):
         ("shading", C.c_int32), ("skip_empty", C.c_int32), ("filter_mode", C.c_int32),
         ("max_num_scatters", C.c_int32), ("light_pos", _f3), ("light_ambient", C.c_float),
         ("clip_lo", _f3), ("clip_hi", _f3), ("mc_majorants", C.c_void_p), ("mc_dims", _i3),
+        ("pt_child_instance_xfm", C.c_int32),
     ]
 
 
@@ -331,6 +332,22 @@ class OracleScene:
         else:
             L.ref_march_rays_mt(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out), C.c_int(threads))
         return out[:, :4].copy(), out[:, 4:].copy()
+
+    def ref_path(self, pixels_xy, frame_index=1):
+        """The REFERENCE's own delta_tracking() / pathtracing() / render_pathtracing() (oracle/ref_march_shim.cpp, namespace pt) for
+        the listed pixels, one frame: rgba [n, 4]; None where oracle/_ref was not built. self.s.pt_child_instance_xfm = 1:
+        scattered rays go through the instance transform a second time before they are clipped, as OptiX does; 0: clipped as
+        the object-space rays they are."""
+        so = os.path.join(_HERE, "_ref", "libovr_ref_march.so")
+        if not os.path.exists(so):
+            return None
+        lib()
+        L = C.CDLL(so)
+        self.s.frame_index = frame_index
+        px = np.ascontiguousarray(pixels_xy, np.int32).reshape(-1, 2)
+        out = np.zeros((len(px), 4), np.float32)
+        L.ref_path_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        return out
 
     def render_path(self, rect=None, stride=(1, 1), threads=0, frame_index=1):
         s = self.s

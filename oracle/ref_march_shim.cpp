@@ -26,6 +26,12 @@
 #include <gdt/math/mat.h>
 #include <gdt/math/vec.h>
 
+#undef __device__
+#define __device__
+#undef __forceinline__
+#define __forceinline__ inline
+#include <dda.h> // ovr/devices/optix7/accel/dda.h (ovr::dda::DDAIter), used by the path tracer's macrocell iterator
+
 #include "ovr_oracle.h" // the texture-unit model: ovr_oracle_sample_volume, ovr_oracle_tex1d
 
 namespace ref_march {
@@ -69,6 +75,28 @@ template<> inline float4 tex1D<float4>(const Tex1& t, float u)
   return float4{ out[0], out[1], out[2], out[3] };
 }
 
+// ---- path tracing only: RandomTEA (ovr/common/random/random.h:146-188), the macrocell grid and its delta-tracking iterator
+// (accel/spatial_partition.h:23-121), cut out at build time by oracle/Makefile and oracle/extract_march.py ----
+namespace tea {
+struct float2 { // CUDA's float2 with the conversion gdt::vec2f has under nvcc
+  float x, y;
+  operator vec2f() const { return vec2f(x, y); }
+};
+static inline float2 make_float2(float x, float y) { return float2{ x, y }; }
+#include <random_tea_extract.h>
+}
+typedef tea::RandomTEA RandomTEA;
+namespace dda = ovr::dda;
+struct range1f { float lower, upper; };
+constexpr float float_epsilon = std::numeric_limits<float>::epsilon(); // ovr/common/math_def.h:58
+#define __NVCC__ 1
+#include <singlemc_extract.h>
+template<>
+#include <delta_iter_extract.h>
+inline DeviceSpacePartiton_SingleMC::DeltaTrackingIter<true>
+#include <p_sp_iter.h>
+#undef __NVCC__
+
 // ---- device-side structs, members named as the shaders use them (array.h, volume.h:40-62, params.h:55-99) ----
 struct Array3DScalarOptix7 {
   Tex3 data;
@@ -85,11 +113,15 @@ struct DeviceStructuredRegularVolume {
   Array3DScalarOptix7 volume;
   struct { Array1DFloat4Optix7 color; Array1DScalarOptix7 opacity; } tfn;
   float step, base;
+  DeviceSpacePartiton_SingleMC sp; // volume.h:46
+  int use_dda = 1;                 // volume.h:54
 };
 struct LaunchParams {
   struct DeviceCamera { vec3f position, direction, horizontal, vertical; };
   DeviceCamera camera, last_camera;
   vec3f light_directional_pos;
+  float light_ambient_intensity = 1.f; // params.h:80
+  int max_num_scatters = 24;           // params.h:86
   int traversable = 0;
 };
 static thread_local LaunchParams optix_launch_params;
@@ -111,8 +143,6 @@ static inline void* unpack_pointer(uint32_t i0, uint32_t i1) { return reinterpre
 static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float, OptixVisibilityMask, int, int, int, int, uint32_t& u0,
                        uint32_t& u1);
 
-#define __device__
-#define __forceinline__ inline
 #include <m_shadow_payload.h>
 #include <m_march_payload.h>
 static inline float
@@ -163,6 +193,51 @@ static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float,
   else
     data.t_max = tmax; // __miss__shadow
 }
+
+
+// ---- the delta-tracking path tracer: delta_tracking(), pathtracing(), render_pathtracing() (shaders_pathtracing.cu:269-542,
+// 603-631) compiled from the reference's text; this namespace supplies that file's ray-type enum and what the pipeline does
+// with a PATHTRACING_RAY_TYPE ray ----
+namespace pt {
+enum RayType { PATHTRACING_RAY_TYPE = 0, RAY_TYPE_COUNT }; // shaders_pathtracing.cu:45
+#define USE_DELTA_TRACKING_ITER 1                          // shaders_pathtracing.cu:38-39
+#define VARYING_MAJORANT 1
+// 1: OptiX semantics -- the instance's world-to-object transform is applied to EVERY traced ray before __intersection__volume
+//    clips it, also to the scattered rays, which pathtracing() hands to optixTrace already in object space (:510-513);
+// 0: scattered rays are clipped as the object-space rays they are (the B200 kernels' default).
+// Same meaning as ovr_oracle_scene::pt_child_instance_xfm, which ref_path_rays reads.
+static thread_local int g_child_instance_xfm = 1;
+static inline int optixGetGASTraversableHandle() { return 0; }
+struct OptixVisibilityMask { explicit OptixVisibilityMask(int) {} }; // own types: argument-dependent lookup must not reach the
+enum { OPTIX_RAY_FLAG_DISABLE_ANYHIT = 1 };                          // shadow-ray optixTrace of the enclosing namespace
+static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float, OptixVisibilityMask, int, int, int, int, uint32_t& u0,
+                       uint32_t& u1);
+#include <p_payload.h>
+static inline vec3f
+#include <spherical_extract.h>
+static inline vec3f
+#include <uniform_sphere_extract.h>
+static inline bool
+#include <p_delta_tracking.h>
+static inline void
+#include <p_pathtracing.h>
+static inline void
+#include <p_render_pathtracing.h>
+
+// __intersection__volume (shaders_common.h:379-392) on the object-space ray, then __closesthit__volume_pathtracing
+// (shaders_pathtracing.cu:548-565: t0 = the reported hit distance, t1 = attribute 1, world ray as passed to optixTrace);
+// __miss__pathtracing leaves the payload untouched.
+static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float, OptixVisibilityMask, int, int, int, int, uint32_t& u0,
+                       uint32_t& u1)
+{
+  PathTracingPayload& data = *(PathTracingPayload*)unpack_pointer(u0, u1);
+  const affine3f wto = get_xfm_wto();
+  const bool as_is = g_child_instance_xfm == 0 && data.wto != nullptr;
+  const vec3f o = as_is ? org : xfmPoint(wto, org), d = as_is ? dir : xfmVector(wto, dir);
+  float t0 = tmin, t1 = tmax;
+  if (intersect_box(t0, t1, o, d, vec3f(0.f), vec3f(1.f))) pathtracing(*g_self, org, dir, t0, t1, data);
+}
+} // namespace pt
 
 } // namespace ref_march
 
@@ -240,4 +315,72 @@ extern "C" void ref_march_rays_mt(const ovr_oracle_scene* s, const int32_t* pixe
   for (int i = 1; i < threads; i++) pool.emplace_back(work);
   work();
   for (auto& t : pool) t.join();
+}
+
+// One path-traced frame through the reference's render_pathtracing(): for every listed pixel the loop of
+// __raygen__render_frame (shaders_pathtracing.cu:633-676: RandomTEA(frame_index, pixel_index), spp samples with pixel jitter when
+// spp > 1, mean). s->mc_majorants / mc_dims: the macrocell majorants (ovr_oracle_build_macrocells); spac as
+// SpacePartiton_SingleMC::allocate derives it (sp_singlemc.cu:99-104). out: 4 floats per pixel (r, g, b, a), one frame, no
+// accumulation. s->pt_child_instance_xfm: see pt::g_child_instance_xfm.
+extern "C" void ref_path_rays(const ovr_oracle_scene* s, const int32_t* pixels_xy, int64_t n_pixels, float* out)
+{
+  using namespace ref_march;
+  g_filter_mode = s->filter_mode;
+  pt::g_child_instance_xfm = s->pt_child_instance_xfm;
+  DeviceStructuredRegularVolume self;
+  self.volume.data = Tex3{ s->voxels, { s->dims[0], s->dims[1], s->dims[2] } };
+  self.volume.dims = vec3i(s->dims[0], s->dims[1], s->dims[2]);
+  self.volume.lower.v = s->tf_lower, self.volume.upper.v = s->tf_upper;
+  self.volume.scale.v = 1.f / (s->tf_upper - s->tf_lower); // volume.cpp:145
+  self.tfn.color.data = Tex1{ s->tf_color, s->n_color, 4 }, self.tfn.color.dims.v = s->n_color;
+  self.tfn.opacity.data = Tex1{ s->tf_alpha, s->n_alpha, 1 }, self.tfn.opacity.dims.v = s->n_alpha;
+  self.step = s->step, self.base = s->base;
+  self.sp.majorants = const_cast<float*>(s->mc_majorants);
+  self.sp.dims = vec3i(s->mc_dims[0], s->mc_dims[1], s->mc_dims[2]);
+  self.sp.spac = vec3f((float)DeviceSpacePartiton_SingleMC::MACROCELL_SIZE) / vec3f(self.volume.dims);
+  self.sp.spac_rcp = 1.f / self.sp.spac;
+  g_self = &self;
+  std::memcpy(g_otw, s->obj_to_world, sizeof(g_otw));
+  {
+    affine3f a;
+    a.l.vx = vec3f(g_otw[0], g_otw[4], g_otw[8]), a.l.vy = vec3f(g_otw[1], g_otw[5], g_otw[9]), a.l.vz = vec3f(g_otw[2], g_otw[6], g_otw[10]);
+    a.p = vec3f(g_otw[3], g_otw[7], g_otw[11]);
+    const affine3f inv = rcp(a);
+    const float m[12] = { inv.l.vx.x, inv.l.vy.x, inv.l.vz.x, inv.p.x, inv.l.vx.y, inv.l.vy.y, inv.l.vz.y, inv.p.y,
+                          inv.l.vx.z, inv.l.vy.z, inv.l.vz.z, inv.p.z };
+    std::memcpy(g_wto, m, sizeof(m));
+  }
+  LaunchParams& lp = optix_launch_params;
+  lp.camera.position = vec3f(s->cam_position[0], s->cam_position[1], s->cam_position[2]);
+  lp.camera.direction = vec3f(s->cam_direction[0], s->cam_direction[1], s->cam_direction[2]);
+  lp.camera.horizontal = vec3f(s->cam_horizontal[0], s->cam_horizontal[1], s->cam_horizontal[2]);
+  lp.camera.vertical = vec3f(s->cam_vertical[0], s->cam_vertical[1], s->cam_vertical[2]);
+  lp.last_camera = lp.camera;
+  lp.light_ambient_intensity = s->light_ambient;
+  lp.max_num_scatters = s->max_num_scatters;
+  const vec2f rsize = vec2f(1.f) / vec2f((float)s->width, (float)s->height);
+  const int spp = s->spp;
+  for (int64_t i = 0; i < n_pixels; i++) {
+    const int ix = pixels_xy[2 * i], iy = pixels_xy[2 * i + 1];
+    const vec2f screen_coord = vec2f((float)ix + .5f, (float)iy + .5f) * rsize; // compute_screen_position, method 1
+    const uint32_t pixel_index = (uint32_t)ix + (uint32_t)iy * (uint32_t)s->width;
+    RandomTEA rng_state((uint32_t)s->frame_index, pixel_index);
+    float alpha = 0.f;
+    vec3f color = 0.f, gradient = 0.f;
+    vec2f flow = 0.f;
+    for (int k = 0; k < spp; k++) {
+      vec2f screen = screen_coord;
+      if (spp > 1) {
+        const vec2f pixel_jitter = vec2f(rng_state.get_floats()) - 0.5f;
+        screen += pixel_jitter * rsize;
+      }
+      const vec3f ray_dir = normalize(lp.camera.direction + (screen.x - 0.5f) * lp.camera.horizontal + (screen.y - 0.5f) * lp.camera.vertical);
+      pt::render_pathtracing(lp.camera.position, ray_dir, &rng_state, alpha, color, gradient, flow);
+    }
+    const float rspp = 1.f / spp;
+    alpha *= rspp;
+    color *= rspp;
+    float* o = out + 4 * i;
+    o[0] = color.x, o[1] = color.y, o[2] = color.z, o[3] = alpha;
+  }
 }

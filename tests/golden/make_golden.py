@@ -15,6 +15,7 @@ where /root/reference exists):
   shader_helpers.npz  intersect_box and uniform_sample_sphere from the reference's shaders_common.h
 
   ref_march.npz     whole frames from the reference's own raymarching() / raymarching_shadow() run on the host
+  ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
 Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
 """
@@ -272,6 +273,43 @@ def make_march_ref():
     np.savez_compressed(os.path.join(HERE, "ref_march.npz"), **out)
 
 
+# (volume size, TF, camera, spp, frame index, (width, height)): two sizes that are multiples of the 16-voxel macrocell and two that
+# are not (there the reference's scattered rays run on into the overhang of the last macrocells)
+PATH_REF_CASES = [(32, "sparse", "oblique", 1, 1, (48, 32)), (32, "ramp", "inside", 4, 7, (40, 24)),
+                  (20, "ramp", "oblique", 2, 1, (32, 20)), (28, "dense", "oblique", 1, 3, (36, 24))]
+
+
+def path_ref_scene(case, child_instance_xfm):
+    """OracleScene of one PATH_REF_CASES entry (shared by the generator and the test)."""
+    import ovr_b200
+    from helpers import oracle_desc
+    n, tf, cam, spp, fi, (w, h) = case
+    sc = ovr_b200.scenes.noise_scene(n, tf=tf, camera=cam, rate=1.0)
+    o = pyoracle.OracleScene(oracle_desc(sc, w, h, spp=spp))
+    o.s.pt_child_instance_xfm = int(child_instance_xfm)
+    return o, w, h, fi
+
+
+def make_path_ref():
+    """ref_path.npz: frames computed by the REFERENCE's own delta_tracking() / pathtracing() / render_pathtracing(), its macrocell
+    iterator and RandomTEA, cut out of shaders_pathtracing.cu / spatial_partition.h / random.h and executed on the host
+    (oracle/ref_march_shim.cpp, namespace pt). Two frames per case: x1 = scattered rays carried through the instance transform
+    again before the clip, as OptiX does (the reference's behaviour); x0 = clipped as the object-space rays they are."""
+    pyoracle.build()
+    out = {"n": np.int32(len(PATH_REF_CASES))}
+    for k, case in enumerate(PATH_REF_CASES):
+        for x in (0, 1):
+            o, w, h, fi = path_ref_scene(case, x)
+            ys, xs = np.mgrid[0:h, 0:w]
+            r = o.ref_path(np.stack([xs.ravel(), ys.ravel()], 1), frame_index=fi)
+            assert r is not None, "oracle/_ref/libovr_ref_march.so missing (needs /root/reference)"
+            out[f"rgba{k}_x{x}"] = r.reshape(h, w, 4)
+        d = (out[f"rgba{k}_x0"].view(np.uint32) != out[f"rgba{k}_x1"].view(np.uint32)).any(-1)
+        print(f"path case {k} {case}: mean radiance {out[f'rgba{k}_x1'][..., :3].mean():.4f} (x1) {out[f'rgba{k}_x0'][..., :3].mean():.4f} (x0), "
+              f"{int(d.sum())} of {w * h} pixels differ between the two clips")
+    np.savez_compressed(os.path.join(HERE, "ref_path.npz"), **out)
+
+
 def make_delta():
     """delta_hashit.npz: outputs of the reference's own DeltaTrackingIter<true>::hashit (oracle/ref_shim.cpp) for delta_cases()."""
     pyoracle.build()
@@ -295,6 +333,8 @@ if __name__ == "__main__":
         make_shader_helpers()
     elif len(sys.argv) > 1 and sys.argv[1] == "march":
         make_march_ref()
+    elif len(sys.argv) > 1 and sys.argv[1] == "path":
+        make_path_ref()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
     elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
@@ -306,3 +346,4 @@ if __name__ == "__main__":
         make_delta()
         make_shader_helpers()
         make_march_ref()
+        make_path_ref()

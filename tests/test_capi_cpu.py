@@ -25,16 +25,16 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/b200vr.h but not exported"
     assert sorted(capi.SYMBOLS) == names, "ctypes table and header drifted apart"
-    assert capi.lib().b200vr_abi_version() == 1
+    assert capi.lib().b200vr_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
-    assert C.sizeof(capi.Params) == 56
+    assert C.sizeof(capi.Params) == 60
     assert C.sizeof(capi.Stats) == 56
     p = capi.Params()
     capi.lib().b200vr_default_params(C.byref(p))
     assert (p.sampling_rate, p.base, p.spp, p.mode, p.shading, p.skip_empty, p.max_num_scatters) == (1.0, 1.0, 1, 0, 1, 1, 24)
-    assert abs(p.light_pos[1] - 2205.875) < 1e-3 and p.light_ambient == 1.0
+    assert abs(p.light_pos[1] - 2205.875) < 1e-3 and p.light_ambient == 1.0 and p.pt_child_instance_xfm == 0
 
 
 def _no_gpu():

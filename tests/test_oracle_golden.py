@@ -213,3 +213,49 @@ def test_reference_march_shim_live_and_threaded_equals_the_golden_frames():
             rgba, grad = o.ref_march(px, threads=threads)
             assert np.array_equal(rgba.reshape(h, w, 4).view(np.uint32), G[f"rgba{k}"].view(np.uint32)), (k, threads)
             assert np.array_equal(grad.reshape(h, w, 3).view(np.uint32), G[f"grad{k}"].view(np.uint32)), (k, threads)
+
+
+def _make_golden_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(__file__), "golden", "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    return mg
+
+
+def test_oracle_path_tracer_equals_the_reference_shader_code_bit_for_bit():
+    """The oracle's delta-tracking path tracer (oracle_path.cpp: TEA streams, pixel jitter, macrocell free-path iteration,
+    TF-classified tentative collisions, uniform sphere scattering, scatter_index bookkeeping, ambient term, albedo product)
+    against tests/golden/ref_path.npz -- whole frames computed by the REFERENCE's own delta_tracking() / pathtracing() /
+    render_pathtracing(), DeltaTrackingIter<true> and RandomTEA, cut out of its sources and executed on the host by
+    oracle/ref_march_shim.cpp. Both clips of the scattered rays: x1 = through the instance transform a second
+    time, as OptiX does with the object-space ray pathtracing() hands it (the reference's behaviour), x0 = clipped against the
+    volume (the B200 kernels' default). spp 1, 2 and 4 (pixel jitter on), frame indices 1, 3 and 7, volume sizes that are and
+    are not multiples of the 16-voxel macrocell. Every pixel bit-exact (host logf / sincosf on both sides)."""
+    mg = _make_golden_module()
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_path.npz"))
+    assert int(G["n"]) == len(mg.PATH_REF_CASES) >= 4
+    differ = []
+    for k, case in enumerate(mg.PATH_REF_CASES):
+        for x in (0, 1):
+            o, w, h, fi = mg.path_ref_scene(case, x)
+            rgba, cnt = o.render_path(frame_index=fi)
+            assert np.array_equal(rgba.view(np.uint32), G[f"rgba{k}_x{x}"].view(np.uint32)), f"case {k} {case} x{x}"
+            assert cnt["delta_samples"] > cnt["rays"] > 0 and rgba[..., :3].max() > 0
+        differ.append(int((G[f"rgba{k}_x0"].view(np.uint32) != G[f"rgba{k}_x1"].view(np.uint32)).any(-1).sum()))
+    # q14 shows exactly where the last macrocells overhang the volume: 32^3 no, 20^3 and 28^3 yes
+    assert differ[0] == 0 and differ[1] == 0 and differ[2] > 50 and differ[3] > 50
+
+
+def test_reference_path_shim_live_equals_the_golden_frames():
+    """Where oracle/_ref exists: the reference's path-tracing functions run live reproduce tests/golden/ref_path.npz."""
+    if not os.path.exists(os.path.join(os.path.dirname(pyoracle.__file__), "_ref", "libovr_ref_march.so")):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    mg = _make_golden_module()
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_path.npz"))
+    for k in (1, 2):
+        for x in (0, 1):
+            o, w, h, fi = mg.path_ref_scene(mg.PATH_REF_CASES[k], x)
+            ys, xs = np.mgrid[0:h, 0:w]
+            r = o.ref_path(np.stack([xs.ravel(), ys.ravel()], 1), frame_index=fi).reshape(h, w, 4)
+            assert np.array_equal(r.view(np.uint32), G[f"rgba{k}_x{x}"].view(np.uint32)), (k, x)
