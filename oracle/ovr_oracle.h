@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE ONLY -- CPU oracle for the B200 volume device. The reference tree has no tests, golden images or
  * known-answer vectors for this path; the oracle is pinned by outputs of the reference's own code
- * compiled and run on the host (oracle/_ref: whole ray-marched frames from its raymarching() / raymarching_shadow(), its
- * dda.h, RandomTEA, DeltaTrackingIter, intersect_box, uniform_sample_sphere, gdt transforms, mask kernels, tfn loader --
+ * compiled and run on the host (oracle/_ref: whole ray-marched frames from its raymarching() / raymarching_shadow(), whole
+ * path-traced frames from its delta_tracking() / pathtracing() / render_pathtracing(), its dda.h, RandomTEA, DeltaTrackingIter, intersect_box, uniform_sample_sphere, gdt transforms, mask kernels, tfn loader --
  * fixtures under tests/golden/, all bit-exact) and, for the texture unit, by fetches captured on the B200.
  *
  * A CPU restatement (fp32, C++17, no CUDA) of the reference's optix7 shader arithmetic:
