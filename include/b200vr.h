@@ -59,8 +59,9 @@ typedef struct b200vr_params {
    * (shaders_pathtracing.cu:510-513) and OptiX applies the instance's world-to-object transform to them once more before
    * __intersection__volume (shaders_common.h:379-392) clips them, so in the reference their far end is bounded by the
    * macrocell grid, not by the volume: where dims % 16 != 0 they go on colliding with clamp-to-edge voxels in the
-   * overhang of the last macrocells. 0 (default) = clip them against the volume as the object-space rays they are;
-   * 1 = the reference's behaviour, bit for bit (oracle/ref_march_shim.cpp runs the reference code). */
+   * overhang of the last macrocells. 1 (default) = the reference's behaviour (pinned by the reference's
+   * own code run on the host, oracle/ref_march_shim.cpp); 0 = clip them against the volume as the object-space rays they
+   * are. Frames are identical under both where every dim is a multiple of 16. */
   int32_t pt_child_instance_xfm;
 } b200vr_params;
 

@@ -148,7 +148,7 @@ extern "C" void b200vr_default_params(b200vr_params* p)
   p->light_pos[1] = 2205.875f;
   p->light_pos[2] = -400.0267f;
   p->light_ambient = 1.f;
-  p->pt_child_instance_xfm = 0;
+  p->pt_child_instance_xfm = 1; // the reference's behaviour
 }
 
 extern "C" const char* b200vr_last_error(const b200vr_t* h) { return h ? h->error.c_str() : g_create_error.c_str(); }

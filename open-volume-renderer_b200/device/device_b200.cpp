@@ -81,7 +81,7 @@ struct DeviceB200::Impl {
     prm.shading = env_int("OVR_B200_SHADING", B200VR_SHADING_REF);
     prm.sampler = env_int("OVR_B200_SAMPLER", B200VR_SAMPLER_TEX3D);
     prm.skip_empty = env_int("OVR_B200_SKIP_EMPTY", 1);
-    prm.pt_child_instance_xfm = env_int("OVR_B200_PT_CHILD_INSTANCE_XFM", 0);
+    prm.pt_child_instance_xfm = env_int("OVR_B200_PT_CHILD_INSTANCE_XFM", 1);
     build_scene(parent->current_scene);
     initialized = true;
   }

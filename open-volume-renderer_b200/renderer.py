@@ -81,7 +81,7 @@ class MainRenderer:
         self.shading = capi.SHADING_REF
         self.sampler = capi.SAMPLER_TEX3D
         self.skip_empty = True
-        self.pt_child_instance_xfm = False  # b200vr_params::pt_child_instance_xfm (the reference's scattered-ray clip, q14)
+        self.pt_child_instance_xfm = True  # b200vr_params::pt_child_instance_xfm (the reference's scattered-ray clip, q14)
         self.premultiplied = False
         # sparse sampling state as the device holds it (defaults of apps/main_app.cpp:122-126)
         self._focus_center, self._focus_scale, self._base_noise, self._sparse = (0.5, 0.5), 0.06, 0.07, False

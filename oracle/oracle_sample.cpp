@@ -212,6 +212,7 @@ extern "C" void ovr_oracle_default_scene(ovr_oracle_scene* s)
   s->light_pos[2] = -400.0267f;
   s->light_ambient = 1.f;
   for (int i = 0; i < 3; i++) s->clip_hi[i] = 1.f;
+  s->pt_child_instance_xfm = 1; // the reference's behaviour under OptiX
 }
 
 extern "C" void ovr_oracle_camera(const float from[3], const float at[3], const float up[3], float fovy, int width,

@@ -63,8 +63,8 @@ typedef struct ovr_oracle_scene {
   /* macrocells, built with ovr_oracle_build_macrocells (needed by skip_empty and by path tracing) */
   const float* mc_majorants;
   int32_t mc_dims[3];
-  /* path tracing, SURVEY A.7 q14: 0 = scattered rays are clipped against the unit cube as the object-space rays they are (what
-   * the B200 kernels do); 1 = as the reference behaves under OptiX: pathtracing() hands the scattered ray to optixTrace already
+  /* path tracing, SURVEY A.7 q14: 0 = scattered rays are clipped against the unit cube as the object-space rays they are;
+   * 1 (default, ovr_oracle_default_scene) = as the reference behaves under OptiX: pathtracing() hands the scattered ray to optixTrace already
    * in object space (shaders_pathtracing.cu:510-513) and the instance transform is applied to it a second time before
    * __intersection__volume clips it, so its far end is bounded by the macrocell grid only (differs when dims % 16 != 0). */
   int32_t pt_child_instance_xfm;

@@ -204,7 +204,7 @@ enum RayType { PATHTRACING_RAY_TYPE = 0, RAY_TYPE_COUNT }; // shaders_pathtracin
 #define VARYING_MAJORANT 1
 // 1: OptiX semantics -- the instance's world-to-object transform is applied to EVERY traced ray before __intersection__volume
 //    clips it, also to the scattered rays, which pathtracing() hands to optixTrace already in object space (:510-513);
-// 0: scattered rays are clipped as the object-space rays they are (the B200 kernels' default).
+// 0: scattered rays are clipped as the object-space rays they are.
 // Same meaning as ovr_oracle_scene::pt_child_instance_xfm, which ref_path_rays reads.
 static thread_local int g_child_instance_xfm = 1;
 static inline int optixGetGASTraversableHandle() { return 0; }

@@ -34,7 +34,7 @@ def test_struct_layouts_match_header():
     p = capi.Params()
     capi.lib().b200vr_default_params(C.byref(p))
     assert (p.sampling_rate, p.base, p.spp, p.mode, p.shading, p.skip_empty, p.max_num_scatters) == (1.0, 1.0, 1, 0, 1, 1, 24)
-    assert abs(p.light_pos[1] - 2205.875) < 1e-3 and p.light_ambient == 1.0 and p.pt_child_instance_xfm == 0
+    assert abs(p.light_pos[1] - 2205.875) < 1e-3 and p.light_ambient == 1.0 and p.pt_child_instance_xfm == 1
 
 
 def _no_gpu():
