@@ -506,8 +506,8 @@ extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, in
 
 static void derive_camera(b200vr_t* h)
 {
-  // device_impl.cpp:125-136; tan is evaluated in double on the host like the reference
-  const float t = 2.f * (float)std::tan((double)(h->la_fovy * 0.5f * (float)M_PI / 180.f));
+  // device_impl.cpp:125-136; tan(float) is the float overload (tanf) in the reference's host code (tests/golden/host_derivations.npz)
+  const float t = 2.f * std::tan(h->la_fovy * 0.5f * (float)M_PI / 180.f);
   const float aspect = (float)h->width / (float)h->height;
   const f3 from = mk3(h->la_from[0], h->la_from[1], h->la_from[2]), at = mk3(h->la_at[0], h->la_at[1], h->la_at[2]);
   const f3 up = mk3(h->la_up[0], h->la_up[1], h->la_up[2]);

@@ -219,8 +219,9 @@ extern "C" void ovr_oracle_camera(const float from[3], const float at[3], const 
                                   int height, float position[3], float direction[3], float horizontal[3],
                                   float vertical[3])
 {
-  // device_impl.cpp:125-136 ("the factor 2.f ... to match ospray"); tan evaluated in double like the host code
-  const float t = 2.f * float(std::tan(double(fovy * 0.5f * float(M_PI) / 180.f)));
+  // device_impl.cpp:125-136 ("the factor 2.f ... to match ospray"); the reference's unqualified tan(float) resolves to the float
+  // overload (tanf) under g++ / libstdc++: pinned by ref_camera (oracle/ref_shim.cpp) in tests/golden/host_derivations.npz
+  const float t = 2.f * std::tan(fovy * 0.5f * float(M_PI) / 180.f);
   const float aspect = float(width) / float(height);
   const vec3 f = v3(from[0], from[1], from[2]), a = v3(at[0], at[1], at[2]), u = v3(up[0], up[1], up[2]);
   const vec3 d = normalize(a - f);

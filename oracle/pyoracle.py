@@ -144,6 +144,24 @@ def ref_clip(org, dr, lo, hi, t0=0.0, t1=np.finfo(np.float32).max):
     return bool(ok), a.value, b.value
 
 
+def ref_camera(frm, at, up, fovy, width, height):
+    """Device camera from the look-at camera by the reference's own statements (device_impl.cpp:128-136, oracle/ref_shim.cpp):
+    float32 [12] = position, direction, horizontal, vertical."""
+    out = np.zeros(12, np.float32)
+    ref_kat_lib().ref_camera(_fp(np.ascontiguousarray(frm, np.float32)), _fp(np.ascontiguousarray(at, np.float32)),
+                             _fp(np.ascontiguousarray(up, np.float32)), C.c_float(fovy), int(width), int(height), _fp(out))
+    return out
+
+
+def ref_volume_matrix(grid_origin, grid_spacing, dims):
+    """Object-to-world matrix of the volume instance and its inverse by the reference's own statements
+    (device_impl.cpp:288-296, gdt rcp): float32 [24] = otw 3x4 row major, wto 3x4 row major."""
+    out = np.zeros(24, np.float32)
+    ref_kat_lib().ref_volume_matrix(_fp(np.ascontiguousarray(grid_origin, np.float32)), _fp(np.ascontiguousarray(grid_spacing, np.float32)),
+                                    _p(np.ascontiguousarray(dims, np.int32)), _fp(out))
+    return out
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 

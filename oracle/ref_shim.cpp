@@ -188,3 +188,37 @@ extern "C" void ref_uniform_sphere(float sx, float sy, float out[3])
   const vec3f v = ref_shader::uniform_sample_sphere(1.f, vec2f(sx, sy));
   out[0] = v.x, out[1] = v.y, out[2] = v.z;
 }
+
+// ---- host-side derivations of DeviceOptix7::Impl, statement ranges cut out of ovr/devices/optix7/device_impl.cpp at build time ----
+// commit(): the device camera from the look-at camera (:128-136). out = position, direction, horizontal, vertical.
+extern "C" void ref_camera(const float from[3], const float at[3], const float up[3], float fovy_deg, int width, int height, float out[12])
+{
+  struct { vec3f from, at, up; struct { float fovy; } perspective; } camera;
+  camera.from = vec3f(from[0], from[1], from[2]), camera.at = vec3f(at[0], at[1], at[2]), camera.up = vec3f(up[0], up[1], up[2]);
+  camera.perspective.fovy = fovy_deg;
+  struct DeviceCamera { vec3f position, direction, horizontal, vertical; };
+  struct { struct { vec2i size; } frame; DeviceCamera camera, last_camera; } params;
+  params.frame.size = vec2i(width, height);
+#include <camera_extract.h>
+  const vec3f v[4] = { params.camera.position, params.camera.direction, params.camera.horizontal, params.camera.vertical };
+  for (int i = 0; i < 4; i++) out[3 * i] = v[i].x, out[3 * i + 1] = v[i].y, out[3 * i + 2] = v[i].z;
+}
+
+// buildScene(): object-to-world matrix of the volume instance (:288-296), then its inverse as get_xfm_wto() rebuilds it from
+// the instance's 3x4 (gdt rcp). out = otw 3x4 row major, wto 3x4 row major.
+extern "C" void ref_volume_matrix(const float grid_origin[3], const float grid_spacing[3], const int32_t dims[3], float out[24])
+{
+  struct { vec3f grid_origin, grid_spacing; struct D { vec3i dims; } d, *data = &d; } scene_volume;
+  scene_volume.grid_origin = vec3f(grid_origin[0], grid_origin[1], grid_origin[2]);
+  scene_volume.grid_spacing = vec3f(grid_spacing[0], grid_spacing[1], grid_spacing[2]);
+  scene_volume.d.dims = vec3i(dims[0], dims[1], dims[2]);
+  struct { affine3f matrix; } v;
+#include <volume_matrix_extract.h>
+  const affine3f a = v.matrix, inv = rcp(a);
+  const affine3f* m[2] = { &a, &inv };
+  for (int k = 0; k < 2; k++) {
+    const affine3f& x = *m[k];
+    const float r[12] = { x.l.vx.x, x.l.vy.x, x.l.vz.x, x.p.x, x.l.vx.y, x.l.vy.y, x.l.vz.y, x.p.y, x.l.vx.z, x.l.vy.z, x.l.vz.z, x.p.z };
+    for (int i = 0; i < 12; i++) out[12 * k + i] = r[i];
+  }
+}

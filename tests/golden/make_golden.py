@@ -15,6 +15,7 @@ where /root/reference exists):
   shader_helpers.npz  intersect_box and uniform_sample_sphere from the reference's shaders_common.h
 
   ref_march.npz     whole frames from the reference's own raymarching() / raymarching_shadow() run on the host
+  host_derivations.npz  device camera and instance matrices from the reference's own host statements (device_impl.cpp)
   ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
 Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
@@ -310,6 +311,35 @@ def make_path_ref():
     np.savez_compressed(os.path.join(HERE, "ref_path.npz"), **out)
 
 
+def host_derivation_inputs():
+    """Seeded look-at cameras / frame sizes and volume placements (shared by the generator and the test)."""
+    rng = np.random.default_rng(20261105)
+    cams = []
+    for k in range(400):
+        frm = (rng.normal(size=3) * rng.choice([1, 100, 1000])).astype(np.float32)
+        at = (rng.normal(size=3) * 10).astype(np.float32)
+        up = rng.normal(size=3).astype(np.float32)
+        cams.append((frm, at, up, np.float32(rng.uniform(5, 120)), int(rng.integers(16, 4000)), int(rng.integers(16, 3000))))
+    cams.append((np.array([0, 0, -5], np.float32), np.zeros(3, np.float32), np.array([0, 1, 0], np.float32), np.float32(60), 1920, 1080))
+    vols = []
+    for k in range(200):
+        org = (rng.normal(size=3) * rng.choice([0, 1, 10])).astype(np.float32)
+        vols.append((np.abs(org) * np.sign(org + 1e-30).astype(np.float32) if k % 2 else np.zeros(3, np.float32),
+                     rng.uniform(0.1, 3, size=3).astype(np.float32), rng.integers(2, 4097, size=3).astype(np.int32)))
+    return cams, vols
+
+
+def make_host_derivations():
+    """host_derivations.npz: the device camera of DeviceOptix7::Impl::commit (device_impl.cpp:128-136) and the instance matrix of
+    buildScene (:288-296) with its gdt inverse, computed by the reference's own statements (cut out at build time, ref_shim.cpp)."""
+    pyoracle.build()
+    cams, vols = host_derivation_inputs()
+    out = {"camera": np.array([pyoracle.ref_camera(*c) for c in cams]),
+           "matrix": np.array([pyoracle.ref_volume_matrix(*v) for v in vols])}
+    np.savez_compressed(os.path.join(HERE, "host_derivations.npz"), **out)
+    print(f"wrote host_derivations.npz: {len(cams)} cameras, {len(vols)} volume placements")
+
+
 def make_delta():
     """delta_hashit.npz: outputs of the reference's own DeltaTrackingIter<true>::hashit (oracle/ref_shim.cpp) for delta_cases()."""
     pyoracle.build()
@@ -335,6 +365,8 @@ if __name__ == "__main__":
         make_march_ref()
     elif len(sys.argv) > 1 and sys.argv[1] == "path":
         make_path_ref()
+    elif len(sys.argv) > 1 and sys.argv[1] == "host":
+        make_host_derivations()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
         make_sparse()
     elif len(sys.argv) > 1 and sys.argv[1] == "tfn":
@@ -347,3 +379,4 @@ if __name__ == "__main__":
         make_shader_helpers()
         make_march_ref()
         make_path_ref()
+        make_host_derivations()

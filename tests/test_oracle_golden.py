@@ -5,7 +5,7 @@ import os
 import numpy as np
 import pytest
 
-from helpers import pyoracle
+from helpers import ovr_b200, pyoracle
 
 G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_kat.npz"))
 
@@ -259,3 +259,24 @@ def test_reference_path_shim_live_equals_the_golden_frames():
             ys, xs = np.mgrid[0:h, 0:w]
             r = o.ref_path(np.stack([xs.ravel(), ys.ravel()], 1), frame_index=fi).reshape(h, w, 4)
             assert np.array_equal(r.view(np.uint32), G[f"rgba{k}_x{x}"].view(np.uint32)), (k, x)
+
+
+def test_host_derivations_equal_the_reference_statements():
+    """Camera set-up of commit() (device_impl.cpp:128-136; its tan(float) is the float overload) and the instance matrix of
+    buildScene() (:288-296) with the gdt inverse the shaders rebuild: the oracle's ovr_oracle_camera (same expression as
+    b200vr.cu derive_camera) bit-exact on 401 cameras; Volume.obj_to_world + the oracle's affine inverse equal on 200 placements
+    (numerically: the reference's translate * scale product turns a -0 origin into +0)."""
+    mg = _make_golden_module()
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "host_derivations.npz"))
+    cams, vols = mg.host_derivation_inputs()
+    assert len(cams) == len(G["camera"]) and len(vols) == len(G["matrix"])
+    for c, want in zip(cams, G["camera"]):
+        got = pyoracle.camera(*c)
+        got = np.concatenate([np.asarray(got[k], np.float32) for k in ("position", "direction", "horizontal", "vertical")])
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), c
+    for (org, sp, dims), want in zip(vols, G["matrix"]):
+        v = ovr_b200.scenes.Volume(noise={"seed": 1, "org": (0, 0, 0), "dims": tuple(int(d) for d in dims)},
+                                   grid_origin=tuple(org), grid_spacing=tuple(sp))
+        m = np.asarray(v.obj_to_world(), np.float32)
+        inv = pyoracle.xfm(m, np.zeros(3, np.float32))[12:24]
+        assert np.array_equal(m, want[:12]) and np.array_equal(inv, want[12:]), (org, sp, dims)
