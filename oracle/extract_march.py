@@ -32,6 +32,7 @@ ITEMS = [
     (COMMON, r"^sample_transfer_function\(", r"^\}", "m_sample_tf.h"),
     (MARCH, r"^raymarching_shadow\(", r"^\}", "m_raymarching_shadow.h"),
     (MARCH, r"^raymarching\(", r"^\}", "m_raymarching.h"),
+    (MARCH, r"^render_raymarching\(vec3f org,", r"^\}", "m_render_raymarching.h"),
     # delta-tracking path tracer (ref_march_shim.cpp, namespace pt)
     (COMMON, r"^struct PathTracingPayload \{", r"^\};", "p_payload.h"),
     (SPART, r"^  DeviceSpacePartiton_SingleMC::iter\(", r"^  \}", "p_sp_iter.h"),

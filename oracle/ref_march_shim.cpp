@@ -11,7 +11,8 @@
 //     raymarching_shadow), restated in optixTrace() below with the reference's own intersect_box;
 //   * launch parameters, transform getters' matrix source, __frcp_rn (IEEE), __powf (its CUDA definition exp2f(y * log2f(x)) with the host's exp2 / log2: only reached when
 //     step * base is not within 1e-7 of 1, i.e. at the last partial step of a ray or when the running fp32 sum drifts by an ulp).
-// tests/golden/make_golden.py drives ref_march_rays() to produce tests/golden/ref_march.npz, which pins the oracle's march.
+// tests/golden/make_golden.py drives ref_march_rays() to produce tests/golden/ref_march.npz and ref_march_spp.npz, and
+// ref_path_rays() (the reference's path tracer, namespace pt below) to produce ref_path.npz; they pin the oracle.
 #include <algorithm>
 #include <cassert>
 #include <cmath>
@@ -132,8 +133,13 @@ static inline void optixGetObjectToWorldTransformMatrix(float m[12]) { std::memc
 
 // ---- OptiX plumbing of the shadow ray ----
 enum RayType { RAYMARCHING_RAY_TYPE = 0, SHADOW_RAY_TYPE, RAY_TYPE_COUNT }; // shaders_raymarching.cu:41
-struct OptixVisibilityMask { explicit OptixVisibilityMask(int) {} };
+struct OptixVisibilityMask {
+  unsigned m;
+  explicit OptixVisibilityMask(unsigned long long v) : m((unsigned)(v & 255u)) {} // 8-bit masks in OptiX
+};
 enum { OPTIX_RAY_FLAG_DISABLE_ANYHIT = 1 };
+#define VISIBILITY_VOLUME (1ULL << 0) // params.h:52-53
+#define VISIBILITY_GEOMETRY (1ULL << 1)
 static inline void pack_pointer(void* ptr, uint32_t& i0, uint32_t& i1)
 {
   const uint64_t u = reinterpret_cast<uint64_t>(ptr);
@@ -177,23 +183,43 @@ static inline void
 #include <m_raymarching_shadow.h>
 static inline void
 #include <m_raymarching.h>
+static inline void
+#include <m_render_raymarching.h>
 
-// what the pipeline does with a SHADOW_RAY_TYPE ray: __intersection__volume, then __closesthit__volume_shadow
-static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float, OptixVisibilityMask, int, int, int, int, uint32_t& u0,
-                       uint32_t& u1)
+// what the pipeline does with a traced ray. SHADOW_RAY_TYPE: __intersection__volume, then __closesthit__volume_shadow
+// (shaders_raymarching.cu:205-229) or __miss__shadow (:249-253). RAYMARCHING_RAY_TYPE (render_raymarching's two traces):
+// the scene holds one volume instance (visibility VISIBILITY_VOLUME) and no geometry, so the "non-volume" trace misses;
+// the volume trace runs __intersection__volume on the instance-transformed ray, then __closesthit__volume_raymarching
+// (:178-203, ray jitter compiled out) or __miss__raymarching (:237-246).
+static void optixTrace(int, vec3f org, vec3f dir, float tmin, float tmax, float, OptixVisibilityMask mask, int, int ray_type, int, int,
+                       uint32_t& u0, uint32_t& u1)
 {
-  ShadowPayload& data = *(ShadowPayload*)unpack_pointer(u0, u1);
   const affine3f wto = get_xfm_wto();
   float t0 = tmin, t1 = tmax;
-  if (intersect_box(t0, t1, xfmPoint(wto, org), xfmVector(wto, dir), vec3f(0.f), vec3f(1.f))) {
-    const float step = g_self->step * 10.f; // "we use a lower sampling rate for shadow"
-    raymarching_shadow(*g_self, org, dir, t0, t1, step, data);
+  if (ray_type == SHADOW_RAY_TYPE) {
+    ShadowPayload& data = *(ShadowPayload*)unpack_pointer(u0, u1);
+    if (intersect_box(t0, t1, xfmPoint(wto, org), xfmVector(wto, dir), vec3f(0.f), vec3f(1.f))) {
+      const float step = g_self->step * 10.f; // "we use a lower sampling rate for shadow"
+      raymarching_shadow(*g_self, org, dir, t0, t1, step, data);
+      data.t_max = t1 + float_small;
+    }
+    else
+      data.t_max = tmax; // __miss__shadow
+    return;
+  }
+  RayMarchingPayload& data = *(RayMarchingPayload*)unpack_pointer(u0, u1);
+  if ((mask.m & VISIBILITY_VOLUME) && intersect_box(t0, t1, xfmPoint(wto, org), xfmVector(wto, dir), vec3f(0.f), vec3f(1.f))) {
+    raymarching(*g_self, org, dir, t0, t1, data);
     data.t_max = t1 + float_small;
   }
-  else
-    data.t_max = tmax; // __miss__shadow
+  else { // __miss__raymarching
+    data.t_max = tmax;
+    if (mask.m & ~VISIBILITY_VOLUME) {
+      data.color = vec3f(0.0, 0.0, 0.0);
+      data.alpha = 0.f;
+    }
+  }
 }
-
 
 // ---- the delta-tracking path tracer: delta_tracking(), pathtracing(), render_pathtracing() (shaders_pathtracing.cu:269-542,
 // 603-631) compiled from the reference's text; this namespace supplies that file's ray-type enum and what the pipeline does
@@ -277,19 +303,29 @@ extern "C" void ref_march_rays(const ovr_oracle_scene* s, const int32_t* pixels_
   lp.last_camera = lp.camera;
   lp.light_directional_pos = vec3f(s->light_pos[0], s->light_pos[1], s->light_pos[2]);
   const vec2f rsize = vec2f(1.f) / vec2f((float)s->width, (float)s->height);
+  const int spp = s->spp;
   for (int64_t i = 0; i < n_pixels; i++) {
+    // __raygen__render_frame (:323-413): RandomTEA(frame_index, pixel_index), pixel jitter when spp > 1, mean over spp
     const int ix = pixels_xy[2 * i], iy = pixels_xy[2 * i + 1];
-    const vec2f screen = vec2f((float)ix + .5f, (float)iy + .5f) * rsize; // compute_screen_position, method 1
-    const vec3f org = lp.camera.position;
-    const vec3f dir = normalize(lp.camera.direction + (screen.x - 0.5f) * lp.camera.horizontal + (screen.y - 0.5f) * lp.camera.vertical);
-    RayMarchingPayload payload;
-    const affine3f wto = get_xfm_wto();
-    float t0 = 0.f, t1 = ref_march::inf;
-    if (intersect_box(t0, t1, xfmPoint(wto, org), xfmVector(wto, dir), vec3f(0.f), vec3f(1.f)))
-      raymarching(self, org, dir, t0, t1, payload);
-    const float alpha = payload.alpha; // background alpha 0
-    const vec3f c = alpha_blend(payload.color, vec3f(0.f), payload.alpha, 0.f, alpha);
-    const vec3f g = alpha_blend(payload.gradient, vec3f(0.f), payload.alpha, 0.f, alpha);
+    const vec2f screen_coord = vec2f((float)ix + .5f, (float)iy + .5f) * rsize; // compute_screen_position, method 1
+    const uint32_t pixel_index = (uint32_t)ix + (uint32_t)iy * (uint32_t)s->width;
+    RandomTEA rng_state((uint32_t)s->frame_index, pixel_index);
+    float alpha = 0.f;
+    vec3f c = 0.f, g = 0.f;
+    vec2f flow = 0.f;
+    for (int k = 0; k < spp; k++) {
+      vec2f screen = screen_coord;
+      if (spp > 1) {
+        const vec2f pixel_jitter = vec2f(rng_state.get_floats()) - 0.5f;
+        screen += pixel_jitter * rsize;
+      }
+      const vec3f dir = normalize(lp.camera.direction + (screen.x - 0.5f) * lp.camera.horizontal + (screen.y - 0.5f) * lp.camera.vertical);
+      render_raymarching(lp.camera.position, dir, &rng_state, alpha, c, g, flow);
+    }
+    const float rspp = 1.f / spp;
+    alpha *= rspp;
+    c *= rspp;
+    g *= rspp;
     float* o = out + 7 * i;
     o[0] = c.x, o[1] = c.y, o[2] = c.z, o[3] = alpha, o[4] = g.x, o[5] = g.y, o[6] = g.z;
   }

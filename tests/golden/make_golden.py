@@ -16,6 +16,7 @@ where /root/reference exists):
 
   ref_march.npz     whole frames from the reference's own raymarching() / raymarching_shadow() run on the host
   host_derivations.npz  device camera and instance matrices from the reference's own host statements (device_impl.cpp)
+  ref_march_spp.npz the same with 2-4 samples per pixel (RandomTEA pixel jitter of the raygen program)
   ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
 Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
@@ -274,6 +275,35 @@ def make_march_ref():
     np.savez_compressed(os.path.join(HERE, "ref_march.npz"), **out)
 
 
+# n, TF preset, camera preset, sampling rate, spp, frame index, (W, H): pixel jitter + mean over spp of __raygen__render_frame
+MARCH_SPP_CASES = [(32, "sparse", "oblique", 1.0, 4, 1, (48, 32)), (24, "ramp", "inside", 2.0, 2, 5, (40, 24)),
+                   (28, "dense", "front", 0.7, 3, 2, (36, 24))]
+
+
+def march_spp_scene(case):
+    import ovr_b200
+    from helpers import oracle_desc
+    n, tf, cam, rate, spp, fi, (w, h) = case
+    sc = ovr_b200.scenes.noise_scene(n, tf=tf, camera=cam, rate=rate)
+    return pyoracle.OracleScene(oracle_desc(sc, w, h, spp=spp)), w, h, fi
+
+
+def make_march_spp():
+    """ref_march_spp.npz: ray-marched frames with several samples per pixel -- the reference's render_raymarching() (two traces,
+    background blend) and raymarching() under the raygen loop of __raygen__render_frame (RandomTEA pixel jitter, mean)."""
+    pyoracle.build()
+    out = {"n": np.int32(len(MARCH_SPP_CASES))}
+    for k, case in enumerate(MARCH_SPP_CASES):
+        o, w, h, fi = march_spp_scene(case)
+        o.s.frame_index = fi
+        ys, xs = np.mgrid[0:h, 0:w]
+        r = o.ref_march(np.stack([xs.ravel(), ys.ravel()], 1), threads=0)
+        assert r is not None, "oracle/_ref/libovr_ref_march.so missing (needs /root/reference)"
+        out[f"rgba{k}"], out[f"grad{k}"] = r[0].reshape(h, w, 4), r[1].reshape(h, w, 3)
+    np.savez_compressed(os.path.join(HERE, "ref_march_spp.npz"), **out)
+    print(f"wrote ref_march_spp.npz: {len(MARCH_SPP_CASES)} frames")
+
+
 # (volume size, TF, camera, spp, frame index, (width, height)): two sizes that are multiples of the 16-voxel macrocell and two that
 # are not (there the reference's scattered rays run on into the overhang of the last macrocells, SURVEY A.7 q14)
 PATH_REF_CASES = [(32, "sparse", "oblique", 1, 1, (48, 32)), (32, "ramp", "inside", 4, 7, (40, 24)),
@@ -365,6 +395,8 @@ if __name__ == "__main__":
         make_march_ref()
     elif len(sys.argv) > 1 and sys.argv[1] == "path":
         make_path_ref()
+    elif len(sys.argv) > 1 and sys.argv[1] == "march_spp":
+        make_march_spp()
     elif len(sys.argv) > 1 and sys.argv[1] == "host":
         make_host_derivations()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
@@ -380,3 +412,4 @@ if __name__ == "__main__":
         make_march_ref()
         make_path_ref()
         make_host_derivations()
+        make_march_spp()

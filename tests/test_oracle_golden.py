@@ -280,3 +280,18 @@ def test_host_derivations_equal_the_reference_statements():
         m = np.asarray(v.obj_to_world(), np.float32)
         inv = pyoracle.xfm(m, np.zeros(3, np.float32))[12:24]
         assert np.array_equal(m, want[:12]) and np.array_equal(inv, want[12:]), (org, sp, dims)
+
+
+def test_oracle_march_with_pixel_jitter_equals_the_reference_shader_code():
+    """spp 2 / 3 / 4, frame indices 1 / 5 / 2: the oracle's raygen loop (TEA(frame_index, pixel_index), jitter, mean over spp,
+    background blend) against frames from the reference's render_raymarching() + raymarching() under the same loop
+    (tests/golden/ref_march_spp.npz); every pixel and layer bit-exact."""
+    mg = _make_golden_module()
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_march_spp.npz"))
+    assert int(G["n"]) == len(mg.MARCH_SPP_CASES)
+    for k, case in enumerate(mg.MARCH_SPP_CASES):
+        o, w, h, fi = mg.march_spp_scene(case)
+        rgba, grad, cnt = o.render_march(frame_index=fi)
+        assert cnt["rays"] == w * h * case[4]
+        assert np.array_equal(rgba.view(np.uint32), G[f"rgba{k}"].view(np.uint32)), case
+        assert np.array_equal(grad.view(np.uint32), G[f"grad{k}"].view(np.uint32)), case
