@@ -153,6 +153,16 @@ def ref_camera(frm, at, up, fovy, width, height):
     return out
 
 
+def ref_value_ranges(vol):
+    """Macrocell value ranges [mz, my, mx, 2] by the reference's own value_range_kernel run on the host (oracle/ref_shim.cpp)."""
+    vol = np.ascontiguousarray(vol, np.float32)
+    dims = (vol.shape[2], vol.shape[1], vol.shape[0])
+    mc = macrocell_dims(dims)
+    r = np.empty((mc[2], mc[1], mc[0], 2), np.float32)
+    ref_kat_lib().ref_value_ranges(_fp(vol), _i3(*dims), _fp(r))
+    return r
+
+
 def ref_volume_matrix(grid_origin, grid_spacing, dims):
     """Object-to-world matrix of the volume instance and its inverse by the reference's own statements
     (device_impl.cpp:288-296, gdt rcp): float32 [24] = otw 3x4 row major, wto 3x4 row major."""

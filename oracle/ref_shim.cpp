@@ -222,3 +222,41 @@ extern "C" void ref_volume_matrix(const float grid_origin[3], const float grid_s
     for (int i = 0; i < 12; i++) out[12 * k + i] = r[i];
   }
 }
+
+// ---- macrocell value ranges: the reference's value_range_kernel (accel/sp_singlemc.cu:10-54), body cut out at build time and run
+// one "thread" per macrocell on the host. The texture is point-read at voxel centres there ((i + 0.5) / dims with a linear
+// filter: weight 0), so tex3D is the voxel itself. (majorant_kernel is not run here: its float -> uint32 conversion of -1.f is
+// undefined behaviour and gives 0xffffffff on x86 where the GPU saturates to 0 -- SURVEY A.7 q7.) ----
+#include <gdt/math/box.h>
+namespace ref_mc {
+using gdt::range1f;
+struct Idx3 { int x, y, z; };
+static Idx3 threadIdx, blockIdx, blockDim;
+struct Tex { const float* v; int nx, ny, nz; };
+typedef const Tex* cudaTextureObject_t;
+static inline void tex3D(float* f, cudaTextureObject_t t, float x, float y, float z)
+{
+  const int ix = std::min(t->nx - 1, std::max(0, (int)std::floor(x * (float)t->nx)));
+  const int iy = std::min(t->ny - 1, std::max(0, (int)std::floor(y * (float)t->ny)));
+  const int iz = std::min(t->nz - 1, std::max(0, (int)std::floor(z * (float)t->nz)));
+  *f = t->v[(size_t)ix + (size_t)t->nx * ((size_t)iy + (size_t)t->ny * (size_t)iz)];
+}
+static void
+#include <value_range_extract.h>
+} // namespace ref_mc
+
+extern "C" void ref_value_ranges(const float* voxels, const int32_t dims[3], float* ranges)
+{
+  using namespace ref_mc;
+  const Tex tex{ voxels, dims[0], dims[1], dims[2] };
+  const vec3i mc((dims[0] + 15) / 16, (dims[1] + 15) / 16, (dims[2] + 15) / 16); // div_round_up, sp_singlemc.cu:102
+  std::vector<range1f> out((size_t)mc.x * mc.y * mc.z);
+  ref_mc::blockDim = { 1, 1, 1 }, ref_mc::threadIdx = { 0, 0, 0 };
+  for (int z = 0; z < mc.z; z++)
+    for (int y = 0; y < mc.y; y++)
+      for (int x = 0; x < mc.x; x++) {
+        ref_mc::blockIdx = { x, y, z };
+        value_range_kernel(vec3i(dims[0], dims[1], dims[2]), &tex, mc, 16u, out.data());
+      }
+  for (size_t i = 0; i < out.size(); i++) ranges[2 * i] = out[i].lower, ranges[2 * i + 1] = out[i].upper;
+}

@@ -17,6 +17,7 @@ where /root/reference exists):
   ref_march.npz     whole frames from the reference's own raymarching() / raymarching_shadow() run on the host
   host_derivations.npz  device camera and instance matrices from the reference's own host statements (device_impl.cpp)
   ref_march_spp.npz the same with 2-4 samples per pixel (RandomTEA pixel jitter of the raygen program)
+  value_ranges.npz  macrocell value ranges from the reference's value_range_kernel run on the host
   ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
 Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
@@ -341,6 +342,22 @@ def make_path_ref():
     np.savez_compressed(os.path.join(HERE, "ref_path.npz"), **out)
 
 
+VALUE_RANGE_DIMS = [(32, 32, 32), (70, 45, 33), (17, 16, 15), (100, 1, 37), (48, 31, 64)]
+
+
+def value_range_volume(dims):
+    rng = np.random.default_rng(dims[0] * 1000003 + dims[1] * 1009 + dims[2])
+    return rng.random((dims[2], dims[1], dims[0]), dtype=np.float32)
+
+
+def make_value_ranges():
+    """value_ranges.npz: macrocell value ranges from the reference's value_range_kernel (accel/sp_singlemc.cu:10-54) run on the host."""
+    pyoracle.build()
+    out = {f"r{k}": pyoracle.ref_value_ranges(value_range_volume(d)) for k, d in enumerate(VALUE_RANGE_DIMS)}
+    np.savez_compressed(os.path.join(HERE, "value_ranges.npz"), **out)
+    print(f"wrote value_ranges.npz: {len(VALUE_RANGE_DIMS)} volumes")
+
+
 def host_derivation_inputs():
     """Seeded look-at cameras / frame sizes and volume placements (shared by the generator and the test)."""
     rng = np.random.default_rng(20261105)
@@ -397,6 +414,8 @@ if __name__ == "__main__":
         make_path_ref()
     elif len(sys.argv) > 1 and sys.argv[1] == "march_spp":
         make_march_spp()
+    elif len(sys.argv) > 1 and sys.argv[1] == "ranges":
+        make_value_ranges()
     elif len(sys.argv) > 1 and sys.argv[1] == "host":
         make_host_derivations()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
@@ -413,3 +432,4 @@ if __name__ == "__main__":
         make_path_ref()
         make_host_derivations()
         make_march_spp()
+        make_value_ranges()

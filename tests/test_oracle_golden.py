@@ -295,3 +295,18 @@ def test_oracle_march_with_pixel_jitter_equals_the_reference_shader_code():
         assert cnt["rays"] == w * h * case[4]
         assert np.array_equal(rgba.view(np.uint32), G[f"rgba{k}"].view(np.uint32)), case
         assert np.array_equal(grad.view(np.uint32), G[f"grad{k}"].view(np.uint32)), case
+
+
+def test_macrocell_value_ranges_against_the_reference_kernel():
+    """tests/golden/value_ranges.npz holds the output of the reference's value_range_kernel (accel/sp_singlemc.cu:10-54) run on the
+    host for five volumes (ragged, one-voxel-thin, smaller than a cell). The oracle's MC_REFERENCE mode reproduces it exactly;
+    the footprint the B200 device builds (MC_CONSERVATIVE, bit-exact with the device in the GPU tests) contains it in every
+    cell, so its majorants are never below the reference's."""
+    mg = _make_golden_module()
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "value_ranges.npz"))
+    for k, dims in enumerate(mg.VALUE_RANGE_DIMS):
+        vol = mg.value_range_volume(dims)
+        want = G[f"r{k}"]
+        assert np.array_equal(pyoracle.build_ranges(vol, pyoracle.MC_REFERENCE), want), dims
+        cons = pyoracle.build_ranges(vol, pyoracle.MC_CONSERVATIVE)
+        assert (cons[..., 0] <= want[..., 0]).all() and (cons[..., 1] >= want[..., 1]).all(), dims
