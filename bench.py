@@ -181,29 +181,39 @@ def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
     o = pyoracle.OracleScene(d, skip_empty=False, build_macrocells=(wl["mode"] == "pathtrace"))
     cores = pyoracle.hardware_threads()
 
-    # ray marching with the reference's shading: the REFERENCE's own raymarching() / raymarching_shadow() compiled on the host
-    # (oracle/_ref/libovr_ref_march.so, built where /root/reference exists and shipped with the snapshot) are what is timed;
-    # the oracle port -- pinned bit for bit against them by tests/golden/ref_march.npz -- supplies the sample count of the
-    # same pixels in an untimed pass. Path tracing and unshaded frames have no compiled reference counterpart: port.
+    # Shaded ray marching and path tracing: the REFERENCE's own shader functions compiled on the host
+    # (oracle/_ref/libovr_ref_march.so -- raymarching() / raymarching_shadow() / render_raymarching(), delta_tracking() /
+    # pathtracing() / render_pathtracing() -- built where /root/reference exists and shipped with the snapshot) are what is
+    # timed; the oracle port -- pinned bit for bit against them by tests/golden/ref_march*.npz and ref_path.npz -- supplies the
+    # sample count of the same pixels in an untimed pass. Unshaded frames have no reference counterpart: port.
     W, H = wl["width"], wl["height"]
-    use_ref = (wl["mode"] != "pathtrace" and wl["shading"] == "ref" and not os.environ.get("B200VR_BENCH_CPU_PORT")
+    path = wl["mode"] == "pathtrace"
+    use_ref = ((path or wl["shading"] == "ref") and not os.environ.get("B200VR_BENCH_CPU_PORT")
                and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libovr_ref_march.so")))
-    ref_px, ref_cnt = None, None
+    ref_px = None
     if use_ref:
         ys, xs = np.meshgrid(np.arange(0, H, stride), np.arange(0, W, stride), indexing="ij")
         ref_px = np.stack([xs.ravel(), ys.ravel()], 1).astype(np.int32)
-        _, _, ref_cnt = o.render_march(stride=(stride, stride), threads=cores, frame_index=1)  # untimed: counts only
+
+    def port_frame(fi):
+        if path:
+            return o.render_path(stride=(stride, stride), threads=cores, frame_index=fi)[1]
+        return o.render_march(stride=(stride, stride), threads=cores, frame_index=fi)[2]
 
     def frame(fi):
-        t0 = time.perf_counter()
         if use_ref:
-            o.ref_march(ref_px, threads=cores)
-            cnt = ref_cnt
-        elif wl["mode"] == "pathtrace":
-            _, cnt = o.render_path(stride=(stride, stride), threads=cores, frame_index=fi)
+            cnt = port_frame(fi)  # untimed: counts only (same pixels, same RNG streams)
+            t0 = time.perf_counter()
+            if path:
+                o.ref_path(ref_px, frame_index=fi, threads=cores)
+            else:
+                o.s.frame_index = fi
+                o.ref_march(ref_px, threads=cores)
+            dt = time.perf_counter() - t0
         else:
-            _, _, cnt = o.render_march(stride=(stride, stride), threads=cores, frame_index=fi)
-        dt = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            cnt = port_frame(fi)
+            dt = time.perf_counter() - t0
         return dt, cnt["primary_samples"] + cnt["shadow_samples"] + cnt["delta_samples"], cnt
 
     for k in range(warmup):
@@ -213,7 +223,9 @@ def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
         dt, s, cnt = frame(k + 1)
         tot_t += dt
         tot_s += s
-    what = ("the reference's own raymarching()/raymarching_shadow() (shaders_raymarching.cu:43-171) compiled on the host, texture unit emulated"
+    what = (("the reference's own delta_tracking()/pathtracing() (shaders_pathtracing.cu:269-542) compiled on the host, texture unit emulated"
+             if path else
+             "the reference's own raymarching()/raymarching_shadow() (shaders_raymarching.cu:43-171) compiled on the host, texture unit emulated")
             if use_ref else "CPU port of the reference algorithm without skipping")
     info = {"cores": cores, "kind": "reference" if use_ref else "port",
             "sample": f"every {stride}th pixel in x and y (1/{stride * stride} of the rays) of the {W}x{H} frame, "

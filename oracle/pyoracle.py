@@ -361,7 +361,7 @@ class OracleScene:
             L.ref_march_rays_mt(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out), C.c_int(threads))
         return out[:, :4].copy(), out[:, 4:].copy()
 
-    def ref_path(self, pixels_xy, frame_index=1):
+    def ref_path(self, pixels_xy, frame_index=1, threads=1):
         """The REFERENCE's own delta_tracking() / pathtracing() / render_pathtracing() (oracle/ref_march_shim.cpp, namespace pt) for
         the listed pixels, one frame: rgba [n, 4]; None where oracle/_ref was not built. self.s.pt_child_instance_xfm = 1:
         scattered rays go through the instance transform a second time before they are clipped, as OptiX does; 0: clipped as
@@ -374,7 +374,10 @@ class OracleScene:
         self.s.frame_index = frame_index
         px = np.ascontiguousarray(pixels_xy, np.int32).reshape(-1, 2)
         out = np.zeros((len(px), 4), np.float32)
-        L.ref_path_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        if threads == 1:
+            L.ref_path_rays(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out))
+        else:
+            L.ref_path_rays_mt(C.byref(self.s), _p(px), C.c_int64(len(px)), _fp(out), C.c_int(threads))
         return out
 
     def render_path(self, rect=None, stride=(1, 1), threads=0, frame_index=1):

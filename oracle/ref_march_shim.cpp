@@ -334,7 +334,7 @@ extern "C" void ref_march_rays(const ovr_oracle_scene* s, const int32_t* pixels_
 // The same over `threads` host threads (0: all hardware threads), pixels handed out in chunks of 64 through an atomic counter:
 // the timed CPU arm of bench.py (`--impl reference`, cpu_baseline.kind "reference"). Every worker sets up its own copy of
 // the launch state (thread_local above), so the result is ref_march_rays' pixel for pixel.
-extern "C" void ref_march_rays_mt(const ovr_oracle_scene* s, const int32_t* pixels_xy, int64_t n_pixels, float* out, int threads)
+template<typename Fn> static void run_chunks_mt(int64_t n_pixels, int threads, const Fn& fn)
 {
   if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
   const int64_t chunk = 64;
@@ -343,14 +343,18 @@ extern "C" void ref_march_rays_mt(const ovr_oracle_scene* s, const int32_t* pixe
     for (;;) {
       const int64_t b = next.fetch_add(chunk);
       if (b >= n_pixels) break;
-      const int64_t n = std::min(chunk, n_pixels - b);
-      ref_march_rays(s, pixels_xy + 2 * b, n, out + 7 * b);
+      fn(b, std::min(chunk, n_pixels - b));
     }
   };
   std::vector<std::thread> pool;
   for (int i = 1; i < threads; i++) pool.emplace_back(work);
   work();
   for (auto& t : pool) t.join();
+}
+
+extern "C" void ref_march_rays_mt(const ovr_oracle_scene* s, const int32_t* pixels_xy, int64_t n_pixels, float* out, int threads)
+{
+  run_chunks_mt(n_pixels, threads, [&](int64_t b, int64_t n) { ref_march_rays(s, pixels_xy + 2 * b, n, out + 7 * b); });
 }
 
 // One path-traced frame through the reference's render_pathtracing(): for every listed pixel the loop of
@@ -419,4 +423,11 @@ extern "C" void ref_path_rays(const ovr_oracle_scene* s, const int32_t* pixels_x
     float* o = out + 4 * i;
     o[0] = color.x, o[1] = color.y, o[2] = color.z, o[3] = alpha;
   }
+}
+
+// ref_path_rays over `threads` host threads (0: all), same chunking as ref_march_rays_mt; pixel results do not depend on it
+// (one RandomTEA stream per pixel).
+extern "C" void ref_path_rays_mt(const ovr_oracle_scene* s, const int32_t* pixels_xy, int64_t n_pixels, float* out, int threads)
+{
+  run_chunks_mt(n_pixels, threads, [&](int64_t b, int64_t n) { ref_path_rays(s, pixels_xy + 2 * b, n, out + 4 * b); });
 }

@@ -257,8 +257,9 @@ def test_reference_path_shim_live_equals_the_golden_frames():
         for x in (0, 1):
             o, w, h, fi = mg.path_ref_scene(mg.PATH_REF_CASES[k], x)
             ys, xs = np.mgrid[0:h, 0:w]
-            r = o.ref_path(np.stack([xs.ravel(), ys.ravel()], 1), frame_index=fi).reshape(h, w, 4)
-            assert np.array_equal(r.view(np.uint32), G[f"rgba{k}_x{x}"].view(np.uint32)), (k, x)
+            for threads in (1, 0):  # 0: ref_path_rays_mt on all host threads, the timed CPU arm of bench.py's path-tracing workloads
+                r = o.ref_path(np.stack([xs.ravel(), ys.ravel()], 1), frame_index=fi, threads=threads).reshape(h, w, 4)
+                assert np.array_equal(r.view(np.uint32), G[f"rgba{k}_x{x}"].view(np.uint32)), (k, x, threads)
 
 
 def test_host_derivations_equal_the_reference_statements():
