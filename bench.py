@@ -234,7 +234,8 @@ def cpu_oracle_run(wl, scene, steps, warmup, stride, volume=None):
 
 
 def auto_stride(cores):
-    return 4 if cores >= 32 else 8
+    # 1/16 of the rays where the box has the threads for it (a few seconds of CPU work per sampled frame), else 1/64
+    return 4 if cores >= 16 else 8
 
 
 def run_reference(args):
