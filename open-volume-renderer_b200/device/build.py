@@ -75,7 +75,8 @@ def build(force=False):
         run(CXX + ["-O2", "-shared", "-o", plugin, srcs[0], f"-L{PKG}", "-lb200vr",
                    "-Wl,-rpath,$ORIGIN:$ORIGIN/../../open-volume-renderer_b200", "-L/usr/local/cuda/lib64", "-lcudart"])
     exe = os.path.join(OUT, "renderbatch")
-    if force or not os.path.exists(exe):
+    dump, dump_src = os.path.join(OUT, "scenedump"), os.path.join(ROOT, "oracle", "ref_scene_dump.cpp")
+    if force or not os.path.exists(exe) or not newer(dump, [dump_src]):
         def compile_one(item):
             rel, flags = item
             obj = os.path.join(OUT, rel.replace("/", "_").replace(".cpp", ".o"))
@@ -86,6 +87,12 @@ def build(force=False):
         # -rdynamic: objectFactory also searches the executable itself (Library.cpp:169-191)
         run(["g++", "-rdynamic", "-o", exe] + objs + ["-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread",
                                                        "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
+        # scenedump (test infrastructure): the reference's scene loader behind oracle/ref_scene_dump.cpp, same objects
+        dump_obj = os.path.join(OUT, "ref_scene_dump.o")
+        run(CXX + ["-O1", "-c", dump_src, "-o", dump_obj])
+        run(["g++", "-rdynamic", "-o", dump, dump_obj] + [o for o in objs if "main_batch" not in o] +
+            ["-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread", "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
+        os.remove(dump_obj)
         for o in objs:
             os.remove(o)
     return exe

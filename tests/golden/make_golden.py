@@ -18,6 +18,7 @@ where /root/reference exists):
   host_derivations.npz  device camera and instance matrices from the reference's own host statements (device_impl.cpp)
   ref_march_spp.npz the same with 2-4 samples per pixel (RandomTEA pixel jitter of the raygen program)
   value_ranges.npz  macrocell value ranges from the reference's value_range_kernel run on the host
+  scene_dump.json   synthetic VIDI3D scenes (all value types, endianness, offset, scales) as parsed by the reference's own loader
   ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
 Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
@@ -342,6 +343,62 @@ def make_path_ref():
     np.savez_compressed(os.path.join(HERE, "ref_path.npz"), **out)
 
 
+def scene_dump_cases(tmpdir):
+    """Synthetic VIDI3D configs + payloads written into tmpdir: every value type, big-endian payloads, a file offset, `scales`,
+    an unnormalised mapping range, alpha ends below 0.01. -> [(name, json path)] (shared by the generator and the test)."""
+    import json
+    import ovr_b200
+    from ovr_b200 import scene_io
+    S = ovr_b200.scenes
+    rng = np.random.default_rng(77)
+    cases = []
+    kinds = [("u8", np.uint8, 255), ("i8", np.int8, 127), ("u16", np.uint16, 60000), ("i16", np.int16, 30000), ("u32", np.uint32, 4e9),
+             ("i32", np.int32, 2e9), ("f32", np.float32, 1.0), ("f64", np.float64, 1.0)]
+    for k, (name, dt, top) in enumerate(kinds):
+        dims = (5 + k, 4 + (k % 3), 3 + (k % 2))  # nz, ny, nx
+        vol = (rng.random(dims) * top).astype(dt)
+        cam = S.Camera((1.5 + k, 2.5, -3.0), (0.1, 0.2 * k, 0.3), (0.0, 1.0, 0.0), 30.0 + 5 * k)
+        alpha = rng.random(8 + 3 * k).astype(np.float32)
+        alpha[0], alpha[-1] = (0.005, 0.5) if k % 2 else (0.3, 0.009)
+        cc = [(0.0, (0, 0, 1)), (0.35, (0, 1, 0.25)), (1.0, (1, 0, 0))]
+        path = scene_io.write_vidi3d_scene(os.path.join(tmpdir, f"case_{name}.json"), vol, alpha, cc, cam, sample_distance=0.25 * (k + 1),
+                                           scalar_range=(0.1, 0.9))
+        root = json.load(open(path))
+        ds = root["dataSource"][0]
+        raw = ds["fileName"][0]
+        if k % 3 == 1:   # big-endian payload behind a 12-byte header
+            with open(raw, "wb") as f:
+                f.write(b"x" * 12)
+                f.write(vol.astype(vol.dtype.newbyteorder(">")).tobytes())
+            ds["endian"], ds["offset"] = "BIG_ENDIAN", 12
+        if k % 3 == 2:
+            ds["scales"] = {"x": 1.0, "y": 0.5 + k, "z": 2.25}
+        if k % 4 == 3:
+            root["view"]["volume"]["scalarMappingRangeUnnormalized"] = {"minimum": 3.0 + k, "maximum": 40.5 + k}
+        json.dump(root, open(path, "w"), indent=1)
+        cases.append((name, path))
+    return cases
+
+
+def make_scene_dump():
+    """scene_dump.json: what the reference's own scene loader (create_scene: scene.cpp + serializer_vidi3d.cpp, compiled from
+    /root/reference into build/ovr/scenedump behind oracle/ref_scene_dump.cpp) makes of scene_dump_cases()."""
+    import json
+    import subprocess
+    import tempfile
+    exe = os.path.join(ROOT, "build", "ovr", "scenedump")
+    assert os.path.exists(exe), "build/ovr/scenedump missing: python open-volume-renderer_b200/device/build.py (needs /root/reference)"
+    with tempfile.TemporaryDirectory() as d:
+        cases = scene_dump_cases(d)
+        r = subprocess.run([exe] + [p for _, p in cases], capture_output=True, text=True, check=True)
+        rows = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(rows) == len(cases) and not any("error" in x for x in rows), rows
+    for (name, _), row in zip(cases, rows):
+        row["file"] = name
+    json.dump(rows, open(os.path.join(HERE, "scene_dump.json"), "w"), indent=0)
+    print(f"wrote scene_dump.json: {len(rows)} scenes")
+
+
 VALUE_RANGE_DIMS = [(32, 32, 32), (70, 45, 33), (17, 16, 15), (100, 1, 37), (48, 31, 64)]
 
 
@@ -416,6 +473,8 @@ if __name__ == "__main__":
         make_march_spp()
     elif len(sys.argv) > 1 and sys.argv[1] == "ranges":
         make_value_ranges()
+    elif len(sys.argv) > 1 and sys.argv[1] == "scenes":
+        make_scene_dump()
     elif len(sys.argv) > 1 and sys.argv[1] == "host":
         make_host_derivations()
     elif len(sys.argv) > 1 and sys.argv[1] == "sparse":
@@ -433,3 +492,4 @@ if __name__ == "__main__":
         make_host_derivations()
         make_march_spp()
         make_value_ranges()
+        make_scene_dump()

@@ -311,3 +311,33 @@ def test_macrocell_value_ranges_against_the_reference_kernel():
         assert np.array_equal(pyoracle.build_ranges(vol, pyoracle.MC_REFERENCE), want), dims
         cons = pyoracle.build_ranges(vol, pyoracle.MC_CONSERVATIVE)
         assert (cons[..., 0] <= want[..., 0]).all() and (cons[..., 1] >= want[..., 1]).all(), dims
+
+
+def test_scene_io_reads_what_the_reference_loader_reads(tmp_path):
+    """tests/golden/scene_dump.json = the reference's own scene loader (ovr::scene::create_scene, compiled from /root/reference
+    into build/ovr/scenedump behind oracle/ref_scene_dump.cpp) on eight synthetic VIDI3D scenes: every value type, big-endian
+    payloads behind a file offset, `scales`, normalised and unnormalised mapping ranges, alpha ends below 0.01. scene_io, the
+    Python mirror of that loader, must hand over the same voxels (FNV-1a of the bytes, type, dims, min / max), grid spacing,
+    transfer-function tables and value range, camera and sampling rate."""
+    import json
+    mg = _make_golden_module()
+    rows = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "scene_dump.json")))
+    cases = mg.scene_dump_cases(str(tmp_path))
+    assert [r["file"] for r in rows] == [n for n, _ in cases] and len(rows) == 8
+    f32 = lambda x: np.asarray(x, np.float32)
+    for (name, path), want in zip(cases, rows):
+        sc = ovr_b200.scene_io.read_vidi3d_scene(path)
+        data = sc.volume.data
+        assert [data.shape[2], data.shape[1], data.shape[0]] == want["dims"] and data.dtype.itemsize == want["type_bytes"], name
+        h = 1469598103934665603
+        for b in data.tobytes():
+            h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        assert f"{h:016x}" == want["fnv"], name
+        assert float(data.min()) == want["min"] and float(data.max()) == want["max"], name
+        assert np.array_equal(f32(sc.volume.grid_spacing), f32(want["spacing"])) and np.array_equal(f32(sc.volume.grid_origin), f32(want["origin"])), name
+        assert np.array_equal(f32(sc.tfn.value_range), f32(want["tf_range"])), (name, sc.tfn.value_range, want["tf_range"])
+        assert np.float32(sc.volume_sampling_rate) == np.float32(want["rate"]), name
+        assert np.array_equal(f32(sc.camera.frm), f32(want["eye"])) and np.array_equal(f32(sc.camera.at), f32(want["center"])), name
+        assert np.array_equal(f32(sc.camera.up), f32(want["up"])) and np.float32(sc.camera.fovy) == np.float32(want["fovy"]), name
+        assert np.array_equal(f32(sc.tfn.opacity), f32(want["opacity"])), name
+        assert np.allclose(f32(sc.tfn.color).ravel(), f32(want["color"]), rtol=0, atol=1e-6), name
