@@ -2,6 +2,7 @@
 
   build/ovr/libdevice_b200.so   DeviceB200 : ovr::MainRenderer (device_b200.cpp) compiled against the reference's UNCHANGED
                                 headers, linked to open-volume-renderer_b200/libb200vr.so
+  build/ovr/scenedump           test infrastructure: oracle/ref_scene_dump.cpp linked with the same reference objects (its scene loader)
   build/ovr/renderbatch         the reference's own apps/main_batch.cpp + host sources (renderer.cpp, scene.cpp,
                                 serializer_{vidi3d,diva}.cpp, imageio.cpp, dylink/Library.cpp) compiled where they lie under
                                 /root/reference with OVR_BUILD_OPTIX7 / OVR_BUILD_OSPRAY undefined -- nothing is copied
