@@ -21,7 +21,7 @@ where /root/reference exists):
   scene_dump.json   synthetic VIDI3D scenes (all value types, endianness, offset, scales) as parsed by the reference's own loader
   ref_path.npz      whole frames from the reference's own delta_tracking() / pathtracing() run on the host (both scattered-ray clips)
 
-Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march]
+Usage: python tests/golden/make_golden.py [sparse|tfn|delta|helpers|march|march_spp|path|host|ranges|scenes]
 """
 import base64
 import ctypes as C
