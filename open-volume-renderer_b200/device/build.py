@@ -2,7 +2,7 @@
 
   build/ovr/libdevice_b200.so   DeviceB200 : ovr::MainRenderer (device_b200.cpp) compiled against the reference's UNCHANGED
                                 headers, linked to open-volume-renderer_b200/libb200vr.so
-  build/ovr/scenedump           test infrastructure: oracle/ref_scene_dump.cpp linked with the same reference objects (its scene loader)
+  build/ovr/libovr_host.a       the same reference objects without main_batch.o, for other host tools built from the reference
   build/ovr/renderbatch         the reference's own apps/main_batch.cpp + host sources (renderer.cpp, scene.cpp,
                                 serializer_{vidi3d,diva}.cpp, imageio.cpp, dylink/Library.cpp) compiled where they lie under
                                 /root/reference with OVR_BUILD_OPTIX7 / OVR_BUILD_OSPRAY undefined -- nothing is copied
@@ -76,8 +76,8 @@ def build(force=False):
         run(CXX + ["-O2", "-shared", "-o", plugin, srcs[0], f"-L{PKG}", "-lb200vr",
                    "-Wl,-rpath,$ORIGIN:$ORIGIN/../../open-volume-renderer_b200", "-L/usr/local/cuda/lib64", "-lcudart"])
     exe = os.path.join(OUT, "renderbatch")
-    dump, dump_src = os.path.join(OUT, "scenedump"), os.path.join(ROOT, "oracle", "ref_scene_dump.cpp")
-    if force or not os.path.exists(exe) or not newer(dump, [dump_src]):
+    hostlib = os.path.join(OUT, "libovr_host.a")
+    if force or not os.path.exists(exe) or not os.path.exists(hostlib):
         def compile_one(item):
             rel, flags = item
             obj = os.path.join(OUT, rel.replace("/", "_").replace(".cpp", ".o"))
@@ -88,12 +88,10 @@ def build(force=False):
         # -rdynamic: objectFactory also searches the executable itself (Library.cpp:169-191)
         run(["g++", "-rdynamic", "-o", exe] + objs + ["-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread",
                                                        "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
-        # scenedump (test infrastructure): the reference's scene loader behind oracle/ref_scene_dump.cpp, same objects
-        dump_obj = os.path.join(OUT, "ref_scene_dump.o")
-        run(CXX + ["-O1", "-c", dump_src, "-o", dump_obj])
-        run(["g++", "-rdynamic", "-o", dump, dump_obj] + [o for o in objs if "main_batch" not in o] +
-            ["-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread", "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
-        os.remove(dump_obj)
+        # the reference's host objects without main(): other host tools built from the reference link against them
+        if os.path.exists(hostlib):
+            os.remove(hostlib)
+        run(["ar", "rcs", hostlib] + [o for o in objs if "main_batch" not in o])
         for o in objs:
             os.remove(o)
     return exe

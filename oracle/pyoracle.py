@@ -61,7 +61,27 @@ def build(force=False):
     ref_srcs = ("ref_shim.cpp", "ref_tfn_shim.cpp", "ref_march_shim.cpp", "extract_march.py", "Makefile", "liboracle.so")
     if os.path.isdir("/root/reference/ovr") and (force or any(_stale(os.path.join(_HERE, "_ref", r), ref_srcs) for r in refs)):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+    build_scenedump(force)
     return so
+
+
+def build_scenedump(force=False):
+    """build/ovr/scenedump: oracle/ref_scene_dump.cpp linked with the reference's own host objects (build/ovr/libovr_host.a, made by
+    open-volume-renderer_b200/device/build.py from /root/reference) -- the reference's scene loader as a command-line dump. Skipped
+    where the reference tree or the archive is absent."""
+    root = os.path.dirname(_HERE)
+    ref, hostlib = "/root/reference", os.path.join(root, "build", "ovr", "libovr_host.a")
+    exe, src = os.path.join(root, "build", "ovr", "scenedump"), os.path.join(_HERE, "ref_scene_dump.cpp")
+    if not (os.path.isdir(os.path.join(ref, "ovr")) and os.path.exists(hostlib)):
+        return None
+    if not force and os.path.exists(exe) and os.path.getmtime(exe) >= max(os.path.getmtime(src), os.path.getmtime(hostlib)):
+        return exe
+    inc = [ref, f"{ref}/ovr", f"{ref}/ovr/common", f"{ref}/ovr/common/cuda", f"{ref}/extern", f"{ref}/extern/gdt", f"{ref}/extern/tfn",
+           "/usr/local/cuda/include"]
+    subprocess.run(["g++", "-std=c++17", "-O1", "-w", "-DOVR_BUILD_CUDA_DEVICES", "-rdynamic", "-o", exe, src] + [f"-I{i}" for i in inc] +
+                   ["-Wl,--whole-archive", hostlib, "-Wl,--no-whole-archive", "-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread",
+                    "-Wl,-rpath,/usr/local/cuda/lib64"], check=True, capture_output=True)
+    return exe
 
 
 def lib():

@@ -1,6 +1,6 @@
 // TEST INFRASTRUCTURE ONLY -- prints what the REFERENCE's own scene loader (ovr::scene::create_scene: ovr/scene.cpp,
-// ovr/serializer/serializer_vidi3d.cpp, compiled from /root/reference by open-volume-renderer_b200/device/build.py into
-// build/ovr/scenedump) hands to a device for each scene file on the command line, one JSON object per line:
+// ovr/serializer/serializer_vidi3d.cpp: the reference's host objects in build/ovr/libovr_host.a; linked into
+// build/ovr/scenedump by oracle/pyoracle.py build_scenedump) hands to a device for each scene file on the command line, one JSON object per line:
 // dims, value type, grid origin / spacing, FNV-1a of the voxel bytes, voxel min / max, transfer-function colours, opacities
 // and value range, camera, sampling rate. tests/golden/make_golden.py feeds it synthetic VIDI3D configs; the output
 // (tests/golden/scene_dump.json) pins open-volume-renderer_b200/scene_io.py, the Python mirror of that loader.

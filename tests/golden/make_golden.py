@@ -395,7 +395,7 @@ def make_scene_dump():
     assert len(rows) == len(cases) and not any("error" in x for x in rows), rows
     for (name, _), row in zip(cases, rows):
         row["file"] = name
-    json.dump(rows, open(os.path.join(HERE, "scene_dump.json"), "w"), indent=0)
+    json.dump(rows, open(os.path.join(HERE, "scene_dump.json"), "w"), separators=(",", ":"))
     print(f"wrote scene_dump.json: {len(rows)} scenes")
 
 
