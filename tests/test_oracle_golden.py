@@ -54,7 +54,7 @@ def test_scene_vorts1_fixture():
     assert float(S["sample_distance"]) == 0.25 and len(S["color_controls"]) == 7
 
 
-# ---- texture unit: outputs of the real B200 tex3D captured on the GPU box (tools/tex_calibration.py, tools/tex_probe.py)
+# ---- texture unit: outputs of the real B200 tex3D captured on the GPU box (tests/tools/tex_calibration.py, tests/tools/tex_probe.py)
 HW = np.load(os.path.join(os.path.dirname(__file__), "golden", "tex_b200_hw.npz"))
 
 

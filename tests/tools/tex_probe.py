@@ -1,4 +1,4 @@
-"""GPU experiment runner: reads tools/_probe_job.npz (keys <name>_vol [nz,ny,nx] f32 and <name>_pts [n,3] f32, made
+"""GPU experiment runner: reads tests/tools/_probe_job.npz (keys <name>_vol [nz,ny,nx] f32 and <name>_pts [n,3] f32, made
 locally), samples every job with the hardware texture unit and the software sampler through b200vr_probe and writes
 gpurun_out/probe_result.npz (<name>_tex, <name>_man). Used to fit the oracle's texture-unit model to the real unit."""
 import ctypes as C
@@ -7,12 +7,12 @@ import sys
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import ovr_b200  # noqa: E402
 
 capi, S = ovr_b200.capi, ovr_b200.scenes
-job = np.load(os.path.join(ROOT, "tools", "_probe_job.npz"))
+job = np.load(os.path.join(ROOT, "tests", "tools", "_probe_job.npz"))
 out = {}
 for key in job.files:
     if not key.endswith("_vol"):
