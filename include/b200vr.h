@@ -201,6 +201,13 @@ int b200vr_ipc_export_frame(b200vr_t* h, int buffer /* 0 | 1: rgba, 2 | 3: grad 
 int b200vr_ipc_open(b200vr_t* h, const unsigned char handle[64], void** dev_ptr_out);
 int b200vr_ipc_close(b200vr_t* h, void* dev_ptr);
 int b200vr_current_buffer(b200vr_t* h); /* index of the buffer b200vr_map returns */
+/* Pure host arithmetic of the device set-up, callable without a handle or a GPU (known-answer tests against the reference's own
+ * statements, tests/golden/host_derivations.npz): the device camera b200vr_set_camera_lookat derives
+ * (DeviceOptix7::Impl::commit, device_impl.cpp:128-136; out = position, direction, horizontal, vertical) and the mapping of a
+ * transfer-function range bound given in file units into texture units (integer_normalize(float, ValueType), array.h:92-106,
+ * for the element type the texture has after CreateArray3DScalarOptix7, array.cpp:322-351). */
+int b200vr_host_camera(const float from[3], const float at[3], const float up[3], float fovy, int width, int height, float out[12]);
+float b200vr_host_integer_normalize(float value, int value_type /* B200VR_TYPE_* */);
 /* fused sort-first exchange: render the owned tiles straight into these buffers (W*H float4 and W*H*3 float, normally the
  * display rank's frame opened with b200vr_ipc_open) -- the kernel's own pixel stores are the transfer, there is no pack /
  * gather / unpack step. Both NULL: back to the handle's own double buffer. */

@@ -40,6 +40,8 @@ _FP = C.POINTER(C.c_float)
 _IP = C.POINTER(C.c_int32)
 SYMBOLS = {
     "b200vr_abi_version": (C.c_int, []),
+    "b200vr_host_camera": (C.c_int, [_FP, _FP, _FP, C.c_float, C.c_int, C.c_int, _FP]),
+    "b200vr_host_integer_normalize": (C.c_float, [C.c_float, C.c_int]),
     "b200vr_create": (C.c_int, [C.POINTER(_P), C.c_int]),
     "b200vr_destroy": (None, [_P]),
     "b200vr_last_error": (C.c_char_p, [_P]),

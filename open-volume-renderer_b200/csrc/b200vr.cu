@@ -504,19 +504,36 @@ extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, in
   return B200VR_OK;
 }
 
-static void derive_camera(b200vr_t* h)
+static void derive_camera_values(const float la_from[3], const float la_at[3], const float la_up[3], float fovy, int width, int height,
+                                 f3& pos, f3& dir, f3& hor, f3& ver)
 {
   // device_impl.cpp:125-136; tan(float) is the float overload (tanf) in the reference's host code (tests/golden/host_derivations.npz)
-  const float t = 2.f * std::tan(h->la_fovy * 0.5f * (float)M_PI / 180.f);
-  const float aspect = (float)h->width / (float)h->height;
-  const f3 from = mk3(h->la_from[0], h->la_from[1], h->la_from[2]), at = mk3(h->la_at[0], h->la_at[1], h->la_at[2]);
-  const f3 up = mk3(h->la_up[0], h->la_up[1], h->la_up[2]);
-  h->cam_pos = from;
-  h->cam_dir = normalize3(at - from);
-  h->cam_hor = (t * aspect) * normalize3(cross3(h->cam_dir, up));
-  h->cam_ver = cross3(h->cam_hor, h->cam_dir) / aspect;
+  const float t = 2.f * std::tan(fovy * 0.5f * (float)M_PI / 180.f);
+  const float aspect = (float)width / (float)height;
+  const f3 from = mk3(la_from[0], la_from[1], la_from[2]), at = mk3(la_at[0], la_at[1], la_at[2]);
+  const f3 up = mk3(la_up[0], la_up[1], la_up[2]);
+  pos = from;
+  dir = normalize3(at - from);
+  hor = (t * aspect) * normalize3(cross3(dir, up));
+  ver = cross3(hor, dir) / aspect;
+}
+
+static void derive_camera(b200vr_t* h)
+{
+  derive_camera_values(h->la_from, h->la_at, h->la_up, h->la_fovy, h->width, h->height, h->cam_pos, h->cam_dir, h->cam_hor, h->cam_ver);
   h->has_camera = true;
 }
+
+extern "C" int b200vr_host_camera(const float from[3], const float at[3], const float up[3], float fovy, int width, int height, float out[12])
+{
+  if (!from || !at || !up || !out || width <= 0 || height <= 0) return B200VR_EINVAL;
+  f3 v[4];
+  derive_camera_values(from, at, up, fovy, width, height, v[0], v[1], v[2], v[3]);
+  for (int i = 0; i < 4; i++) out[3 * i] = v[i].x, out[3 * i + 1] = v[i].y, out[3 * i + 2] = v[i].z;
+  return B200VR_OK;
+}
+
+extern "C" float b200vr_host_integer_normalize(float value, int value_type) { return integer_normalize(value, value_type); }
 
 extern "C" int b200vr_set_camera(b200vr_t* h, const float position[3], const float direction[3], const float horizontal[3],
                                  const float vertical[3])

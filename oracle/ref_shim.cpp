@@ -260,3 +260,20 @@ extern "C" void ref_value_ranges(const float* voxels, const int32_t dims[3], flo
       }
   for (size_t i = 0; i < out.size(); i++) ranges[2 * i] = out[i].lower, ranges[2 * i + 1] = out[i].upper;
 }
+
+// ---- integer_normalize (ovr/devices/optix7/array.h:64-106): how a transfer-function range bound in file units is carried into
+// texture units for each element type; templates and the switch cut out at build time, ValueType from ovr/scene.h ----
+#include <scene.h>
+#include <stdexcept>
+#include <type_traits>
+namespace ref_norm {
+using namespace ovr;
+#include <integer_normalize_extract.h>
+}
+// type: 0..7 = UINT8, INT8, UINT16, INT16, UINT32, INT32, FLOAT, DOUBLE (the order of B200VR_TYPE_*)
+extern "C" float ref_integer_normalize(float value, int type)
+{
+  static const ovr::ValueType map[8] = { ovr::VALUE_TYPE_UINT8, ovr::VALUE_TYPE_INT8, ovr::VALUE_TYPE_UINT16, ovr::VALUE_TYPE_INT16,
+                                         ovr::VALUE_TYPE_UINT32, ovr::VALUE_TYPE_INT32, ovr::VALUE_TYPE_FLOAT, ovr::VALUE_TYPE_DOUBLE };
+  return ref_norm::integer_normalize(value, map[type]);
+}

@@ -433,13 +433,36 @@ def host_derivation_inputs():
     return cams, vols
 
 
+# value type of the texture the reference creates for each scene value type (CreateArray3DScalarOptix7, array.cpp:322-351):
+# 16-bit and double arrays are converted to float; indices follow B200VR_TYPE_* (u8 i8 u16 i16 u32 i32 f32 f64)
+TEXTURE_TYPE = {0: 0, 1: 1, 2: 6, 3: 6, 4: 4, 5: 5, 6: 6, 7: 6}
+
+
+def integer_normalize_inputs():
+    rng = np.random.default_rng(9)
+    rows = []
+    for t in range(8):
+        top = {0: 255, 1: 127, 2: 65535, 3: 32767, 4: 4294967295, 5: 2147483647, 6: 1.0, 7: 1.0}[t]
+        lo = {1: -128, 3: -32768, 5: -2147483648}.get(t, 0)
+        vals = np.concatenate([rng.uniform(lo, top, 200), [lo, top, 0, 1, top / 2]]).astype(np.float32)
+        if t in (4, 5):  # stay inside the integer range: the cast of a larger float is undefined
+            vals = np.clip(vals, lo, np.float32(top) - 256).astype(np.float32)
+        rows += [(t, v) for v in vals]
+    return rows
+
+
 def make_host_derivations():
     """host_derivations.npz: the device camera of DeviceOptix7::Impl::commit (device_impl.cpp:128-136) and the instance matrix of
     buildScene (:288-296) with its gdt inverse, computed by the reference's own statements (cut out at build time, ref_shim.cpp)."""
     pyoracle.build()
     cams, vols = host_derivation_inputs()
+    import ctypes as C
+    L = pyoracle.ref_kat_lib()
+    L.ref_integer_normalize.restype = C.c_float
     out = {"camera": np.array([pyoracle.ref_camera(*c) for c in cams]),
-           "matrix": np.array([pyoracle.ref_volume_matrix(*v) for v in vols])}
+           "matrix": np.array([pyoracle.ref_volume_matrix(*v) for v in vols]),
+           # integer_normalize(float, ValueType) (array.h:64-106) for the texture's element type
+           "norm": np.array([L.ref_integer_normalize(C.c_float(v), TEXTURE_TYPE[t]) for t, v in integer_normalize_inputs()], np.float32)}
     np.savez_compressed(os.path.join(HERE, "host_derivations.npz"), **out)
     print(f"wrote host_derivations.npz: {len(cams)} cameras, {len(vols)} volume placements")
 
