@@ -1,6 +1,7 @@
-"""GPU parity of b200vr_params::pt_child_instance_xfm, through the C ABI. Runs last (file name): the switch was
-added after the round's last GPU session, its oracle side is pinned bit for bit against the reference's own path-tracing code
-(tests/test_oracle_golden.py, tests/golden/ref_path.npz)."""
+"""GPU parity of b200vr_params::pt_child_instance_xfm, through the C ABI: the scattered-ray clip of the path
+tracer, the reference's behaviour under OptiX (default) and the clip against the volume. The oracle side of both settings is
+pinned bit for bit against the reference's own path-tracing code (tests/test_oracle_golden.py, tests/golden/ref_path.npz);
+B200 output of this file: profiles/r1g_q14_tests_gpu.txt."""
 import ctypes as C
 
 import numpy as np
