@@ -66,6 +66,9 @@ SYMBOLS = {
     "b200vr_set_clip_box": (C.c_int, [_P, _FP, _FP]),
     "b200vr_set_tile_partition": (C.c_int, [_P, C.c_int, C.c_int]),
     "b200vr_render": (C.c_int, [_P, C.POINTER(Stats)]),
+    "b200vr_render_async": (C.c_int, [_P]),
+    "b200vr_wait": (C.c_int, [_P, C.POINTER(Stats)]),
+    "b200vr_set_option": (C.c_int, [_P, C.c_char_p, C.c_char_p]),
     "b200vr_map": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P)]),
     "b200vr_swap": (C.c_int, [_P]),
     "b200vr_download": (C.c_int, [_P, _P, _P]),

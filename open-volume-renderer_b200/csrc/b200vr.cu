@@ -9,21 +9,48 @@
 #include "raymarch.cuh"
 #include "march_sm.cuh"
 #include "march_q.cuh"
+#include "march_qb.cuh"
 #include "march_ring.cuh"
 #include "march_ns.cuh"
 #include "sparse.cuh"
 
+#include <cub/device/device_radix_sort.cuh>
+
+#include <cctype>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 using namespace b200k;
 
 namespace {
 thread_local std::string g_create_error;
+
+// Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
+// what is computed per sample; they choose between kernels / launch orders that render the same frame.
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_RING, KERNEL_LEGACY, KERNEL_SM };
+enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
+       TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
+struct Tuning {
+  int kernel = KERNEL_AUTO;
+  int tile_order = TILE_ORDER_AUTO;
+  int sheet_px = 8;         // width of a sheet strip in pixels (TILE_ORDER_SHEET)
+  int max_ctas_per_sm = 0;  // 0: as many as fit
+  int ring_high = 4;        // blocks kept ready per CTA for warps that have run out of tiles (march_ring.cuh)
+  int occ_smem = -1;        // macrocell occupancy mask in shared memory: -1 when it fits (march_q.cuh Q_OCC_SMEM_WORDS), 0 never
+  int carveout = -1;        // cudaFuncAttributePreferredSharedMemoryCarveout in percent; -1: just what the launch needs
+  int tex_native8 = 1;      // 8-bit volumes stay 8-bit 3-D arrays
+  int debug_tiles = 0;
+};
+
+struct LaunchConfig {
+  int per_sm = 0; // resident CTAs per SM (occupancy API), cached per (kernel, threads, shared bytes, carve-out)
+};
 }
 
 struct b200vr {
@@ -105,6 +132,23 @@ struct b200vr {
   unsigned int* sp_count = nullptr;
   int sp_alloc_px = 0;             // pixels sp_xy was allocated for
   int sp_last_count = -1;          // entries of sp_xy after the last sparse render (-1: none yet)
+  // tuning + cached launch configurations
+  Tuning tune;
+  std::map<std::tuple<const void*, int, size_t, int>, LaunchConfig> launch_cache;
+  // sheet order of the warp tiles (build.cuh sheet_key_kernel): keys / values before and after the sort, sort scratch
+  unsigned int* wt_keys[2] = { nullptr, nullptr };
+  unsigned int* wt_vals[2] = { nullptr, nullptr };
+  void* wt_tmp = nullptr;
+  size_t wt_tmp_bytes = 0;
+  int wt_alloc = 0;                // entries allocated
+  int wt_count = 0;                // entries of the valid table (0: none)
+  f3 wt_dir, wt_hor, wt_ver, wt_light; // camera / light the valid table was built for
+  int wt_rank = -1, wt_nranks = -1, wt_w = 0, wt_h = 0, wt_px = 0;
+  // last frame (b200vr_render_async -> b200vr_wait)
+  int last_launches = 0, last_grid = 0, last_warps_per_cta = 1;
+  int order_mode_done = -1;        // super-tile order mode h->tile_order currently holds
+  bool last_ring = false;
+  bool pending = false;            // a frame was enqueued and its counters have not been fetched
 };
 
 #define CK(call)                                                                                   \
@@ -127,6 +171,68 @@ static int grid_for(size_t n, int threads, int sm_count)
   const size_t want = (n + threads - 1) / threads;
   const size_t cap = (size_t)sm_count * 16;
   return (int)std::max<size_t>(1, std::min(want, cap));
+}
+
+// ---- tuning options -------------------------------------------------------------------------------------------------
+static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "occ_smem", "carveout",
+                                            "tex_native8", "debug_tiles" };
+
+static int apply_option(b200vr_t* h, const std::string& name, const char* value)
+{
+  Tuning& t = h->tune;
+  if (name == "kernel") {
+    static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
+                                                         { "qb8", KERNEL_QB8 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+    for (const auto& n : names)
+      if (std::strcmp(value, n.first) == 0) {
+        t.kernel = n.second;
+        return B200VR_OK;
+      }
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, ring, legacy, sm");
+  }
+  char* end = nullptr;
+  const long v = std::strtol(value, &end, 10);
+  if (end == value || *end != 0) return fail(h, B200VR_EINVAL, "set_option: value is not an integer");
+  if (name == "tile_order") {
+    if (v < TILE_ORDER_AUTO || v > TILE_ORDER_SHEET) return fail(h, B200VR_EINVAL, "set_option: tile_order is -1 (auto) or 0..7");
+    t.tile_order = (int)v;
+    h->wt_count = 0;
+  }
+  else if (name == "sheet_px") {
+    if (v < 1 || v > 4096) return fail(h, B200VR_EINVAL, "set_option: sheet_px out of range");
+    t.sheet_px = (int)v;
+    h->wt_count = 0;
+  }
+  else if (name == "max_ctas_per_sm") t.max_ctas_per_sm = (int)std::max(0l, v);
+  else if (name == "ring_high") t.ring_high = (int)std::max(1l, v);
+  else if (name == "occ_smem") t.occ_smem = v == 0 ? 0 : -1;
+  else if (name == "carveout") {
+    if (v < -1 || v > 100) return fail(h, B200VR_EINVAL, "set_option: carveout is -1 or a percentage");
+    t.carveout = (int)v;
+  }
+  else if (name == "tex_native8") t.tex_native8 = v != 0;
+  else if (name == "debug_tiles") t.debug_tiles = v != 0;
+  else return fail(h, B200VR_EINVAL, "set_option: unknown option");
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_set_option(b200vr_t* h, const char* name, const char* value)
+{
+  if (!h) return B200VR_EINVAL;
+  if (!name || !value) return fail(h, B200VR_EINVAL, "set_option: NULL argument");
+  return apply_option(h, name, value);
+}
+
+// defaults of a new handle: B200VR_<OPTION> in the environment (A/B runs without touching the caller)
+static void options_from_env(b200vr_t* h)
+{
+  for (const char* name : kOptionNames) {
+    std::string env = "B200VR_";
+    for (const char* c = name; *c; c++) env += (char)std::toupper((unsigned char)*c);
+    if (const char* v = std::getenv(env.c_str()))
+      if (apply_option(h, name, v) != B200VR_OK) std::fprintf(stderr, "[b200vr] ignoring %s=%s: %s\n", env.c_str(), v, h->error.c_str());
+  }
+  h->error.clear();
 }
 
 extern "C" int b200vr_abi_version(void) { return B200VR_ABI_VERSION; }
@@ -170,6 +276,7 @@ extern "C" int b200vr_create(b200vr_t** out, int cuda_device)
   b200vr_t* h = new b200vr();
   h->device = cuda_device;
   b200vr_default_params(&h->prm);
+  options_from_env(h);
   auto bail = [&](cudaError_t err, const char* what) {
     g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
     delete h;
@@ -245,6 +352,8 @@ extern "C" void b200vr_destroy(b200vr_t* h)
   cudaFree(h->minmax);
   cudaFree(h->sp_noise);
   cudaFree(h->sp_count);
+  for (int i = 0; i < 2; i++) cudaFree(h->wt_keys[i]), cudaFree(h->wt_vals[i]);
+  cudaFree(h->wt_tmp);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -262,11 +371,10 @@ static int rebuild_majorants(b200vr_t* h);
 // native8: device copy of the original 8-bit voxels (or nullptr). The reference keeps 8-bit volumes as 8-bit 3-D arrays read
 // through cudaReadModeNormalizedFloat (array.cpp:300-306); so does this device: a 32-byte sector of the texture then holds four
 // times as many texels, which is what the L1TEX tag stage (4 sectors/clk/SM, the limiter of the march kernels, DESIGN.md
-// section 5) and HBM see. B200VR_TEX_NATIVE8=0 forces the fp32 array (A/B runs). The fp32 copy `lin` is kept either way.
+// section 5) and HBM see. Option tex_native8 = 0 forces the fp32 array (A/B runs). The fp32 copy `lin` is kept either way.
 static int finish_volume(b200vr_t* h, const float obj_to_world[12], const void* native8 = nullptr, bool native8_signed = false)
 {
-  if (const char* e = std::getenv("B200VR_TEX_NATIVE8"))
-    if (std::atoi(e) == 0) native8 = nullptr;
+  if (!h->tune.tex_native8) native8 = nullptr;
   const cudaChannelFormatDesc desc = !native8 ? cudaCreateChannelDesc<float>()
                                      : native8_signed ? cudaCreateChannelDesc<signed char>() : cudaCreateChannelDesc<unsigned char>();
   const cudaExtent ext = make_cudaExtent((size_t)h->nx, (size_t)h->ny, (size_t)h->nz);
@@ -337,14 +445,22 @@ static int upload_typed(b200vr_t* h, const void* voxels, size_t n, int on_device
 {
   const T* src = (const T*)voxels;
   T* staged = nullptr;
+  cudaError_t e = cudaSuccess;
   if (!on_device) {
-    CK(cudaMalloc(&staged, n * sizeof(T)));
-    CK(cudaMemcpyAsync(staged, voxels, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    e = cudaMalloc(&staged, n * sizeof(T));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(staged, voxels, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
     src = staged;
   }
-  convert_kernel<T><<<grid_for(n, 256, h->sm_count), 256, 0, h->stream>>>(h->lin, src, n);
-  CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(h->stream));
+  if (e == cudaSuccess) {
+    convert_kernel<T><<<grid_for(n, 256, h->sm_count), 256, 0, h->stream>>>(h->lin, src, n);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) {
+    cudaFree(staged);
+    h->error = std::string("upload_typed: ") + cudaGetErrorString(e);
+    return B200VR_ECUDA;
+  }
   if (keep) {
     *keep = src;
     *owned = staged != nullptr;
@@ -455,8 +571,9 @@ static int rebuild_majorants(b200vr_t* h)
   const int n_cells = h->mc.x * h->mc.y * h->mc.z;
   const int threads = 256;
   const int grid = std::max(1, std::min((n_cells + threads - 1) / threads, h->sm_count * 8));
-  majorant_kernel<<<grid, threads, (size_t)h->n_alpha * sizeof(float), h->stream>>>(h->ranges, n_cells, h->tf_alpha, h->n_alpha,
-                                                                                     h->tf_lower, h->tf_upper, h->majorants);
+  const size_t maj_smem = (size_t)h->n_alpha * sizeof(float);
+  if (maj_smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)majorant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)maj_smem));
+  majorant_kernel<<<grid, threads, maj_smem, h->stream>>>(h->ranges, n_cells, h->tf_alpha, h->n_alpha, h->tf_lower, h->tf_upper, h->majorants);
   CK(cudaGetLastError());
   const int n_pad = (h->mc.x + 2) * (h->mc.y + 2) * (h->mc.z + 2);
   majorant_pad_kernel<<<std::max(1, std::min((n_pad + threads - 1) / threads, h->sm_count * 8)), threads, 0, h->stream>>>(
@@ -473,7 +590,10 @@ extern "C" int b200vr_set_transfer_function(b200vr_t* h, const float* colors, in
 {
   if (!h) return B200VR_EINVAL;
   if (!colors || !alphas || n_colors <= 0 || n_alphas <= 0) return fail(h, B200VR_EINVAL, "set_transfer_function: empty table");
-  if (tf_shared_bytes(n_colors, n_alphas) > 200 * 1024) return fail(h, B200VR_EINVAL, "set_transfer_function: table exceeds shared memory");
+  // every march kernel stages the opacity table in shared memory (8 B per entry as value / slope pairs next to 16-72 KB of task
+  // queues, or 4 B + 16 B per colour entry in the older kernels): refuse here what no kernel could launch with
+  if (q_alpha_bytes(n_alphas) + qb_queue_bytes<8>() > 200 * 1024 || tf_fast_shared_bytes(n_colors, n_alphas) > 200 * 1024)
+    return fail(h, B200VR_EINVAL, "set_transfer_function: table too large for shared memory (at most ~16000 opacity / ~8000 colour entries)");
   CK(cudaSetDevice(h->device));
   // volume.cpp:104-121: colours -> float4(r,g,b,1); alphas = every second float of the (position, alpha) pairs
   std::vector<float4> c((size_t)n_colors);
@@ -579,6 +699,8 @@ extern "C" int b200vr_set_params(b200vr_t* h, const b200vr_params* p)
   if (p->mode != B200VR_MODE_RAYMARCH && p->mode != B200VR_MODE_PATHTRACE) return fail(h, B200VR_EINVAL, "set_params: bad mode");
   if (p->shading != B200VR_SHADING_NONE && p->shading != B200VR_SHADING_REF) return fail(h, B200VR_EINVAL, "set_params: bad shading");
   if (p->sampler != B200VR_SAMPLER_TEX3D && p->sampler != B200VR_SAMPLER_MANUAL) return fail(h, B200VR_EINVAL, "set_params: bad sampler");
+  // the path tracer keeps one albedo per bounce (scatter_index advances by 2 per bounce) in a stack of PT_MAX_STACK
+  if (p->max_num_scatters > 2 * PT_MAX_STACK) return fail(h, B200VR_EINVAL, "set_params: max_num_scatters above 32 is not supported");
   const float base = p->base > 0.f ? p->base : h->prm.base; // set_sampling_rate(r, b): b <= 0 keeps base (volume.cpp:156-162)
   h->prm = *p;
   h->prm.base = base;
@@ -619,6 +741,8 @@ extern "C" int b200vr_resize(b200vr_t* h, int width, int height)
     for (int i = 0; i < 2; i++) CK(cudaMalloc(&h->tile_cost[i], (size_t)h->tile_slots * sizeof(unsigned int)));
     CK(cudaMalloc(&h->tile_order, (size_t)h->tile_slots * sizeof(int)));
     h->cost_valid = false;
+    h->order_mode_done = -1;
+    h->wt_count = 0;
     cudaFree(h->acc);
     cudaFree(h->ray_alpha);
     CK(cudaMalloc(&h->acc, n * 3 * sizeof(unsigned long long)));
@@ -672,7 +796,7 @@ extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
 {
   if (!h) return B200VR_EINVAL;
   if (nranks < 1 || rank < 0 || rank >= nranks) return fail(h, B200VR_EINVAL, "set_tile_partition: bad rank");
-  if (rank != h->rank || nranks != h->nranks) h->cost_valid = false; // slots mean other super tiles now
+  if (rank != h->rank || nranks != h->nranks) h->cost_valid = false, h->order_mode_done = -1, h->wt_count = 0; // slots mean other super tiles now
   h->rank = rank;
   h->nranks = nranks;
   h->reset = true;
@@ -685,72 +809,97 @@ extern "C" int b200vr_set_tile_partition(b200vr_t* h, int rank, int nranks)
 
 typedef void (*render_kernel_t)(const LaunchParams);
 
-// Which kernel renders a frame. Texture sampler: deferred-shading queue kernel (march_q.cuh) for the reference's
-// gradient + shadow shading, the lean single-loop kernel (march_sm.cuh) without shading. Software sampler: the first
-// generation nested-loop kernel (raymarch.cuh). B200VR_KERNEL=legacy|sm forces the older ones for A/B runs.
+// Which kernel renders a frame. Texture sampler: deferred-shading queue kernels (march_q.cuh one task per lane and pass,
+// march_qb.cuh J tasks per lane and pass, march_ring.cuh with work sharing between warps) for the reference's gradient + shadow
+// shading, the lean kernel (march_ns.cuh) without shading. Software sampler: the first-generation nested-loop kernel
+// (raymarch.cuh). Option kernel = legacy | sm forces the older ones for A/B runs.
 struct KernelChoice {
   render_kernel_t fn;
   int threads;
   size_t smem;
   bool ring = false; // march_ring.cuh: needs the task ring, one launch per sample + resolve_kernel
+  const char* name = "";
 };
+
+// the six instantiations of a march kernel template: no skipping | skipping with the occupancy mask in shared / global memory,
+// each with the power-of-two transfer-function fast path or the generic one
+#define B200VR_PICK(KERNEL, skip, pow2, occs)                                                                                     \
+  (!(skip) ? ((pow2) ? KERNEL(false, true, false) : KERNEL(false, false, false))                                                  \
+   : (occs) ? ((pow2) ? KERNEL(true, true, true) : KERNEL(true, false, true))                                                     \
+            : ((pow2) ? KERNEL(true, true, false) : KERNEL(true, false, false)))
+#define B200VR_K_Q(a, b, c) raymarch_q_kernel<a, b, c>
+#define B200VR_K_QB2(a, b, c) raymarch_qb_kernel<a, b, c, 2>
+#define B200VR_K_QB4(a, b, c) raymarch_qb_kernel<a, b, c, 4>
+#define B200VR_K_QB8(a, b, c) raymarch_qb_kernel<a, b, c, 8>
+#define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
+#define B200VR_K_NS(a, b, c) raymarch_ns_kernel<a, b, c>
 
 static KernelChoice pick_kernel(const b200vr_t* h)
 {
   const b200vr_params& p = h->prm;
-  const char* force = std::getenv("B200VR_KERNEL");
-  const bool legacy = force && std::strcmp(force, "legacy") == 0, sm = force && std::strcmp(force, "sm") == 0;
-  // Per-warp queue kernel (march_q.cuh) or queue + work-sharing rings (march_ring.cuh). Measured on C2: the whole frame on
-  // one GPU 2.29 vs 2.65 ms (the rings cost ~8 % more instructions), an eighth of its tiles 1.06-1.50 vs 0.80-1.13 ms (the
-  // heaviest warp tile alone takes ~1 ms with the queue kernel): rings when the frame is split sort-first, queue otherwise.
+  const int force = h->tune.kernel;
+  const bool legacy = force == KERNEL_LEGACY, sm = force == KERNEL_SM;
+  // Per-warp queue kernels or queue + work-sharing rings (march_ring.cuh). Measured on C2: the whole frame on one GPU 2.29 vs
+  // 2.65 ms (the rings cost ~8 % more instructions), an eighth of its tiles 1.06-1.50 vs 0.80-1.13 ms (the heaviest warp tile
+  // alone takes ~1 ms with the queue kernel): rings when the frame is split sort-first, queue otherwise.
   // Sparse (foveated) frames keep the heavy tiles around the focus and drop most of the light ones: the launch is as long as
   // its heaviest warp tile with the queue kernel (C2-sparse 1.59 ms for a quarter of the samples), so they take the rings too.
   // Not while accumulating: resolve_kernel rewrites every pixel, the reference leaves unsampled pixels untouched then.
   const bool sparse_ring = h->sparse && !p.accumulate;
-  const bool q = force ? std::strcmp(force, "q") == 0 : (h->nranks == 1 && !sparse_ring);
+  const bool ring = force == KERNEL_RING || (force == KERNEL_AUTO && (h->nranks != 1 || sparse_ring));
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
   if (p.mode == B200VR_MODE_PATHTRACE) {
     k.fn = p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
+    k.name = "pathtrace_kernel";
     return k;
   }
   if (p.sampler == B200VR_SAMPLER_TEX3D && !legacy) {
+    const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
+    const bool occs = p.skip_empty && h->tune.occ_smem != 0 && q_occ_in_smem(h->occ_words);
+    const bool skip = p.skip_empty != 0;
     if (p.shading == B200VR_SHADING_REF && !sm) {
-      const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
-      const bool occs = p.skip_empty && q_occ_in_smem(h->occ_words);
-      if (q) {
-        if (!p.skip_empty) k.fn = pow2 ? raymarch_q_kernel<false, true, false> : raymarch_q_kernel<false, false, false>;
-        else if (occs) k.fn = pow2 ? raymarch_q_kernel<true, true, true> : raymarch_q_kernel<true, false, true>;
-        else k.fn = pow2 ? raymarch_q_kernel<true, true, false> : raymarch_q_kernel<true, false, false>;
+      const size_t tables = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0);
+      if (ring) {
+        k.fn = B200VR_PICK(B200VR_K_RING, skip, pow2, occs);
+        k.ring = true;
+        k.threads = Q_THREADS, k.smem = tables + q_queue_bytes(), k.name = "raymarch_ring_kernel";
+      }
+      else if (force == KERNEL_QB2) {
+        k.fn = B200VR_PICK(B200VR_K_QB2, skip, pow2, occs);
+        k.threads = QB_THREADS, k.smem = tables + qb_queue_bytes<2>(), k.name = "raymarch_qb_kernel";
+      }
+      else if (force == KERNEL_QB4) {
+        k.fn = B200VR_PICK(B200VR_K_QB4, skip, pow2, occs);
+        k.threads = QB_THREADS, k.smem = tables + qb_queue_bytes<4>(), k.name = "raymarch_qb_kernel";
+      }
+      else if (force == KERNEL_QB8) {
+        k.fn = B200VR_PICK(B200VR_K_QB8, skip, pow2, occs);
+        k.threads = QB_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qb_kernel";
       }
       else {
-        if (!p.skip_empty) k.fn = pow2 ? raymarch_ring_kernel<false, true, false> : raymarch_ring_kernel<false, false, false>;
-        else if (occs) k.fn = pow2 ? raymarch_ring_kernel<true, true, true> : raymarch_ring_kernel<true, false, true>;
-        else k.fn = pow2 ? raymarch_ring_kernel<true, true, false> : raymarch_ring_kernel<true, false, false>;
-        k.ring = true;
+        k.fn = B200VR_PICK(B200VR_K_Q, skip, pow2, occs);
+        k.threads = Q_THREADS, k.smem = tables + q_queue_bytes(), k.name = "raymarch_q_kernel";
       }
-      k.threads = Q_THREADS;
-      k.smem = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0) + q_queue_bytes();
       return k;
     }
     if (p.shading == B200VR_SHADING_NONE && !sm) { // lean classification + compositing kernel (march_ns.cuh)
-      const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
-      const bool occs = p.skip_empty && q_occ_in_smem(h->occ_words);
-      if (!p.skip_empty) k.fn = pow2 ? raymarch_ns_kernel<false, true, false> : raymarch_ns_kernel<false, false, false>;
-      else if (occs) k.fn = pow2 ? raymarch_ns_kernel<true, true, true> : raymarch_ns_kernel<true, false, true>;
-      else k.fn = pow2 ? raymarch_ns_kernel<true, true, false> : raymarch_ns_kernel<true, false, false>;
+      k.fn = B200VR_PICK(B200VR_K_NS, skip, pow2, occs);
       k.threads = NS_THREADS;
       k.smem = ns_shared_bytes(h->n_color, h->n_alpha, occs ? h->occ_words : 0);
+      k.name = "raymarch_ns_kernel";
       return k;
     }
     k.smem = tf_fast_shared_bytes(h->n_color, h->n_alpha);
+    k.name = "raymarch_sm_kernel";
     if (p.shading == B200VR_SHADING_REF)
       k.fn = p.skip_empty ? raymarch_sm_kernel<SHADING_REF, true> : raymarch_sm_kernel<SHADING_REF, false>;
     else
       k.fn = p.skip_empty ? raymarch_sm_kernel<SHADING_NONE, true> : raymarch_sm_kernel<SHADING_NONE, false>;
     return k;
   }
+  k.name = "raymarch_kernel";
   const int key = (p.shading == B200VR_SHADING_REF ? 4 : 0) | (p.sampler == B200VR_SAMPLER_MANUAL ? 2 : 0) | (p.skip_empty ? 1 : 0);
   switch (key) {
   case 0: k.fn = raymarch_kernel<SHADING_NONE, SAMPLER_TEX3D, false>; break;
@@ -972,42 +1121,153 @@ extern "C" int64_t b200vr_get_sparse_samples(b200vr_t* h, int32_t* xy_out, int64
   return h->sp_last_count;
 }
 
-extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
+// Sheet order of the owned warp tiles (build.cuh sheet_key_kernel): key per tile on the device, one radix sort, the sorted tile
+// origins become P.wt_order. The table is kept while camera basis, light, image size and partition stay (nearly) the same:
+// the order is a locality heuristic, any permutation renders the same frame.
+static int build_sheet_order(b200vr_t* h, LaunchParams& P, int& launches)
 {
-  if (!h) return B200VR_EINVAL;
+  const int n = P.n_warp_tiles;
+  if (n <= 0) return B200VR_OK;
+  const f3 L = P.light_dir;
+  auto close3 = [](f3 a, f3 b, float tol) { return std::fabs(a.x - b.x) <= tol && std::fabs(a.y - b.y) <= tol && std::fabs(a.z - b.z) <= tol; };
+  const float tol = 1e-3f * std::sqrt(dot3(h->cam_hor, h->cam_hor));
+  if (h->wt_count == n && h->wt_rank == h->rank && h->wt_nranks == h->nranks && h->wt_w == h->width && h->wt_h == h->height &&
+      h->wt_px == h->tune.sheet_px && close3(h->wt_dir, h->cam_dir, 1e-3f) && close3(h->wt_hor, h->cam_hor, tol) &&
+      close3(h->wt_ver, h->cam_ver, tol) && close3(h->wt_light, L, 1e-4f)) {
+    P.wt_order = h->wt_vals[1];
+    return B200VR_OK;
+  }
+  if (h->wt_alloc < n) {
+    CK(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < 2; i++) {
+      cudaFree(h->wt_keys[i]);
+      cudaFree(h->wt_vals[i]);
+      h->wt_keys[i] = h->wt_vals[i] = nullptr;
+    }
+    cudaFree(h->wt_tmp);
+    h->wt_tmp = nullptr, h->wt_alloc = 0, h->wt_count = 0;
+    for (int i = 0; i < 2; i++) {
+      CK(cudaMalloc(&h->wt_keys[i], (size_t)n * sizeof(unsigned int)));
+      CK(cudaMalloc(&h->wt_vals[i], (size_t)n * sizeof(unsigned int)));
+    }
+    size_t bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, h->wt_keys[0], h->wt_keys[1], h->wt_vals[0], h->wt_vals[1], n, 0, 32, h->stream));
+    CK(cudaMalloc(&h->wt_tmp, std::max<size_t>(bytes, 16)));
+    h->wt_tmp_bytes = bytes;
+    h->wt_alloc = n;
+  }
+  SheetParams S;
+  S.cam_dir = h->cam_dir, S.cam_hor = h->cam_hor, S.cam_ver = h->cam_ver;
+  S.light = L;
+  // basis of the plane perpendicular to the light: e1 = the view direction's component in it (phi = 0 at the image centre)
+  f3 e1 = h->cam_dir - dot3(h->cam_dir, L) * L;
+  if (dot3(e1, e1) < 1e-6f * dot3(h->cam_dir, h->cam_dir)) e1 = h->cam_hor - dot3(h->cam_hor, L) * L; // looking along the light
+  e1 = normalize3(e1);
+  S.e1 = e1;
+  S.e2 = cross3(L, e1);
+  S.rw = P.rw, S.rh = P.rh;
+  // strip width: sheet_px pixels where the planes are spread widest on the screen (smallest |grad phi| over a coarse pixel grid)
+  auto phi_at = [&](double x, double y) {
+    const double sx = x / h->width - 0.5, sy = y / h->height - 0.5;
+    const double d[3] = { h->cam_dir.x + sx * h->cam_hor.x + sy * h->cam_ver.x, h->cam_dir.y + sx * h->cam_hor.y + sy * h->cam_ver.y,
+                          h->cam_dir.z + sx * h->cam_hor.z + sy * h->cam_ver.z };
+    return std::atan2(d[0] * S.e2.x + d[1] * S.e2.y + d[2] * S.e2.z, d[0] * S.e1.x + d[1] * S.e1.y + d[2] * S.e1.z);
+  };
+  auto wrap = [](double a) {
+    while (a > M_PI) a -= 2 * M_PI;
+    while (a < -M_PI) a += 2 * M_PI;
+    return a;
+  };
+  double gmin = 1e30;
+  for (int gy = 0; gy <= 8; gy++)
+    for (int gx = 0; gx <= 16; gx++) {
+      const double x = (gx / 16.0) * (h->width - 1) + 0.5, y = (gy / 8.0) * (h->height - 1) + 0.5;
+      const double p0 = phi_at(x, y), dx = wrap(phi_at(x + 1.0, y) - p0), dy = wrap(phi_at(x, y + 1.0) - p0);
+      const double g = std::sqrt(dx * dx + dy * dy);
+      if (g > 0.0) gmin = std::min(gmin, g);
+    }
+  if (!(gmin < 1e29)) gmin = 1.0 / std::max(h->width, h->height);
+  const double dphi = std::max(gmin * (double)h->tune.sheet_px, 2.0 * M_PI / (double)(1 << 18));
+  S.inv_dphi = (float)(1.0 / dphi);
+  S.super_w = P.super_w, S.rank = h->rank, S.nranks = h->nranks, S.n_warp_tiles = n;
+  sheet_key_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(S, h->wt_keys[0], h->wt_vals[0]);
+  CK(cudaGetLastError());
+  size_t bytes = h->wt_tmp_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(h->wt_tmp, bytes, h->wt_keys[0], h->wt_keys[1], h->wt_vals[0], h->wt_vals[1], n, 0, 32, h->stream));
+  launches += 4; // key kernel + the passes of the radix sort (histogram, scan, onesweep: version dependent; counted as 3)
+  h->wt_count = n;
+  h->wt_dir = h->cam_dir, h->wt_hor = h->cam_hor, h->wt_ver = h->cam_ver, h->wt_light = L;
+  h->wt_rank = h->rank, h->wt_nranks = h->nranks, h->wt_w = h->width, h->wt_h = h->height, h->wt_px = h->tune.sheet_px;
+  P.wt_order = h->wt_vals[1];
+  return B200VR_OK;
+}
+
+// resident CTAs per SM of a kernel at (threads, shared bytes), with the shared-memory attributes set once per configuration
+static int launch_config(b200vr_t* h, const KernelChoice& kc, int& per_sm)
+{
+  const auto key = std::make_tuple((const void*)kc.fn, kc.threads, kc.smem, h->tune.carveout);
+  auto it = h->launch_cache.find(key);
+  if (it == h->launch_cache.end()) {
+    if (kc.smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kc.smem));
+    if (h->tune.carveout >= 0)
+      CK(cudaFuncSetAttribute((const void*)kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, h->tune.carveout));
+    LaunchConfig lc;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lc.per_sm, (const void*)kc.fn, kc.threads, kc.smem));
+    it = h->launch_cache.emplace(key, lc).first;
+  }
+  per_sm = it->second.per_sm;
+  return B200VR_OK;
+}
+
+// Enqueues one frame on the handle's stream (Impl::render, device_impl.cpp:199-269, minus the wait): accumulation bookkeeping,
+// launch order, the render kernel(s), events around them. Nothing here blocks the host except a sparse frame's 4-byte
+// pixel-count read (the reference waits for thrust::remove the same way) and a reallocation of the task rings.
+static int render_enqueue(b200vr_t* h)
+{
   if (!h->has_volume) return fail(h, B200VR_ESTATE, "render: no volume");
   if (!h->has_tf) return fail(h, B200VR_ESTATE, "render: no transfer function");
   if (!h->has_camera) return fail(h, B200VR_ESTATE, "render: no camera");
   if (h->width <= 0 || h->height <= 0) return fail(h, B200VR_ESTATE, "render: framebuffer size not set");
   CK(cudaSetDevice(h->device));
   // accumulation bookkeeping (device_impl.cpp:225-241)
-  if (h->prm.accumulate && h->reset) h->frame_index = 0;
+  const bool accum_reset = h->prm.accumulate && h->reset;
+  if (accum_reset) h->frame_index = 0;
   h->reset = false;
   h->frame_index++;
 
   LaunchParams P;
   fill_launch_params(h, P);
   if (h->has_lattice && !(h->prm.mode == B200VR_MODE_RAYMARCH && h->prm.shading == B200VR_SHADING_NONE &&
-                           h->prm.sampler == B200VR_SAMPLER_TEX3D &&
-                           (!std::getenv("B200VR_KERNEL") || std::strcmp(std::getenv("B200VR_KERNEL"), "sm") == 0)))
+                           h->prm.sampler == B200VR_SAMPLER_TEX3D && (h->tune.kernel == KERNEL_AUTO || h->tune.kernel == KERNEL_SM)))
     return fail(h, B200VR_ESTATE, "render: a brick (sort-last) needs ray marching with SHADING_NONE and the tex3D sampler: "
                                   "shadow rays and random walks leave the brick");
   const KernelChoice kc = pick_kernel(h);
-  int sparse_launches = 0;
+  int extra_launches = 0;
   if (h->sparse) {
     if ((kc.ring && h->prm.accumulate) || h->nranks != 1 || h->has_lattice || h->target_rgba)
       return fail(h, B200VR_ESTATE, "render: sparse sampling is a single-device mode (no tile partition, brick or frame target)");
-    const int rc = build_sparse_list(h, P, sparse_launches);
+    if (accum_reset) {
+      // framebuffer.reset() on an accumulation reset zeroes both buffers (device_impl.cpp:225-233, optix7_common.h:250-253,
+      // 409-413): pixels the new view does not sample must not keep the previous view's content
+      const size_t npx = (size_t)h->width * h->height;
+      for (int i = 0; i < 2; i++) {
+        CK(cudaMemsetAsync(h->rgba[i], 0, npx * sizeof(float4), h->stream));
+        CK(cudaMemsetAsync(h->grad[i], 0, npx * 3 * sizeof(float), h->stream));
+      }
+      CK(cudaMemsetAsync(h->accum, 0, npx * sizeof(float4), h->stream));
+    }
+    const int rc = build_sparse_list(h, P, extra_launches);
     if (rc != B200VR_OK) return rc;
   }
   const render_kernel_t kernel = kc.fn;
   const size_t smem = kc.smem;
-  if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kernel, kc.threads, smem));
-  if (per_sm < 1) return fail(h, B200VR_ECUDA, "render: kernel does not fit on an SM");
-  if (const char* cap = std::getenv("B200VR_MAX_CTAS_PER_SM")) // experiments: fewer warps in flight = shorter reuse distance in L2
-    per_sm = std::max(1, std::min(per_sm, std::atoi(cap)));
+  {
+    const int rc = launch_config(h, kc, per_sm);
+    if (rc != B200VR_OK) return rc;
+  }
+  if (per_sm < 1) return fail(h, B200VR_ECUDA, "render: kernel does not fit on an SM (transfer-function table too large for shared memory?)");
+  if (h->tune.max_ctas_per_sm > 0) per_sm = std::min(per_sm, h->tune.max_ctas_per_sm); // fewer warps in flight = shorter reuse distance in L2
   const int warps_per_cta = kc.threads / 32;
   const int want = (P.n_warp_tiles + warps_per_cta - 1) / warps_per_cta;
   int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
@@ -1015,18 +1275,27 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
   CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
   {
-    // launch order: owned super tiles by descending cost of the previous frame (no history: centre-out)
+    // launch order of the owned tiles. Super-tile orders (tile_order_kernel): 0 row-major (default), 1 centre-out, 2 by the
+    // previous frame's cost, 3 Z-order, 4/5 columns, 6 middle rows first. Measured on C2 with the queue kernel: 2.29 / 2.52 /
+    // 2.42 ms for 0 / 1 / 2 -- launching neighbouring tiles together keeps their texels in L1/L2, and a heavy tile is itself
+    // the critical path whenever it starts (tools/partition_probe.py), so "expensive first" buys nothing. 7: warp tiles in
+    // sheet order (build_sheet_order), for shaded frames of volumes much larger than L2.
     const int n_owned = P.n_warp_tiles / WARP_TILES_PER_SUPER;
+    int order_mode = h->tune.tile_order == TILE_ORDER_AUTO ? TILE_ORDER_ROWS : h->tune.tile_order;
+    const bool shaded_march = h->prm.mode == B200VR_MODE_RAYMARCH && h->prm.shading == B200VR_SHADING_REF;
+    if (order_mode == TILE_ORDER_SHEET && (!shaded_march || P.sparse_xy)) order_mode = TILE_ORDER_ROWS;
     if (!h->cost_valid) CK(cudaMemsetAsync(h->tile_cost[h->cost_cur ^ 1], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
-    // 0 (default) row-major, 1 centre-out, 2 by the previous frame's cost. Measured on C2 with the queue kernel: 2.29 / 2.52 /
-    // 2.42 ms -- launching neighbouring tiles together keeps their texels in L1/L2, and a heavy tile is itself the critical
-    // path whenever it starts (tools/partition_probe.py), so "expensive first" buys nothing.
-    const char* om = std::getenv("B200VR_TILE_ORDER");
-    const int order_mode = om ? std::atoi(om) : 0;
-    if (n_owned > 0) {
+    if (order_mode == TILE_ORDER_SHEET && !P.sparse_xy) {
+      const int rc = build_sheet_order(h, P, extra_launches);
+      if (rc != B200VR_OK) return rc;
+    }
+    const int super_mode = order_mode == TILE_ORDER_SHEET ? TILE_ORDER_ROWS : order_mode;
+    if (n_owned > 0 && (super_mode != h->order_mode_done || super_mode == TILE_ORDER_COST || !h->cost_valid)) {
       tile_order_kernel<<<(n_owned + 127) / 128, 128, 0, h->stream>>>(h->tile_cost[h->cost_cur ^ 1], n_owned, h->rank, h->nranks,
-                                                                       P.super_w, P.super_h, h->tile_order, order_mode);
+                                                                       P.super_w, P.super_h, h->tile_order, super_mode);
       CK(cudaGetLastError());
+      h->order_mode_done = super_mode;
+      extra_launches++;
     }
     CK(cudaMemsetAsync(h->tile_cost[h->cost_cur], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
     h->cost_valid = true;
@@ -1035,8 +1304,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
   int launches = 0;
   if (kc.ring && P.n_warp_tiles > 0) {
     // one ring per CTA: high-water mark + one block in flight per warp of the CTA + slack, as a power of two
-    const char* hw = std::getenv("B200VR_RING_HIGH");
-    P.ring_high = hw ? std::max(1, std::atoi(hw)) : 4; // blocks kept ready per CTA for warps that have run out of tiles
+    P.ring_high = h->tune.ring_high;
     int cap = 32;
     while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
     if (cap != h->ring_cap || grid != h->ring_count) {
@@ -1051,6 +1319,7 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
       h->ring_cap = cap, h->ring_count = grid;
       ring_init_kernel<<<64, 256, 0, h->stream>>>(h->ring_seq, cap, grid, h->ring_ctrl, (int)ring_ctrl_words(grid));
       CK(cudaGetLastError());
+      extra_launches++;
     }
     P.ring_ctrl = h->ring_ctrl, P.ring_seq = h->ring_seq, P.ring_data = h->ring_data, P.ring_cap = h->ring_cap;
   }
@@ -1069,8 +1338,11 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
       if (sidx > 0) CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
       ring_start_kernel<<<(grid + 127) / 128, 128, 0, h->stream>>>(h->ring_ctrl, RING_CTRL_STRIDE, grid, warps_per_cta);
       CK(cudaGetLastError());
+      // The warps of the ring kernel wait on one another (draining warps for marching ones): every CTA has to be resident.
+      // A cooperative launch fails with an error instead of hanging when the grid cannot be (another handle or stream on
+      // the same GPU, an MPS limit).
       void* args[] = { (void*)&P };
-      CK(cudaLaunchKernel((const void*)kernel, dim3((unsigned)grid), dim3((unsigned)kc.threads), args, smem, h->stream));
+      CK(cudaLaunchCooperativeKernel((const void*)kernel, dim3((unsigned)grid), dim3((unsigned)kc.threads), args, smem, h->stream));
       const size_t npx = (size_t)n_owned * SUPER_TILE_W * SUPER_TILE_H;
       resolve_kernel<<<(unsigned)std::min<size_t>((npx + 255) / 256, (size_t)h->sm_count * 16), 256, 0, h->stream>>>(P, n_owned);
       CK(cudaGetLastError());
@@ -1078,26 +1350,45 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     }
   }
   CK(cudaEventRecord(h->ev1, h->stream));
+  h->last_launches = launches + extra_launches;
+  h->last_ring = kc.ring;
+  h->last_grid = grid, h->last_warps_per_cta = warps_per_cta;
+  h->pending = true;
+  return B200VR_OK;
+}
+
+// Waits for the frame enqueued last and fetches its counters (the cudaDeviceSynchronize of DeviceOptix7::render, device.cpp:34-43)
+static int render_wait(b200vr_t* h, b200vr_stats* stats)
+{
+  CK(cudaSetDevice(h->device));
   Counters c;
-  CK(cudaMemcpyAsync(&c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+  std::memset(&c, 0, sizeof(c));
   unsigned int ring_err = 0;
-  if (kc.ring && h->ring_ctrl) CK(cudaMemcpyAsync(&ring_err, h->ring_ctrl + (size_t)h->ring_count * RING_CTRL_PER_RING + RING_CTRL_STRIDE, sizeof(ring_err), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream)); // synchronous like DeviceOptix7::render (device.cpp:34-43)
+  if (h->pending) {
+    CK(cudaMemcpyAsync(&c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+    if (h->last_ring && h->ring_ctrl)
+      CK(cudaMemcpyAsync(&ring_err, h->ring_ctrl + (size_t)h->ring_count * RING_CTRL_PER_RING + RING_CTRL_STRIDE, sizeof(ring_err),
+                         cudaMemcpyDeviceToHost, h->stream));
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  const bool had_frame = h->pending;
+  h->pending = false;
   if (ring_err) {
     h->ring_cap = 0; // rebuilt on the next render
     return fail(h, B200VR_ECUDA, "render: the deferred-shading ring timed out (internal error)");
   }
-  if (B200VR_TILE_STATS && std::getenv("B200VR_DEBUG_TILES")) { // build with -DB200VR_TILE_STATS=1
+  if (B200VR_TILE_STATS && h->tune.debug_tiles && had_frame) { // build with -DB200VR_TILE_STATS=1
     float ms = 0.f;
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    const int warps = h->last_grid * h->last_warps_per_cta;
     std::fprintf(stderr, "[b200] tiles: kernel %.3f ms, longest warp tile %.0f kclk, all tiles %.0f Mclk over %d warps = %.0f kclk each\n", ms,
-                 c.tile_clocks_max * 1e-3, c.tile_clocks_sum * 1e-6, grid * warps_per_cta, c.tile_clocks_sum * 1e-3 / (grid * warps_per_cta));
+                 c.tile_clocks_max * 1e-3, c.tile_clocks_sum * 1e-6, warps, c.tile_clocks_sum * 1e-3 / warps);
     std::fprintf(stderr, "[b200] ring: longest warp %.0f kclk, after the last tile %.0f kclk per warp, blocks published %llu, taken by draining warps %llu\n",
-                 c.warp_clocks_max * 1e-3, c.drain_clocks_sum * 1e-3 / (grid * warps_per_cta), c.blocks_published, c.blocks_stolen);
+                 c.warp_clocks_max * 1e-3, c.drain_clocks_sum * 1e-3 / warps, c.blocks_published, c.blocks_stolen);
   }
   if (stats) {
     float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    if (had_frame) CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     stats->ms = ms;
     stats->primary_samples = c.primary_samples;
     stats->shadow_samples = c.shadow_samples;
@@ -1105,9 +1396,29 @@ extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
     stats->delta_samples = c.delta_samples;
     stats->rays = c.rays;
     stats->frame_index = h->frame_index;
-    stats->kernel_launches = launches + sparse_launches;
+    stats->kernel_launches = h->last_launches;
   }
   return B200VR_OK;
+}
+
+extern "C" int b200vr_render(b200vr_t* h, b200vr_stats* stats)
+{
+  if (!h) return B200VR_EINVAL;
+  const int rc = render_enqueue(h);
+  if (rc != B200VR_OK) return rc;
+  return render_wait(h, stats);
+}
+
+extern "C" int b200vr_render_async(b200vr_t* h)
+{
+  if (!h) return B200VR_EINVAL;
+  return render_enqueue(h);
+}
+
+extern "C" int b200vr_wait(b200vr_t* h, b200vr_stats* stats)
+{
+  if (!h) return B200VR_EINVAL;
+  return render_wait(h, stats);
 }
 
 extern "C" int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev)

@@ -226,6 +226,41 @@ __global__ void tile_order_kernel(const unsigned int* __restrict__ cost, int n_o
   order[pos] = i;
 }
 
+// ---- sheet order of the warp tiles (shaded frames) -----------------------------------------------------------------
+// All shadow rays are parallel (fixed directional light L, params.h:79). The primary rays of the pixels on one image line
+// through the vanishing point of L lie in one plane through the eye that contains L, and so do all their shadow rays: the
+// planes form a pencil around the axis (eye, L) and cut the volume into disjoint wedges. Warp tiles launched in the order of
+// their plane angle phi (then along the plane) make the tiles in flight share a few wedges instead of spreading their
+// shadow slabs over the whole volume: the voxels a wedge needs stay in L2 while its tiles run. Any order is a valid order
+// (the frame does not depend on it); this one is chosen for the 1024^3 volume, where the rays of a row-major launch re-read
+// the volume from HBM ~13 times (profiles/r1c_ncu_full_raymarch_q_C3.txt).
+struct SheetParams {
+  f3 cam_dir, cam_hor, cam_ver;
+  f3 e1, e2, light;   // e1, e2: orthonormal basis of the plane perpendicular to the light direction; phi = atan2(d.e2, d.e1)
+  float rw, rh;       // 1 / image size
+  float inv_dphi;     // 1 / (plane angle per strip)
+  int super_w, rank, nranks, n_warp_tiles;
+};
+__global__ void sheet_key_kernel(const SheetParams S, unsigned int* __restrict__ keys, unsigned int* __restrict__ vals)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= S.n_warp_tiles) return;
+  // k-th owned warp tile in the default (row-major) walk, as warp_tile_origin() with the identity order
+  const int m = k / WARP_TILES_PER_SUPER, r = k % WARP_TILES_PER_SUPER;
+  const int s = S.rank + m * S.nranks;
+  const int b = r / TILE_CHUNK, i = r % TILE_CHUNK;
+  const int px = (s % S.super_w) * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W;
+  const int py = (s / S.super_w) * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
+  const float sx = ((float)px + 0.5f * WARP_TILE_W) * S.rw, sy = ((float)py + 0.5f * WARP_TILE_H) * S.rh;
+  const f3 d = S.cam_dir + (sx - 0.5f) * S.cam_hor + (sy - 0.5f) * S.cam_ver; // centre ray of the tile (unnormalised)
+  const float phi = atan2f(dot3(d, S.e2), dot3(d, S.e1));
+  const int strip = min(max(__float2int_rd(phi * S.inv_dphi) + (1 << 18), 0), (1 << 19) - 1);
+  const float along = dot3(d, S.light) * rsqrtf(dot3(d, d)); // cosine between the ray and the light: position along the strip
+  const int a = min(max(__float2int_rn((along * 0.5f + 0.5f) * 4095.f), 0), 4095);
+  keys[k] = ((unsigned int)strip << 12) | (unsigned int)a;
+  vals[k] = (unsigned int)(px / WARP_TILE_W) | ((unsigned int)(py / WARP_TILE_H) << 16);
+}
+
 // ---- end of a ring-kernel sample: fixed-point sums -> frame (the tail of raymarch_q_kernel, per pixel of the owned super tiles) ----
 __global__ void resolve_kernel(const LaunchParams P, int n_owned)
 {

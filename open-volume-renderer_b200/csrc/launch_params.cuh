@@ -88,6 +88,7 @@ struct LaunchParams {
   int n_warp_tiles;         // warp tiles this launch has to render
   unsigned int* tile_counter;
   const int* tile_order;    // launch order of the owned super tiles: tile_order[j] = slot m (super tile rank + m * nranks)
+  const unsigned int* wt_order; // optional launch order of the owned WARP tiles (sheet order, build.cuh): entry k = (px / 8) | (py / 4) << 16
   unsigned int* tile_cost;  // per slot m: warp clocks / 64 spent on its warp tiles in THIS launch (orders the next one)
   Counters* counters;
   // ---- sparse (foveated) sampling, sparse.cuh: when set, warp tile k renders list entries 32k .. 32k+31 ----
@@ -128,8 +129,13 @@ __device__ __forceinline__ int warp_tile_pixel(const LaunchParams& P, int k, int
     ix = c.x, iy = c.y;
     return -1;
   }
-  int px, py;
-  const int m = warp_tile_origin(P, k, px, py);
+  int px, py, m;
+  if (P.wt_order != nullptr) { // explicit order of the warp tiles (sheet order): the table holds the tile origin
+    const unsigned int v = __ldg(P.wt_order + k);
+    px = (int)(v & 0xffffu) * WARP_TILE_W, py = (int)(v >> 16) * WARP_TILE_H;
+    m = ((px / SUPER_TILE_W) + (py / SUPER_TILE_H) * P.super_w - P.rank) / P.nranks; // cost-table slot of its super tile
+  }
+  else m = warp_tile_origin(P, k, px, py);
   ix = px + (lane & (WARP_TILE_W - 1)), iy = py + (lane / WARP_TILE_W);
   return m;
 }

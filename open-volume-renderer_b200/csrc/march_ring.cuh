@@ -110,7 +110,7 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
   int count = 0; // tasks staged (warp-uniform)
   const long long warp_t0 = clock64();
   long long drain_t0 = 0;
-  unsigned int n_pub = 0, n_stolen = 0;
+  unsigned int n_pub = 0, n_stolen = 0, idle_spins = 0;
 
   for (;;) {
     if (marching && !have_tile) {
@@ -243,11 +243,20 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
         }
         if (found < 0) {
           int done = 0;
-          if (lane == 0) done = ld_acquire_u32(r_left_all) == 0u || ld_relaxed_u32(r_err) != 0u;
+          if (lane == 0) {
+            done = ld_acquire_u32(r_left_all) == 0u || ld_relaxed_u32(r_err) != 0u;
+            // bounded like every other wait: r_left_all counts all warps of the grid, also those of CTAs that are not resident
+            // yet -- the launch is cooperative (b200vr.cu), so they are, but a hang must never be the failure mode
+            if (!done && ++idle_spins > RING_SPIN_LIMIT / 16) {
+              atomicExch(r_err, 1u);
+              done = 1;
+            }
+          }
           if (__shfl_sync(0xffffffffu, done, 0)) break; // nobody marches any more and every published block was claimed
           __nanosleep(500);
           continue;
         }
+        idle_spins = 0u;
         unsigned int* const c_ctrl = P.ring_ctrl + (size_t)found * RING_CTRL_PER_RING;
         unsigned int* const c_seq = P.ring_seq + (size_t)found * P.ring_cap;
         unsigned int t = 0;

@@ -77,7 +77,8 @@ class MainRenderer:
         self._cuda_device = cuda_device
         self._h = None
         self._initialized = False
-        # device-specific switches (the C++ plugin reads them from argv: --b200-shading, --b200-sampler, --b200-no-skip)
+        # device-specific switches (the C++ plugin reads them from the environment: OVR_B200_SHADING, OVR_B200_SAMPLER, ...)
+        self._options = {}               # tuning options set before init (b200vr_set_option)
         self.shading = capi.SHADING_REF
         self.sampler = capi.SAMPLER_TEX3D
         self.skip_empty = True
@@ -132,6 +133,14 @@ class MainRenderer:
     def set_light_radius(self, v): self.params["radius"].assign(v)
     def set_light_intensity(self, v): self.params["intensity"].assign(v)
 
+    def set_option(self, name, value):
+        """b200vr_set_option: tuning switches that choose between kernels / launch orders rendering the same frame
+        (include/b200vr.h). Before init the option is kept and applied when the device is created."""
+        if self._h is None:
+            self._options[str(name)] = str(value)
+        else:
+            self._ck(capi.lib().b200vr_set_option(self._h, str(name).encode(), str(value).encode()))
+
     # ---- unsafe getters ----
     def unsafe_get_fbsize(self):
         return self.params["fbsize"].get()
@@ -171,6 +180,8 @@ class MainRenderer:
         if rc != capi.OK:
             raise RuntimeError("[b200] " + L.b200vr_last_error(None).decode())
         self._h = h
+        for k, v in self._options.items():
+            self._ck(L.b200vr_set_option(self._h, k.encode(), v.encode()))
         self._rate, self._spp, self._path_tracing, self._accumulate = float(scene.volume_sampling_rate), 1, False, False
         # set_scene (ovr/renderer.h:299-341): flatten the TF into (rgb...) and (pos, alpha)... float arrays
         tfn = scene.tfn
@@ -258,6 +269,19 @@ class MainRenderer:
         self.render_time += (time.perf_counter() - t0) * 1e3
         self.last_stats = st.as_dict()
         self.variance = 0.0
+
+    def render_async(self):
+        """b200vr_render_async: the frame is enqueued on the device's stream; wait() collects its counters."""
+        if self.params["fbsize"].get() is None:
+            return
+        self._ck(capi.lib().b200vr_render_async(self._h))
+        self.variance = 0.0
+
+    def wait(self):
+        st = capi.Stats()
+        self._ck(capi.lib().b200vr_wait(self._h, C.byref(st)))
+        self.last_stats = st.as_dict()
+        return self.last_stats
 
     def use_stream(self, cuda_stream_handle):
         """Run every kernel / copy of this device on the given CUDA stream (e.g. torch.cuda.current_stream().cuda_stream), so

@@ -171,6 +171,56 @@ def test_raymarch_matches_oracle(case):
     r.close()
 
 
+VARIANT_SCENES = [
+    # name, dims, tf, camera, rate, W, H
+    ("noise64-oblique", (64, 64, 64), "sparse", "oblique", 1.0, 200, 120),
+    ("ragged-dense", (70, 45, 33), "dense", "oblique", 1.0, 203, 117),      # ragged volume and frame: partial tiles, partial passes
+    ("inside-rate2", (48, 48, 48), "ramp", "inside", 2.0, 160, 96),
+]
+VARIANT_OPTIONS = [
+    # every shading kernel, each with the macrocell occupancy mask staged in shared memory (small grids) and read from global
+    # memory (occ_smem = 0: the instantiations that 1024^3-class volumes select, pick_kernel in csrc/b200vr.cu), and the
+    # sheet launch order
+    {"kernel": "q"}, {"kernel": "q", "occ_smem": 0}, {"kernel": "q", "tile_order": 7},
+    {"kernel": "qb2"}, {"kernel": "qb4"}, {"kernel": "qb4", "occ_smem": 0}, {"kernel": "qb4", "occ_smem": 0, "tile_order": 7, "sheet_px": 16},
+    {"kernel": "qb8"}, {"kernel": "qb8", "occ_smem": 0, "max_ctas_per_sm": 1},
+    {"kernel": "ring"}, {"kernel": "ring", "occ_smem": 0}, {"kernel": "ring", "occ_smem": 0, "tile_order": 7},
+]
+
+
+@pytest.mark.parametrize("scene", VARIANT_SCENES, ids=[c[0] for c in VARIANT_SCENES])
+def test_every_shading_kernel_variant_matches_the_oracle(scene):
+    """All kernels that can render a shaded frame, with both placements of the occupancy mask and both launch orders, on the same
+    frame: each within the parity bar of the oracle, the queue kernels bit-identical to one another (same per-task arithmetic,
+    same summation order), the ring kernel within its fixed-point quantisation; identical executed-sample counters."""
+    name, dims, tf, cam, rate, W, H = scene
+    sc = S.noise_scene(max(dims), dims=dims, tf=tf, camera=cam, rate=rate)
+    r = make_renderer(sc, W, H)
+    d = oracle_desc(sc, W, H, volume=device_volume(r, dims))
+    o_rgba, o_grad, o_cnt = pyoracle.OracleScene(d, skip_empty=True).render_march()
+    base = None
+    for opts in VARIANT_OPTIONS:
+        for k in ("kernel", "occ_smem", "tile_order", "sheet_px", "max_ctas_per_sm"):
+            r.set_option(k, opts.get(k, {"kernel": "auto", "occ_smem": -1, "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0}[k]))
+        r.render()
+        rgba, grad = r.download()
+        st = dict(r.last_stats)
+        e, p, eg = max_abs(rgba, o_rgba), psnr(rgba, o_rgba), max_abs(grad, o_grad)
+        print(f"{name} {opts}: max-abs {e:.2e} psnr {p:.1f} dB grad {eg:.2e} samples {st['primary_samples']}+{st['shadow_samples']}")
+        assert e <= TOL and p >= 45.0 and eg <= 4 * TOL, opts
+        if base is None:
+            base = (rgba.copy(), grad.copy(), st)
+            continue
+        for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
+            assert st[k] == base[2][k], (opts, k)
+        if opts["kernel"] == "ring":
+            assert max_abs(rgba, base[0]) < 1e-4 and max_abs(grad, base[1]) < 1e-4, opts
+        else:
+            assert np.array_equal(rgba.view(np.uint32), base[0].view(np.uint32)), opts
+            assert np.array_equal(grad.view(np.uint32), base[1].view(np.uint32)), opts
+    r.close()
+
+
 def test_spp_jitter_and_accumulation_semantics():
     W, H = 96, 64
     sc = S.noise_scene(32, tf="ramp", camera="oblique")
@@ -231,14 +281,12 @@ def test_sort_first_tiles_reassemble_bit_exact():
     r = make_renderer(sc, W, H)
     r.render()
     full_q = r.download()[0].copy()
-    os.environ["B200VR_KERNEL"] = "ring"
-    try:
-        r.render()
-        full = r.download()[0].copy()
-        r.render()
-        assert np.array_equal(r.download()[0].view(np.uint32), full.view(np.uint32))   # deterministic run to run
-    finally:
-        del os.environ["B200VR_KERNEL"]
+    r.set_option("kernel", "ring")
+    r.render()
+    full = r.download()[0].copy()
+    r.render()
+    assert np.array_equal(r.download()[0].view(np.uint32), full.view(np.uint32))   # deterministic run to run
+    r.set_option("kernel", "auto")
     # 30-bit fixed-point contributions, then C / A: pixels with a tiny opacity amplify the 2^-31 quantisation
     assert max_abs(full, full_q) < 1e-4
     L = capi.lib()

@@ -47,10 +47,10 @@ def main():
     if rank == 0:
         r.render()
         want_q = r.download(want_grad=False)[0].copy()     # undivided frame, queue kernel (float sums in march order)
-        os.environ["B200VR_KERNEL"] = "ring"              # undivided frame, ring kernel: what the partitions must reproduce bit for bit
+        r.set_option("kernel", "ring")                     # undivided frame, ring kernel: what the partitions must reproduce bit for bit
         r.render()
         want = r.download(want_grad=False)[0].copy()
-        del os.environ["B200VR_KERNEL"]
+        r.set_option("kernel", "auto")
     sf = D.SortFirst(r, rank, world)
     sf.step()
     torch.cuda.synchronize()
