@@ -146,7 +146,8 @@ struct b200vr {
   int wt_rank = -1, wt_nranks = -1, wt_w = 0, wt_h = 0, wt_px = 0;
   // last frame (b200vr_render_async -> b200vr_wait)
   int last_launches = 0, last_grid = 0, last_warps_per_cta = 1;
-  int order_mode_done = -1;        // super-tile order mode h->tile_order currently holds
+  int order_mode_done = -1;        // super-tile order mode h->tile_order currently holds,
+  int order_n_done = 0;            // and for how many owned super tiles
   bool last_ring = false;
   bool pending = false;            // a frame was enqueued and its counters have not been fetched
 };
@@ -1290,11 +1291,13 @@ static int render_enqueue(b200vr_t* h)
       if (rc != B200VR_OK) return rc;
     }
     const int super_mode = order_mode == TILE_ORDER_SHEET ? TILE_ORDER_ROWS : order_mode;
-    if (n_owned > 0 && (super_mode != h->order_mode_done || super_mode == TILE_ORDER_COST || !h->cost_valid)) {
+    // the table is kept from frame to frame; sparse frames walk the pixel list and neither use nor touch it
+    if (n_owned > 0 && !P.sparse_xy &&
+        (super_mode != h->order_mode_done || n_owned != h->order_n_done || super_mode == TILE_ORDER_COST || !h->cost_valid)) {
       tile_order_kernel<<<(n_owned + 127) / 128, 128, 0, h->stream>>>(h->tile_cost[h->cost_cur ^ 1], n_owned, h->rank, h->nranks,
                                                                        P.super_w, P.super_h, h->tile_order, super_mode);
       CK(cudaGetLastError());
-      h->order_mode_done = super_mode;
+      h->order_mode_done = super_mode, h->order_n_done = n_owned;
       extra_launches++;
     }
     CK(cudaMemsetAsync(h->tile_cost[h->cost_cur], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
