@@ -169,6 +169,24 @@ int b200vr_set_sparse_noise(b200vr_t* h, const float* table_or_null, int tile_xy
  * pairs in launch order -- image-tile order, not the reference's row-major order; the set is the reference's */
 int64_t b200vr_get_sparse_samples(b200vr_t* h, int32_t* xy_out_or_null, int64_t capacity_pairs);
 
+/* Allocation-free variant of the sparse-sample list above. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same mask, same compaction kernels and same tile-ordered list as a sparse b200vr_render produces
+ * (b200vr_get_sparse_samples), but nothing is allocated, freed, copied back or waited for: the three kernels are enqueued on
+ * the handle's stream and the call returns. The per-block scratch of the compaction lives in a static device array of
+ * B200VR_NOALLOC_MAX_ENTRIES / 1024 words (64 KiB, held by every GPU that loads the library until the process exits), so the
+ * frame, padded to whole 64x32-pixel tiles, may hold at most B200VR_NOALLOC_MAX_ENTRIES pixels (a 3840x2160 frame has 8.4 M);
+ * larger frames are refused with B200VR_EINVAL. All pointers except focus_center are DEVICE pointers the caller owns:
+ * noise_dev = the [y][x][t] table (tile_xy * tile_xy * tile_t floats), xy_out_dev = room for width * height (x, y) int32 pairs
+ * (capacity_pairs says how many; the count is only known on the device), count_out_dev = one uint32 that receives the number of
+ * pairs written. The handle supplies the device and the stream only; its own sparse-sampling state is neither read nor
+ * changed. All calls in a process share the one scratch array of a GPU: calls that overlap on that GPU (different streams or
+ * handles) race; calls on one stream are ordered and need no clearing in between. */
+#define B200VR_NOALLOC_MAX_ENTRIES (1 << 24)
+int b200vr_sparse_samples_noalloc(b200vr_t* h, const float* noise_dev, int tile_xy, int tile_t, int width, int height,
+                                  int frame_index, const float focus_center[2], float focus_scale, float base_noise,
+                                  int32_t* xy_out_dev, int64_t capacity_pairs, uint32_t* count_out_dev);
+
 /* replaces Impl::render (device_impl.cpp:199-269): one synchronous frame; stats may be NULL */
 int b200vr_render(b200vr_t* h, b200vr_stats* stats);
 /* The same frame without the wait: b200vr_render_async enqueues the frame on the handle's stream and returns;

@@ -88,6 +88,8 @@ SYMBOLS = {
     "b200vr_set_sparse_sampling": (C.c_int, [_P, C.c_int, _FP, C.c_float, C.c_float]),
     "b200vr_set_sparse_noise": (C.c_int, [_P, _P, C.c_int, C.c_int]),
     "b200vr_get_sparse_samples": (C.c_int64, [_P, _P, C.c_int64]),
+    "b200vr_sparse_samples_noalloc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _FP, C.c_float, C.c_float,
+                                              _P, C.c_int64, _P]),
 }
 
 _lib = None

@@ -22,6 +22,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <tuple>
 #include <vector>
@@ -1201,6 +1202,78 @@ static int build_sheet_order(b200vr_t* h, LaunchParams& P, int& launches)
   h->wt_rank = h->rank, h->wt_nranks = h->nranks, h->wt_w = h->width, h->wt_h = h->height, h->wt_px = h->tune.sheet_px;
   P.wt_order = h->wt_vals[1];
   return B200VR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// allocation-free variant of the sparse-sample compaction (no counterpart in the reference):
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it)
+// ---------------------------------------------------------------------------------------------------------------------
+// The compaction kernels of sparse.cuh need one word of scratch per 1024 enumeration entries (per-block counts, turned into
+// exclusive offsets in place). b200vr_render keeps that scratch in cudaMalloc'ed memory of the handle (build_sparse_list); here
+// it lives in a file-scope device array of fixed size, which every GPU that loads the library holds until the process exits.
+constexpr int NOALLOC_MAX_BLOCKS = B200VR_NOALLOC_MAX_ENTRIES / SPARSE_BLOCK; // 16384 words = 64 KiB
+static __device__ __align__(256) unsigned int g_noalloc_block_counts[NOALLOC_MAX_BLOCKS];
+
+namespace {
+// In host code the array's name is only a stand-in for the symbol, not a device address: the address is asked of the runtime
+// once per device, with that device current, and handed to the kernels as an ordinary pointer.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned int* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+std::mutex g_noalloc_mutex;
+}
+
+static int noalloc_scratch(b200vr_t* h, unsigned int** out)
+{
+  if (h->device < 0 || h->device >= NOALLOC_MAX_DEVICES) return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: device index above 63");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[h->device]) {
+    unsigned int* ptr = nullptr;
+    CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_block_counts)); // the caller made h->device current
+    g_noalloc_ptr[h->device] = ptr;
+  }
+  *out = g_noalloc_ptr[h->device];
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_sparse_samples_noalloc(b200vr_t* h, const float* noise_dev, int tile_xy, int tile_t, int width, int height,
+                                             int frame_index, const float focus_center[2], float focus_scale, float base_noise,
+                                             int32_t* xy_out_dev, int64_t capacity_pairs, uint32_t* count_out_dev)
+{
+  if (!h) return B200VR_EINVAL;
+  if (!noise_dev || !focus_center || !xy_out_dev || !count_out_dev) return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: NULL argument");
+  if (tile_xy <= 0 || tile_t <= 0 || width <= 0 || height <= 0) return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: sizes must be positive");
+  if (!(focus_scale > 0.f)) return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: focus_scale must be positive");
+  const long long super_w = (width + SUPER_TILE_W - 1) / SUPER_TILE_W, super_h = (height + SUPER_TILE_H - 1) / SUPER_TILE_H;
+  const long long n_entries = super_w * super_h * WARP_TILES_PER_SUPER * 32;
+  if (n_entries > (long long)B200VR_NOALLOC_MAX_ENTRIES)
+    return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: frame too large for the static scratch (the image padded to 64x32-pixel tiles "
+                                  "may hold at most B200VR_NOALLOC_MAX_ENTRIES = 16777216 pixels); use b200vr_render with sparse sampling instead");
+  if (capacity_pairs < (int64_t)width * height)
+    return fail(h, B200VR_EINVAL, "sparse_samples_noalloc: xy_out_dev must have room for width * height pairs (the count is not known on the host)");
+  CK(cudaSetDevice(h->device));
+  unsigned int* blocks = nullptr;
+  {
+    const int rc = noalloc_scratch(h, &blocks);
+    if (rc != B200VR_OK) return rc;
+  }
+  SparseParams S;
+  S.noise = noise_dev;
+  S.tile_xy = tile_xy, S.tile_t = tile_t;
+  S.width = width, S.height = height;
+  S.super_w = (int)super_w;
+  S.n_entries = (int)n_entries;
+  S.frame_index = frame_index;
+  S.mean_x = focus_center[0], S.mean_y = focus_center[1];
+  S.sigma_rcp2 = 1.f / (focus_scale * focus_scale); // generate_mask.cu:92
+  S.base_noise = base_noise;
+  const int n_blocks = (S.n_entries + SPARSE_BLOCK - 1) / SPARSE_BLOCK;
+  // Nothing has to start at zero: sparse_count_kernel overwrites the first n_blocks words, sparse_scan_kernel rewrites them in
+  // place and writes *count_out_dev; words beyond n_blocks keep an earlier call's contents and are never read.
+  sparse_count_kernel<<<n_blocks, SPARSE_BLOCK, 0, h->stream>>>(S, blocks);
+  sparse_scan_kernel<<<1, 1024, 0, h->stream>>>(blocks, n_blocks, count_out_dev);
+  sparse_scatter_kernel<<<n_blocks, SPARSE_BLOCK, 0, h->stream>>>(S, blocks, (int2*)xy_out_dev);
+  CK(cudaGetLastError());
+  return B200VR_OK; // stream-ordered on the handle's stream: no wait, no read-back, no allocation
 }
 
 // resident CTAs per SM of a kernel at (threads, shared bytes), with the shared-memory attributes set once per configuration
