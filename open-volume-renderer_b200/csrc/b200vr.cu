@@ -10,6 +10,7 @@
 #include "march_sm.cuh"
 #include "march_q.cuh"
 #include "march_qb.cuh"
+#include "march_qc.cuh"
 #include "march_ring.cuh"
 #include "march_ns.cuh"
 #include "sparse.cuh"
@@ -34,7 +35,7 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_RING, KERNEL_LEGACY, KERNEL_SM };
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_RING, KERNEL_LEGACY, KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
 struct Tuning {
@@ -184,13 +185,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -833,6 +834,9 @@ struct KernelChoice {
 #define B200VR_K_QB2(a, b, c) raymarch_qb_kernel<a, b, c, 2>
 #define B200VR_K_QB4(a, b, c) raymarch_qb_kernel<a, b, c, 4>
 #define B200VR_K_QB8(a, b, c) raymarch_qb_kernel<a, b, c, 8>
+#define B200VR_K_QC4(a, b, c) raymarch_qc_kernel<a, b, c, 4>
+#define B200VR_K_QC6(a, b, c) raymarch_qc_kernel<a, b, c, 6>
+#define B200VR_K_QC8(a, b, c) raymarch_qc_kernel<a, b, c, 8>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
 #define B200VR_K_NS(a, b, c) raymarch_ns_kernel<a, b, c>
 
@@ -879,6 +883,18 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       else if (force == KERNEL_QB8) {
         k.fn = B200VR_PICK(B200VR_K_QB8, skip, pow2, occs);
         k.threads = QB_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qb_kernel";
+      }
+      else if (force == KERNEL_QC4) {
+        k.fn = B200VR_PICK(B200VR_K_QC4, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<4>(), k.name = "raymarch_qc_kernel";
+      }
+      else if (force == KERNEL_QC6) {
+        k.fn = B200VR_PICK(B200VR_K_QC6, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel";
+      }
+      else if (force == KERNEL_QC8) {
+        k.fn = B200VR_PICK(B200VR_K_QC8, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel";
       }
       else {
         k.fn = B200VR_PICK(B200VR_K_Q, skip, pow2, occs);

@@ -65,6 +65,28 @@ __device__ __forceinline__ float4 lds_f32x4(unsigned int addr)
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
   return v;
 }
+// The same load as a volatile asm WITHOUT the memory clobber: it is neither removed, merged nor hoisted (the slots it reads
+// change from pass to pass) and it keeps its order among the other volatile asm statements -- all the shared-memory loads and
+// stores of these kernels -- but it is no barrier for the arithmetic and the texture fetches around it, so the loads of
+// independent tasks can be interleaved with them. (A pure, non-volatile asm is wrong here: with loop-invariant operands the
+// compiler reuses one pass's values in the next.)
+__device__ __forceinline__ float4 lds_f32x4_nv(unsigned int addr)
+{
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+// tex3D<float>(t, x, y, z) as ONE predicated instruction (the PTX nvcc emits for tex3D, under a guard predicate): 0 when `on`
+// is false. nvcc puts a branch around a conditional tex3D(); in straight-line code that interleaves several independent
+// tasks a branch per fetch is what keeps the tasks apart.
+__device__ __forceinline__ float tex3d_if(cudaTextureObject_t t, float x, float y, float z, bool on)
+{
+  float v;
+  asm("{\n\t.reg .pred p;\n\t.reg .f32 d1, d2, d3;\n\tsetp.ne.u32 p, %5, 0;\n\tmov.f32 %0, 0f00000000;\n\t"
+      "@p tex.3d.v4.f32.f32 {%0, d1, d2, d3}, [%1, {%2, %3, %4, %4}];\n\t}"
+      : "=f"(v) : "l"(t), "f"(x), "f"(y), "f"(z), "r"((unsigned int)on));
+  return v;
+}
 __device__ __forceinline__ void sts_f32x4(unsigned int addr, float4 v)
 {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" : : "r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");

@@ -1,0 +1,392 @@
+// Ray-march kernel with gradient + shadow shading, sixth generation: the depth-blocked shading passes of march_qb.cuh
+// (J tasks per lane, all shadow lattices walked in lockstep) on a register diet and software-pipelined.
+//
+// Why (profiles/r2d_ncu_metrics_C3_q_vs_qb.csv, 1024^3): depth blocking took the DRAM reads of a frame from 55.5 GB to 23.2 GB
+// (J = 4) / 18.1 GB (J = 8) and the L1 hit rate from 47 % to 72-75 %, but the launch only went from 10.7 to 8.7 ms: at
+// 2.7 TB/s it is no longer HBM-bound, it waits -- 16 resident warps per SM (128 registers per thread), each with J fetches in
+// flight that mostly miss L2 (hit rate 34 %), issue slots 40 % busy. More fetches in flight per register is what is needed:
+//   * a task's position p (3 registers per task in march_qb.cuh) is re-read from its queue slot in shared memory at every
+//     shadow step (one LDS.128; the shared-memory pipe is idle otherwise);
+//   * the lattice clock is shared: a shadow ray starts at t = 0 at its sample (the sample is inside the box), so the running
+//     fp32 sums stx, sty = stx + sstep of raymarching_shadow (shaders_raymarching.cu:44-85) are the same numbers for every
+//     task and are kept once per lane; only the last interval of a ray is cut by its own exit st1 (one register per task).
+//     The rare task whose clip entry is not exactly 0 (a sample a rounding error outside the box) is marched on its own
+//     after the lockstep loop with the plain per-task loop, so every task still sees exactly the reference's lattice;
+//   * per task that leaves st1, the log-transmittance and the fetched value: 3 registers, so that the fetches of step k + 1
+//     are issued BEFORE step k is classified (one more register per task) -- 2 J fetches in flight per lane, speculative
+//     past early termination like the primary march's prefetch (an unused fetch is not counted as a sample).
+// Everything a task computes is shade_task()'s (march_q.cuh) arithmetic, sample for sample; contributions return to the
+// owning pixel in march order: frames are bit-identical to march_q.cuh / march_qb.cuh.
+#pragma once
+#include "march_qb.cuh"
+
+namespace b200k {
+
+#ifndef B200VR_QC_MIN_CTAS
+#define B200VR_QC_MIN_CTAS 2
+#endif
+constexpr int QC_THREADS = 256;
+constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
+
+// slot layout (32 bytes): [0] p.x  [4] p.y  [8] p.z  [12] s  [16] w  [20] log2-transmittance of an off-lattice task  [24] [28] -
+// after shading:          [0] C.x  [4] C.y  [8] C.z  [12] G.x [16] G.y [20] G.z
+
+template<bool SKIP, bool POW2, bool OCCS, int J>
+__global__ void __launch_bounds__(QC_THREADS, QC_MIN_CTAS)
+raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
+{
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float2* const s_apair = reinterpret_cast<float2*>(smem);
+  unsigned int* const s_occ = reinterpret_cast<unsigned int*>(smem + q_alpha_bytes(P.n_alpha));
+  const unsigned int apair_base = pin_u32((unsigned int)__cvta_generic_to_shared(smem));
+  const unsigned int occ_base = pin_u32(apair_base + (unsigned int)q_alpha_bytes(P.n_alpha));
+  const unsigned int queue_base = pin_u32(occ_base + (unsigned int)(OCCS ? q_occ_bytes(P.occ_words) : 0) +
+                                          (unsigned int)warp * (unsigned int)(qb_slots<J>() * Q_SLOT_FLOATS * sizeof(float)));
+  if (SKIP && OCCS)
+    for (int i = threadIdx.x; i < P.occ_words; i += blockDim.x) s_occ[i] = P.occ_bits[i];
+  for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
+    const float v0 = P.tf_alpha[min(i, P.n_alpha - 1)], v1 = P.tf_alpha[min(i + 1, P.n_alpha - 1)];
+    s_apair[i] = make_float2(v0, (v1 - v0) * (1.f / 256.f));
+  }
+  __syncthreads();
+  const f3 oo = P.cam_oo;
+  const float step = P.step;
+  unsigned int c_primary = 0, c_shadow = 0, c_shaded = 0, c_rays = 0; // per lane, over all tiles of this warp
+  const unsigned int lt_mask = (1u << lane) - 1u;
+  const unsigned int my_slot0 = queue_base + 32u * (unsigned)lane; // task j of this lane: slot j * 32 + lane
+
+  for (;;) {
+    int k = 0;
+    if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
+    k = __shfl_sync(0xffffffffu, k, 0);
+    if (k >= P.n_warp_tiles) break;
+    int ix, iy;
+    const int tile_slot = warp_tile_pixel(P, k, lane, ix, iy);
+    const long long tile_t0 = clock64();
+    const bool inside = ix < P.width && iy < P.height;
+    const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
+
+    for (int sidx = 0; sidx < P.spp; sidx++) {
+      // ---- ray generation + clip (shaders_common.h:400-404, shaders_raymarching.cu:351-362, shaders_common.h:156-184) ----
+      float sx = ((float)ix + .5f) * P.rw, sy = ((float)iy + .5f) * P.rh;
+      if (P.spp > 1) {
+        Tea rng((unsigned)P.frame_index, pixel_index); // RandomTEA(v0 = frame_index, v1 = pixel_index): draw number sidx + 1
+        float2 j = rng.draw();
+        for (int d = 0; d < sidx; d++) j = rng.draw();
+        sx += (j.x - 0.5f) * P.rw;
+        sy += (j.y - 0.5f) * P.rh;
+      }
+      const f3 dir = normalize3(P.cam_dir + (sx - 0.5f) * P.cam_hor + (sy - 0.5f) * P.cam_ver);
+      f3 od = xfm_vector(P.wto.l, dir);
+      float tx = 0.f, t1 = FLT_MAX;
+      bool alive = inside && intersect_box(tx, t1, oo, od, P.clip_lo, P.clip_hi);
+      if (inside) c_rays++;
+      float ty = fminf(t1, tx + step);
+      alive = alive && ty > tx;
+      float A = 0.f;
+      f3 C = mk3(0.f), G = mk3(0.f);
+      float cell_exit = -1.f; // macrocell the ray is in: valid while the sample parameter stays below cell_exit
+      bool cell_empty = false;
+      float s_pre = 0.f;     // prefetched value of the sample at (tx, ty), valid while have_pre
+      bool have_pre = false;
+      unsigned int mine[J + 1]; // queue slots holding this pixel's tasks, 32 per word
+#pragma unroll
+      for (int g = 0; g <= J; g++) mine[g] = 0u;
+      int count = 0;            // tasks waiting (warp-uniform)
+
+      for (;;) {
+        const bool any_alive = __any_sync(0xffffffffu, alive);
+        if (count >= J * 32 || (!any_alive && count > 0)) {
+          // =================== shading pass: lane takes tasks lane, lane + 32, ... ===================
+          const int n = min(count, J * 32);
+          __syncwarp();
+          // ---- A. exit parameter st1 of every task's shadow ray (__closesthit__volume_shadow, shaders_raymarching.cu:205-229);
+          //         tasks whose clip entry is not exactly 0 do not sit on the shared lattice and are set aside ----
+          float st1[J], slog[J];
+          unsigned int live = 0u, odd = 0u; // bit j: task j of this lane marches in lockstep / is marched on its own afterwards
+#pragma unroll
+          for (int j = 0; j < J; j++) {
+            st1[j] = 0.f;
+            slog[j] = 0.f;
+            if (j * 32 + lane < n) {
+              const float4 q0 = lds_f32x4(my_slot0 + 1024u * (unsigned)j);
+              float t0;
+              if (clip_shadow_p(P, mk3(q0.x, q0.y, q0.z), t0, st1[j])) {
+                if (t0 != 0.f) odd |= 1u << j;
+                else if (fminf(st1[j], P.sstep) > 0.f) live |= 1u << j; // first interval [0, min(st1, 0 + sstep)] is not empty
+              }
+            }
+          }
+          // ---- B. lockstep shadow march on the shared lattice (raymarching_shadow, shaders_raymarching.cu:44-85) ----
+          // The body is straight-line code: every task's arithmetic is done for all J tasks, finished ones included, and only
+          // the texture fetch and the updates are predicated. With per-task branches ptxas keeps the J chains apart and a warp
+          // issues one dependent chain after the other (profiles/r2f: 25 % of the stall samples "wait", 0.5 eligible warps per
+          // scheduler and cycle with 4 resident warps); as selects the J independent chains interleave.
+          // fetches of the interval [a, min(st1, b)] for the tasks in `mask`
+          auto issue = [&](float a, float b, unsigned int mask, float (&sv)[J], unsigned int& fetched) {
+            fetched = 0u;
+#pragma unroll
+            for (int j = 0; j < J; j++) {
+              const float tm = 0.5f * (a + fminf(st1[j], b));
+              const float4 q0 = lds_f32x4_nv(my_slot0 + 1024u * (unsigned)j);
+              const f3 q = mk3(__fmaf_rn(tm, P.sh_d.x, q0.x), __fmaf_rn(tm, P.sh_d.y, q0.y), __fmaf_rn(tm, P.sh_d.z, q0.z));
+              bool on = ((mask >> j) & 1u) != 0u;
+              // a sample in an empty macrocell has alpha == 0 exactly and adds 0 to the log sum: cell test only
+              // (pad_index_floor clamps the index, so the test is harmless for the garbage position of a finished task)
+              if (SKIP) {
+                const bool occ = occ_bit<OCCS>(P, occ_base, pad_index_floor(P, q)); // evaluated for every task: no branch
+                on = on & occ;
+              }
+              sv[j] = tex3d_if(P.tex, q.x, q.y, q.z, on);
+              fetched |= on ? (1u << j) : 0u;
+            }
+          };
+          {
+            float stx = 0.f, sty = P.sstep; // running fp32 sums of the reference: stx += sstep from the clip entry 0
+            float sv0[J], sv1[J];
+            unsigned int f0, f1;
+            issue(stx, sty, live, sv0, f0);
+            while (live != 0u) {
+              const float nsty = sty + P.sstep;
+              unsigned int geo = 0u; // tasks whose ray has a next interval [sty, min(st1, nsty)]
+#pragma unroll
+              for (int j = 0; j < J; j++) geo |= fminf(st1[j], nsty) > sty ? (1u << j) : 0u;
+              geo &= live;
+              issue(sty, nsty, geo, sv1, f1); // in flight while the current step is classified; unused if the ray ends here
+              const unsigned int cls = live & f0;
+              c_shadow += (unsigned int)__popc(cls);
+              unsigned int ert = 0u;
+#pragma unroll
+              for (int j = 0; j < J; j++) {
+                const float a = alpha_lookup<POW2>(P, apair_base, sv0[j]);
+                // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
+                const float v = __fmaf_rn(P.base * (fminf(st1[j], sty) - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog[j]);
+                slog[j] = ((cls >> j) & 1u) ? v : slog[j];
+                ert |= slog[j] > P.log_ert ? (1u << j) : 0u;
+              }
+              live = geo & ert;
+              stx = sty, sty = nsty;
+              f0 = f1;
+#pragma unroll
+              for (int j = 0; j < J; j++) sv0[j] = sv1[j];
+            }
+          }
+          // ---- C. tasks off the shared lattice, one at a time (rare): result through the task's slot ----
+          const unsigned int was_odd = odd;
+          while (odd != 0u) {
+            const int j = __ffs(odd) - 1;
+            odd &= odd - 1u;
+            const unsigned int slot = my_slot0 + 1024u * (unsigned)j;
+            const float4 q0 = lds_f32x4(slot);
+            const f3 p = mk3(q0.x, q0.y, q0.z);
+            float sl = 0.f, stx, st;
+            if (clip_shadow_p(P, p, stx, st)) {
+              float sty = fminf(st, stx + P.sstep);
+              while (sty > stx && sl > P.log_ert) {
+                const float tm = 0.5f * (stx + sty);
+                const f3 q = mk3(__fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
+                if (!SKIP || occ_bit<OCCS>(P, occ_base, pad_index_floor(P, q))) {
+                  c_shadow++;
+                  const float a = alpha_lookup<POW2>(P, apair_base, tex3D<float>(P.tex, q.x, q.y, q.z));
+                  sl = __fmaf_rn(P.base * (sty - stx), lg2_fast(fmaxf(1.f - a, 0.f)), sl);
+                }
+                stx = sty;
+                sty = fminf(st, sty + P.sstep);
+              }
+            }
+            asm volatile("st.shared.f32 [%0], %1;" : : "r"(slot + 20u), "f"(sl) : "memory");
+          }
+          // ---- D. gradient, normals, shading (shaders_raymarching.cu:126-169): the 3 J gradient fetches first, then the arithmetic ----
+          float gx[J], gy[J], gz[J];
+#pragma unroll
+          for (int j = 0; j < J; j++) {
+            gx[j] = gy[j] = gz[j] = 0.f;
+            if (j * 32 + lane < n) {
+              const float4 q0 = lds_f32x4(my_slot0 + 1024u * (unsigned)j);
+              // compute_volume_gradient_object_space (shaders_common.h:195-215): forward differences, step 1/dims
+              const float sx_ = q0.x + P.rdim.x > 1.f ? -P.rdim.x : P.rdim.x;
+              const float sy_ = q0.y + P.rdim.y > 1.f ? -P.rdim.y : P.rdim.y;
+              const float sz_ = q0.z + P.rdim.z > 1.f ? -P.rdim.z : P.rdim.z;
+              gx[j] = tex3D<float>(P.tex, q0.x + sx_, q0.y, q0.z);
+              gy[j] = tex3D<float>(P.tex, q0.x, q0.y + sy_, q0.z);
+              gz[j] = tex3D<float>(P.tex, q0.x, q0.y, q0.z + sz_);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < J; j++) {
+            if (j * 32 + lane < n) {
+              const unsigned int slot = my_slot0 + 1024u * (unsigned)j;
+              const float4 q0 = lds_f32x4(slot), q1 = lds_f32x4(slot + 16u);
+              const float s = q0.w, w = q1.x;
+              const float sl = ((was_odd >> j) & 1u) ? q1.y : slog[j];
+              c_shaded++;
+              const f3 rgb = color_global<POW2>(P, s);
+              const float sx_ = q0.x + P.rdim.x > 1.f ? -P.rdim.x : P.rdim.x;
+              const float sy_ = q0.y + P.rdim.y > 1.f ? -P.rdim.y : P.rdim.y;
+              const float sz_ = q0.z + P.rdim.z > 1.f ? -P.rdim.z : P.rdim.z;
+              // shading normals: v * rsqrt.approx(|v|^2) as in shade_task(); the zero-gradient case gives NaN -> clamp -> 0
+              const f3 normal_o = -normalize3_fast(mk3((gx[j] - s) * rcp_fast(sx_), (gy[j] - s) * rcp_fast(sy_), (gz[j] - s) * rcp_fast(sz_)));
+              const f3 normal_w = normalize3_fast(xfm_vector(P.wto_t, normal_o));
+              const f3 normal_c = normalize3_fast(xfm_vector(P.wtc, normal_w));
+              const float cosNL = fabsf(dot3(P.light_dir, normal_w));
+              const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(sl); // light_rgb = 2; 1 - shadow.alpha = 2^slog
+              const f3 cC = clamp01(rgb * k_sh) * w, cG = clamp01(normal_c) * w; // shaders_raymarching.cu:156-165
+              sts_f32x4(slot, make_float4(cC.x, cC.y, cC.z, cG.x));
+              sts_f32x4(slot + 16u, make_float4(cG.y, cG.z, 0.f, 0.f));
+            }
+          }
+          __syncwarp();
+          // every pixel adds its own samples' contributions in march order (= slot order)
+#pragma unroll
+          for (int g = 0; g < J; g++) {
+            unsigned int own = mine[g];
+            const int left = n - g * 32; // slots of this word that were shaded
+            if (left < 32) own = left > 0 ? own & ((1u << left) - 1u) : 0u;
+            while (own) {
+              const int j = __ffs(own) - 1;
+              own &= own - 1u;
+              const unsigned int slot = queue_base + 32u * (unsigned)(g * 32 + j);
+              const float4 r0 = lds_f32x4(slot), r1 = lds_f32x4(slot + 16u);
+              C = C + mk3(r0.x, r0.y, r0.z);
+              G = G + mk3(r0.w, r1.x, r1.y);
+            }
+          }
+          __syncwarp();
+          // move the tasks that did not fit (at most 31, all in word J) to the front
+          const int rest = count - n;
+          float4 m0, m1;
+          if (lane < rest) m0 = lds_f32x4(queue_base + 32u * (unsigned)(n + lane)), m1 = lds_f32x4(queue_base + 32u * (unsigned)(n + lane) + 16u);
+          __syncwarp();
+          if (lane < rest) sts_f32x4(queue_base + 32u * (unsigned)(lane), m0), sts_f32x4(queue_base + 32u * (unsigned)(lane) + 16u, m1);
+          const unsigned int carried = rest > 0 ? mine[J] : 0u;
+#pragma unroll
+          for (int g = 0; g <= J; g++) mine[g] = 0u;
+          mine[0] = carried;
+          count = rest;
+          continue;
+        }
+        if (!any_alive) break;
+
+        // =================== one primary sample per live ray (raymarching, shaders_raymarching.cu:87-171) ===================
+        bool want = false;
+        f3 tp = mk3(0.f);
+        float ts = 0.f, tw = 0.f;
+        if (alive) {
+          do {
+            const float tm = 0.5f * (tx + ty);
+            const f3 p = mk3(__fmaf_rn(tm, od.x, oo.x), __fmaf_rn(tm, od.y, oo.y), __fmaf_rn(tm, od.z, oo.z));
+            if (SKIP) {
+              if (!(tm < cell_exit)) {
+                i3 c;
+                cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
+                // approximate reciprocals: see march_q.cuh
+                cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od);
+              }
+              if (cell_empty) {
+                // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
+                const float lim = fminf(cell_exit, t1) - 5.f * step;
+                while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
+                  ty += step;
+                  ty += step;
+                  ty += step;
+                  ty += step;
+                }
+                do {
+                  tx = ty;
+                  ty = fminf(tx + step, t1);
+                } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
+                alive = ty > tx;
+                break;
+              }
+            }
+            float s;
+            if (have_pre) s = s_pre;
+            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+            {
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+              const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
+              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
+            }
+            c_primary++;
+            float a = alpha_lookup<POW2>(P, apair_base, s);
+            {
+              const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
+              if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));
+            }
+            if (!SKIP || a != 0.f) {
+              tw = (1.f - A) * a;
+              A += tw;
+              tp = p;
+              ts = s;
+              want = true;
+            }
+            tx = ty;
+            ty = fminf(tx + step, t1);
+            alive = ty > tx && A < 0.9999f;
+          } while (0);
+        }
+        const unsigned int m = __ballot_sync(0xffffffffu, want);
+        if (want) {
+          const int slot = count + __popc(m & lt_mask);
+          sts_f32x4(queue_base + 32u * (unsigned)(slot), make_float4(tp.x, tp.y, tp.z, ts));
+          sts_f32x4(queue_base + 32u * (unsigned)(slot) + 16u, make_float4(tw, 0.f, 0.f, 0.f));
+          const unsigned int bit = 1u << (slot & 31);
+#pragma unroll
+          for (int g = 0; g <= J; g++) mine[g] |= (slot >> 5) == g ? bit : 0u; // selects, not a dynamic index: the words stay in registers
+        }
+        count += __popc(m);
+      }
+      // render_raymarching (shaders_raymarching.cu:260-321): background is always 0 -> alpha_blend = C / A
+      if (!P.premultiplied) { // un-premultiply; A == 0 adds nothing, as alpha_blend does
+        C = A > 0.f ? C / A : mk3(0.f);
+        G = A > 0.f ? G / A : mk3(0.f);
+      }
+      if (inside) {
+        float4 px4 = make_float4(C.x, C.y, C.z, A);
+        float* g = P.grad + 3 * (size_t)pixel_index;
+        if (sidx > 0) { // running sums over the samples of this pixel
+          const float4 prev = P.rgba[pixel_index];
+          px4 = make_float4(prev.x + px4.x, prev.y + px4.y, prev.z + px4.z, prev.w + px4.w);
+          G = G + mk3(g[0], g[1], g[2]);
+        }
+        if (sidx == P.spp - 1) {
+          const float rspp = 1.f / (float)P.spp;
+          px4 = make_float4(px4.x * rspp, px4.y * rspp, px4.z * rspp, px4.w * rspp);
+          G = G * rspp;
+          // frame write / progressive accumulation (shaders_raymarching.cu:389-406)
+          if (P.accumulate) {
+            if (P.frame_index == 1) {
+              P.accum[pixel_index] = px4;
+            }
+            else {
+              const float4 acc = P.accum[pixel_index];
+              const float4 sum = make_float4(acc.x + px4.x, acc.y + px4.y, acc.z + px4.z, acc.w + px4.w);
+              P.accum[pixel_index] = sum;
+              const float fi = (float)P.frame_index;
+              px4 = make_float4(sum.x / fi, sum.y / fi, sum.z / fi, sum.w / fi);
+            }
+          }
+        }
+        P.rgba[pixel_index] = px4;
+        g[0] = G.x;
+        g[1] = G.y;
+        g[2] = G.z;
+      }
+    }
+    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
+  }
+
+  // executed-sample counters: one atomic set per warp
+  const unsigned int n_primary = __reduce_add_sync(0xffffffffu, c_primary), n_shadow = __reduce_add_sync(0xffffffffu, c_shadow);
+  const unsigned int n_shaded = __reduce_add_sync(0xffffffffu, c_shaded), n_rays = __reduce_add_sync(0xffffffffu, c_rays);
+  if (lane == 0) {
+    atomicAdd(&P.counters->primary_samples, (unsigned long long)n_primary);
+    atomicAdd(&P.counters->shadow_samples, (unsigned long long)n_shadow);
+    atomicAdd(&P.counters->gradient_fetches, 3ull * n_shaded);
+    atomicAdd(&P.counters->rays, (unsigned long long)n_rays);
+  }
+}
+
+} // namespace b200k
