@@ -196,6 +196,10 @@ int b200vr_render(b200vr_t* h, b200vr_stats* stats);
  * (ovr/devices/optix7/device.cpp:34-43). */
 int b200vr_render_async(b200vr_t* h);
 int b200vr_wait(b200vr_t* h, b200vr_stats* stats);
+/* name of the render kernel the last frame was enqueued with ("raymarch_q_kernel", "raymarch_qc_kernel<J=6>", "raymarch_ring_kernel",
+ * "raymarch_ns_kernel", "pathtrace_kernel", ...; "" before the first frame): what the measurement tools put beside a time, the
+ * counterpart of reading the OptiX program names off the reference's pipeline (device_impl.cpp:380-460). Owned by the handle. */
+const char* b200vr_last_kernel(const b200vr_t* h);
 /* Tuning switches of a handle; none changes what is computed per sample, they pick between kernels / launch orders that
  * render the same frame (A/B runs, tests of every kernel variant). Defaults come from the environment variable
  * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | ring | legacy | sm),
@@ -209,6 +213,9 @@ int b200vr_set_option(b200vr_t* h, const char* name, const char* value);
  * (rgba: W*H float4, grad: W*H float3, row 0 = bottom), valid until the next render/resize on this handle */
 int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev);
 int b200vr_swap(b200vr_t* h);
+/* the same pointers for buffer 0 or 1 of the double buffer, whichever is current (b200vr_current_buffer): the direct-send
+ * compositor writes the final frame into the buffer nobody rendered into this frame */
+int b200vr_map_index(b200vr_t* h, int buffer, void** rgba_dev, void** grad_dev);
 int b200vr_download(b200vr_t* h, float* rgba_host, float* grad_host_or_null);
 /* same copy enqueued on a caller-owned cudaStream_t without waiting (pinned host memory): lets the application read frame
  * k while frame k+1 renders into the other buffer after b200vr_swap, the loop of apps/main_app.cpp:244-263
@@ -225,6 +232,12 @@ int b200vr_unpack_tiles(b200vr_t* h, const float* slice_dev, int rank, int nrank
 int b200vr_composite_over(b200vr_t* h, const float* front_dev, const float* back_dev, float* out_dev,
                           int64_t n_pixels);
 int b200vr_finalize_premultiplied(b200vr_t* h, float* rgba_dev, int64_t n_pixels);
+/* sort-last, direct-send schedule: out = layers[0] OVER layers[1] OVER ... OVER layers[n-1] (front to back, the same blend
+ * applied layer by layer) over one pixel range of 1..16 premultiplied float4 layers in ONE pass -- `layers_dev` is a HOST array of
+ * device pointers, normally n-1 of them peer mappings of the other GPUs' frames (read once over NVLink) -- written to out_dev,
+ * which may itself be a peer mapping (the display GPU's frame); finalize != 0 un-premultiplies on the way out
+ * (alpha_blend, shaders_common.h:329-337). No counterpart in the single-device reference. */
+int b200vr_composite_layers(b200vr_t* h, const float* const* layers_dev, int n_layers, float* out_dev, int64_t n_pixels, int finalize);
 /* fused sort-last exchange over NVLink (one process per GPU): a rank exports its two rgba frame buffers as CUDA IPC handles
  * (64 bytes each, sent to the peers by any means), opens the peers' handles and passes the resulting device pointers as
  * `back_dev` / `front_dev` of b200vr_composite_over or as `src_dev` of b200vr_copy_device: the blend then reads the

@@ -68,9 +68,11 @@ SYMBOLS = {
     "b200vr_render": (C.c_int, [_P, C.POINTER(Stats)]),
     "b200vr_render_async": (C.c_int, [_P]),
     "b200vr_wait": (C.c_int, [_P, C.POINTER(Stats)]),
+    "b200vr_last_kernel": (C.c_char_p, [_P]),
     "b200vr_set_option": (C.c_int, [_P, C.c_char_p, C.c_char_p]),
     "b200vr_map": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P)]),
     "b200vr_swap": (C.c_int, [_P]),
+    "b200vr_map_index": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(_P)]),
     "b200vr_download": (C.c_int, [_P, _P, _P]),
     "b200vr_download_async": (C.c_int, [_P, _P, _P, _P]),
     "b200vr_set_brick": (C.c_int, [_P, _P, _P, _P, _P]),
@@ -85,6 +87,7 @@ SYMBOLS = {
     "b200vr_unpack_tiles": (C.c_int, [_P, _P, C.c_int, C.c_int]),
     "b200vr_composite_over": (C.c_int, [_P, _P, _P, _P, C.c_int64]),
     "b200vr_finalize_premultiplied": (C.c_int, [_P, _P, C.c_int64]),
+    "b200vr_composite_layers": (C.c_int, [_P, C.POINTER(_P), C.c_int, _P, C.c_int64, C.c_int]),
     "b200vr_set_sparse_sampling": (C.c_int, [_P, C.c_int, _FP, C.c_float, C.c_float]),
     "b200vr_set_sparse_noise": (C.c_int, [_P, _P, C.c_int, C.c_int]),
     "b200vr_get_sparse_samples": (C.c_int64, [_P, _P, C.c_int64]),

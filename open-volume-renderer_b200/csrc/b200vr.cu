@@ -151,6 +151,7 @@ struct b200vr {
   int order_mode_done = -1;        // super-tile order mode h->tile_order currently holds,
   int order_n_done = 0;            // and for how many owned super tiles
   bool last_ring = false;
+  std::string last_kernel;         // name of the render kernel of the last enqueued frame
   bool pending = false;            // a frame was enqueued and its counters have not been fetched
 };
 
@@ -852,7 +853,12 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   // its heaviest warp tile with the queue kernel (C2-sparse 1.59 ms for a quarter of the samples), so they take the rings too.
   // Not while accumulating: resolve_kernel rewrites every pixel, the reference leaves unsampled pixels untouched then.
   const bool sparse_ring = h->sparse && !p.accumulate;
-  const bool ring = force == KERNEL_RING || (force == KERNEL_AUTO && (h->nranks != 1 || sparse_ring));
+  // Volumes whose occupancy mask does not fit into shared memory (edge > 704 voxels: far beyond the 126 MB L2) are bound by the
+  // shadow rays' DRAM / L2 misses, not by the heaviest tile: the depth-blocked passes of march_qc.cuh win on the whole frame
+  // (C3: 6.2 ms against 10.7 ms for the queue kernel and 11.0 ms for the rings, profiles/r2g_ab_C3_qc.json) and on its partitions.
+  const bool large = p.skip_empty && !q_occ_in_smem(h->occ_words);
+  const bool ring = force == KERNEL_RING || (force == KERNEL_AUTO && ((h->nranks != 1 && !large) || sparse_ring));
+  const bool auto_qc6 = force == KERNEL_AUTO && large && !ring;
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
@@ -886,15 +892,15 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       }
       else if (force == KERNEL_QC4) {
         k.fn = B200VR_PICK(B200VR_K_QC4, skip, pow2, occs);
-        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<4>(), k.name = "raymarch_qc_kernel";
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<4>(), k.name = "raymarch_qc_kernel<J=4>";
       }
-      else if (force == KERNEL_QC6) {
+      else if (force == KERNEL_QC6 || auto_qc6) {
         k.fn = B200VR_PICK(B200VR_K_QC6, skip, pow2, occs);
-        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel";
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel<J=6>";
       }
       else if (force == KERNEL_QC8) {
         k.fn = B200VR_PICK(B200VR_K_QC8, skip, pow2, occs);
-        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel";
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel<J=8>";
       }
       else {
         k.fn = B200VR_PICK(B200VR_K_Q, skip, pow2, occs);
@@ -1444,6 +1450,7 @@ static int render_enqueue(b200vr_t* h)
   CK(cudaEventRecord(h->ev1, h->stream));
   h->last_launches = launches + extra_launches;
   h->last_ring = kc.ring;
+  h->last_kernel = kc.name;
   h->last_grid = grid, h->last_warps_per_cta = warps_per_cta;
   h->pending = true;
   return B200VR_OK;
@@ -1513,12 +1520,23 @@ extern "C" int b200vr_wait(b200vr_t* h, b200vr_stats* stats)
   return render_wait(h, stats);
 }
 
+extern "C" const char* b200vr_last_kernel(const b200vr_t* h) { return h ? h->last_kernel.c_str() : ""; }
+
 extern "C" int b200vr_map(b200vr_t* h, void** rgba_dev, void** grad_dev)
 {
   if (!h) return B200VR_EINVAL;
   if (h->width <= 0) return fail(h, B200VR_ESTATE, "map: framebuffer size not set");
   if (rgba_dev) *rgba_dev = h->rgba[h->current];
   if (grad_dev) *grad_dev = h->grad[h->current];
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_map_index(b200vr_t* h, int buffer, void** rgba_dev, void** grad_dev)
+{
+  if (!h || buffer < 0 || buffer > 1) return B200VR_EINVAL;
+  if (h->width <= 0) return fail(h, B200VR_ESTATE, "map_index: framebuffer size not set");
+  if (rgba_dev) *rgba_dev = h->rgba[buffer];
+  if (grad_dev) *grad_dev = h->grad[buffer];
   return B200VR_OK;
 }
 
@@ -1605,6 +1623,26 @@ extern "C" int b200vr_composite_over(b200vr_t* h, const float* front_dev, const 
     (const float4*)front_dev, (const float4*)back_dev, (float4*)out_dev, (size_t)n_pixels);
   CK(cudaGetLastError());
   if (h->stream == h->own_stream) CK(cudaStreamSynchronize(h->stream)); // on a caller's stream the call is stream-ordered
+  return B200VR_OK;
+}
+
+extern "C" int b200vr_composite_layers(b200vr_t* h, const float* const* layers_dev, int n_layers, float* out_dev, int64_t n_pixels,
+                                       int finalize)
+{
+  if (!h || !layers_dev || !out_dev || n_pixels < 0) return B200VR_EINVAL;
+  if (n_layers < 1 || n_layers > COMPOSITE_MAX_LAYERS) return fail(h, B200VR_EINVAL, "composite_layers: 1 to 16 layers");
+  CompositeLayers L;
+  std::memset(&L, 0, sizeof(L));
+  for (int k = 0; k < n_layers; k++) {
+    if (!layers_dev[k]) return fail(h, B200VR_EINVAL, "composite_layers: NULL layer");
+    L.layer[k] = (const float4*)layers_dev[k];
+  }
+  L.n = n_layers;
+  if (n_pixels == 0) return B200VR_OK;
+  CK(cudaSetDevice(h->device));
+  composite_layers_kernel<<<grid_for((size_t)n_pixels, 256, h->sm_count), 256, 0, h->stream>>>(L, (float4*)out_dev, (size_t)n_pixels, finalize);
+  CK(cudaGetLastError());
+  if (h->stream == h->own_stream) CK(cudaStreamSynchronize(h->stream));
   return B200VR_OK;
 }
 

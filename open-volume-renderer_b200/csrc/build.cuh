@@ -366,6 +366,33 @@ __global__ void composite_over_kernel(const float4* __restrict__ front, const fl
     out[i] = make_float4(f.x + tr * b.x, f.y + tr * b.y, f.z + tr * b.z, f.w + tr * b.w);
   }
 }
+// Direct-send compositing (sort-last): one pass blends the same pixel range of up to COMPOSITE_MAX_LAYERS premultiplied
+// layers front to back (layer[0] nearest the eye) -- each layer read once, straight from the GPU that rendered it when the pointer
+// is a peer mapping -- and writes the result once (possibly into the display GPU's frame). finalize: un-premultiply on the way out
+// (alpha_blend, shaders_common.h:329-337). The blend is composite_over_kernel's, applied layer by layer in the same fp32 order.
+constexpr int COMPOSITE_MAX_LAYERS = 16;
+struct CompositeLayers {
+  const float4* layer[COMPOSITE_MAX_LAYERS];
+  int n;
+};
+__global__ void composite_layers_kernel(const __grid_constant__ CompositeLayers L, float4* out, size_t n, int finalize)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    float4 v[COMPOSITE_MAX_LAYERS];
+#pragma unroll
+    for (int k = 0; k < COMPOSITE_MAX_LAYERS; k++)
+      if (k < L.n) v[k] = __ldcs(L.layer[k] + i); // all loads in flight before the first blend (peer reads: ~2 us each)
+    float4 a = v[0];
+#pragma unroll
+    for (int k = 1; k < COMPOSITE_MAX_LAYERS; k++)
+      if (k < L.n) {
+        const float tr = 1.f - a.w;
+        a = make_float4(a.x + tr * v[k].x, a.y + tr * v[k].y, a.z + tr * v[k].z, a.w + tr * v[k].w);
+      }
+    if (finalize) a = a.w > 0.f ? make_float4(a.x / a.w, a.y / a.w, a.z / a.w, a.w) : make_float4(0.f, 0.f, 0.f, a.w);
+    out[i] = a;
+  }
+}
 __global__ void finalize_premultiplied_kernel(float4* __restrict__ px, size_t n)
 {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {

@@ -271,6 +271,96 @@ class SortLast:
 
 
 # ----------------------------------------------------------------------------------------------------------------------
+# sort-last: direct send
+# ----------------------------------------------------------------------------------------------------------------------
+def visibility_order(eye, dims, nranks, **kw):
+    """Ranks front to back as seen from `eye`, for ALL pixels at once: the brick grid is a BSP tree (bit b of a rank picks
+    the side of the level-b plane), so of two ranks the one on the eye's side of the plane of their HIGHEST differing bit
+    is in front -- the same planes, in the same order, that the rounds of the binary swap use."""
+    import functools
+
+    def cmp(a, b):
+        hb = (a ^ b).bit_length() - 1
+        return -1 if in_front(eye, dims, nranks, hb, a, **kw) else 1
+
+    return sorted(range(nranks), key=functools.cmp_to_key(cmp))
+
+
+def direct_send_ranges(nranks, n_pixels, align=32):
+    """Pixel range [lo, hi) rank k composites under direct send: n_pixels cut into nranks nearly equal strips at multiples
+    of `align` pixels (the last strip takes the remainder)."""
+    per = ((n_pixels + nranks - 1) // nranks + align - 1) // align * align
+    return [(min(k * per, n_pixels), min((k + 1) * per, n_pixels)) for k in range(nranks)]
+
+
+class SortLastDirect:
+    """Direct-send compositing over send/recv (NCCL on the GPUs; gloo with an injected blend in the CPU tests): every rank
+    owns one strip of the image, receives that strip of every other rank's layer, blends the N strips front to back in
+    visibility order and the display rank gathers the N results. One exchange round instead of log2 N, N - 1 messages per
+    rank instead of log2 N. The production path is SortLastDirectP2P; this one is its cross-check."""
+
+    def __init__(self, rank, world, dims, n_pixels, handle_renderer=None, blend=None, group=None, dst=0,
+                 grid_spacing=(1.0, 1.0, 1.0), grid_origin=(0.0, 0.0, 0.0), align=32):
+        self.rank, self.world, self.dims, self.n = rank, world, tuple(dims), n_pixels
+        self.r, self.blend, self.group, self.dst = handle_renderer, blend, group, dst
+        self.kw = dict(grid_spacing=grid_spacing, grid_origin=grid_origin)
+        self.ranges = direct_send_ranges(world, n_pixels, align)
+        self.mine = self.ranges[rank]
+        self.launches = 0
+
+    def composite(self, image, eye):
+        """Returns the [n_pixels * 4] final premultiplied frame on `dst` (in place on `image`), None elsewhere."""
+        import torch
+        import torch.distributed as dist
+        lo, hi = self.mine
+        n = (hi - lo) * 4
+        strips = {self.rank: image[lo * 4:hi * 4].clone()}
+        ops = []
+        for k in range(self.world):
+            if k == self.rank:
+                continue
+            klo, khi = self.ranges[k]
+            strips[k] = torch.empty(n, dtype=torch.float32, device=image.device)
+            if khi > klo:
+                ops.append(dist.P2POp(dist.isend, image[klo * 4:khi * 4], k, self.group))
+            if n > 0:
+                ops.append(dist.P2POp(dist.irecv, strips[k], k, self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        order = visibility_order(eye, self.dims, self.world, **self.kw)
+        if n > 0:
+            if self.blend is not None:
+                acc = strips[order[0]].view(-1, 4)
+                for k in order[1:]:
+                    acc = self.blend(acc, strips[k].view(-1, 4))
+                out = acc.reshape(-1)
+            else:
+                if not image.is_cuda:
+                    raise RuntimeError("SortLastDirect: CPU tensors need an injected blend function; the product path is CUDA only")
+                from . import _capi as capi
+                out = torch.empty(n, dtype=torch.float32, device=image.device)
+                ptrs = (C.c_void_p * self.world)(*[strips[k].data_ptr() for k in order])
+                self.r._ck(capi.lib().b200vr_composite_layers(self.r.handle, ptrs, self.world, C.c_void_p(out.data_ptr()), hi - lo, 0))
+                self.launches += 1
+        else:
+            out = torch.empty(0, dtype=torch.float32, device=image.device)
+        if self.world == 1:
+            image[lo * 4:hi * 4] = out
+            return image
+        longest = max(b - a for a, b in self.ranges) * 4
+        strip = torch.zeros(longest, dtype=torch.float32, device=image.device)
+        strip[:n] = out
+        parts = [torch.empty_like(strip) for _ in range(self.world)] if self.rank == self.dst else None
+        dist.gather(strip, parts, dst=self.dst, group=self.group)
+        if self.rank != self.dst:
+            return None
+        for k, (a, b) in enumerate(self.ranges):
+            image[a * 4:b * 4] = parts[k][:(b - a) * 4]
+        return image
+
+
+# ----------------------------------------------------------------------------------------------------------------------
 # sort-last: per-rank scene + renderer setup
 # ----------------------------------------------------------------------------------------------------------------------
 def brick_scene(scene, rank, nranks):
@@ -339,6 +429,7 @@ class SortLastP2P:
         self.kw = dict(grid_spacing=grid_spacing, grid_origin=grid_origin)
         self.plan, self.mine = binary_swap_plan(rank, world, n_pixels, align)
         self.ranges = final_ranges(world, n_pixels, align)
+        self.direct_ranges = direct_send_ranges(world, n_pixels, align)
         self.launches = 0
         # exchange the IPC handles of both frame buffers, open everybody else's
         mine = []
@@ -394,6 +485,41 @@ class SortLastP2P:
                     self.launches += 1
         self._barrier()       # nobody renders the next frame into a buffer that is still being read
         return own if self.rank == self.dst else None
+
+    def composite_direct(self, eye, finalize=True):
+        """Direct send FUSED with the blend over NVLink peer memory: after one barrier every rank runs ONE kernel
+        (b200vr_composite_layers) over the strip it owns -- it reads that strip of all N layers straight out of the GPUs that
+        rendered them, blends them front to back in visibility order, un-premultiplies and stores the result straight into
+        the display rank's OTHER frame buffer (the one nobody rendered into this frame) -- then one more barrier. Two
+        barriers and one launch per rank and frame against log2 N + 2 barriers, log2 N blends and N - 1 pulls for the binary
+        swap; the bytes over NVLink are the same (N - 1) / N of a frame per rank. Returns, on the display rank, the device
+        pointer of the final frame (its buffer `1 - current`), None elsewhere."""
+        r, L = self.r, self.L
+        cur = int(L.b200vr_current_buffer(r.handle))
+        own = r.mapframe().rgba[0]
+        lo, hi = self.direct_ranges[self.rank]
+        order = visibility_order(eye, self.dims, self.world, **self.kw)
+        base = {k: (own if k == self.rank else self.peer[(k, cur)]) for k in range(self.world)}
+        if self.rank == self.dst:
+            p = C.c_void_p()
+            r._ck(L.b200vr_map_index(r.handle, cur ^ 1, C.byref(p), None))
+            out_base = p.value
+        else:
+            out_base = self.peer[(self.dst, cur ^ 1)]
+        self._barrier()   # every rank's layer is rendered
+        if hi > lo:
+            ptrs = (C.c_void_p * self.world)(*[base[k] + lo * 16 for k in order])
+            r._ck(L.b200vr_composite_layers(r.handle, ptrs, self.world, C.c_void_p(out_base + lo * 16), hi - lo, 1 if finalize else 0))
+            self.launches += 1
+        self._barrier()   # all strips have landed in the display rank's buffer; the layers may be overwritten by the next frame
+        return out_base if self.rank == self.dst else None
+
+
+class SortLastDirectP2P(SortLastP2P):
+    """The direct-send schedule as its own class: composite() = SortLastP2P.composite_direct()."""
+
+    def composite(self, eye, finalize=True):
+        return self.composite_direct(eye, finalize)
 
 
 class SortFirstP2P:

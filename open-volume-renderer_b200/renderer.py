@@ -283,6 +283,11 @@ class MainRenderer:
         self.last_stats = st.as_dict()
         return self.last_stats
 
+    @property
+    def last_kernel(self):
+        """b200vr_last_kernel: name of the render kernel the last frame was enqueued with."""
+        return capi.lib().b200vr_last_kernel(self._h).decode()
+
     def use_stream(self, cuda_stream_handle):
         """Run every kernel / copy of this device on the given CUDA stream (e.g. torch.cuda.current_stream().cuda_stream), so
         that they are ordered with the caller's own work (NCCL collectives, peer copies). Handle 0 is the legacy default

@@ -147,6 +147,7 @@ WORKLOADS = {
     "C4": dict(n=1024, width=1920, height=1080, tf="pt", camera="front", rate=1.0, mode="pathtrace", shading="ref"),
     # sort-last: `n` is the edge of ONE brick; N ranks render a (grid * n)^3-ish volume, 4K frame, no shading
     "C5": dict(n=2048, width=3840, height=2160, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none", sortlast=True),
+    "C5-mid": dict(n=1024, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none", sortlast=True),
     "C5-small": dict(n=256, width=1920, height=1080, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="none", sortlast=True),
     "tiny": dict(n=64, width=160, height=96, tf="sparse", camera="oblique", rate=1.0, mode="raymarch", shading="ref"),
 }

@@ -140,13 +140,14 @@ def _layer(rank, npix, seed=11):
     return np.concatenate([c, a], axis=1)
 
 
-def _worker(rank, world, port, npix, eye, dims, out_q):
+def _worker(rank, world, port, npix, eye, dims, out_q, schedule="swap"):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        sl = D.SortLast(rank, world, dims, npix, blend=D.over_torch, align=8)
+        cls = D.SortLast if schedule == "swap" else D.SortLastDirect
+        sl = cls(rank, world, dims, npix, blend=D.over_torch, align=8)
         img = torch.from_numpy(_layer(rank, npix).ravel().copy())
         with pytest.raises(RuntimeError):   # no injected blend + CPU tensors: the product path refuses
             D.SortLast(rank, world, dims, npix)._over(img[:8], img[:8], img[:8].clone())
@@ -171,8 +172,45 @@ def _expected(world, npix, eye, dims):
     return out
 
 
-@pytest.mark.parametrize("world", [2, 4])
-def test_binary_swap_over_gloo_composites_in_visibility_order(world):
+def test_direct_send_order_and_ranges():
+    """visibility_order: a total order that agrees with the brute-force per-axis sort for eyes outside the volume, and with
+    every round of the binary swap for any eye; direct_send_ranges tile the image."""
+    rng = np.random.default_rng(9)
+    dims = (64, 48, 80)
+    for n in (1, 2, 4, 8, 16):
+        g = D.brick_grid(n)
+        for _ in range(25):
+            eye = rng.uniform(-150, 230, 3)
+            order = D.visibility_order(eye, dims, n)
+            assert sorted(order) == list(range(n))
+            pos = {r: i for i, r in enumerate(order)}
+            for r in range(n):
+                for bit in range(n.bit_length() - 1):
+                    # at round `bit` of the swap r's group is blended in front of its partner's group iff in_front says so
+                    p = r ^ (1 << bit)
+                    mine = [m for m in range(n) if (m >> bit) == (r >> bit)]
+                    theirs = [m for m in range(n) if (m >> bit) == (p >> bit)]
+                    if D.in_front(eye, dims, n, bit, r):
+                        assert max(pos[m] for m in mine) < min(pos[m] for m in theirs)
+            outside = all(eye[a] < 0 or eye[a] > dims[a] for a in range(3))
+            if outside:   # along every axis nearer bricks first: any order consistent with that partial order is valid
+                for a_ in range(n):
+                    for b_ in range(n):
+                        ia, ib = D.brick_index(a_, n), D.brick_index(b_, n)
+                        nearer = all((ia[x] <= ib[x]) if eye[x] < 0 else (ia[x] >= ib[x]) for x in range(3))
+                        if nearer and a_ != b_:
+                            assert pos[a_] < pos[b_]
+        for npix in (1920 * 1080, 1000, 37 * 32, 5):
+            ranges = D.direct_send_ranges(n, npix, align=32)
+            covered = np.zeros(npix, np.int32)
+            for lo, hi in ranges:
+                assert 0 <= lo <= hi <= npix and (lo % 32 == 0 or lo == npix)
+                covered[lo:hi] += 1
+            assert (covered == 1).all() and len(ranges) == n
+
+
+@pytest.mark.parametrize("world,schedule", [(2, "swap"), (4, "swap"), (2, "direct"), (4, "direct")])
+def test_binary_swap_over_gloo_composites_in_visibility_order(world, schedule):
     import torch.multiprocessing as mp
     npix, dims = 40 * 24, (64, 64, 64)
     # eyes outside the volume on either side of every axis: the front/back decision flips with the eye
@@ -180,7 +218,7 @@ def test_binary_swap_over_gloo_composites_in_visibility_order(world):
         ctx = mp.get_context("spawn")
         q = ctx.Queue()
         port = _free_port()
-        procs = [ctx.Process(target=_worker, args=(r, world, port, npix, eye, dims, q)) for r in range(world)]
+        procs = [ctx.Process(target=_worker, args=(r, world, port, npix, eye, dims, q, schedule)) for r in range(world)]
         for p in procs:
             p.start()
         got = q.get(timeout=120)

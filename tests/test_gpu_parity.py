@@ -421,6 +421,26 @@ def test_sort_last_separate_brick_volumes_match_the_single_volume(nbricks):
     got = out.cpu().numpy().reshape(H, W, 4)
     print(f"sort-last {nbricks} brick volumes: max-abs {max_abs(got, want):.2e} psnr {psnr(got, want):.1f} dB")
     assert max_abs(got, want) <= 1.0 / 255.0 and psnr(got, want) >= 45.0   # the north-star bar, against the single-device render
+    # direct send: all layers blended front to back in ONE pass (b200vr_composite_layers), un-premultiplied on the way out;
+    # every strip of the image separately, as the N ranks would do it
+    order = D.visibility_order(eye, sc.volume.dims, nbricks)
+    direct = torch.empty(W * H * 4, dtype=torch.float32, device="cuda")
+    for lo, hi in D.direct_send_ranges(nbricks, W * H):
+        ptrs = (C.c_void_p * nbricks)(*[layers[k].data_ptr() + lo * 16 for k in order])
+        ref._ck(L.b200vr_composite_layers(ref.handle, ptrs, nbricks, C.c_void_p(direct.data_ptr() + lo * 16), hi - lo, 1))
+    got_d = direct.cpu().numpy().reshape(H, W, 4)
+    print(f"sort-last {nbricks} brick volumes, direct send: max-abs {max_abs(got_d, want):.2e} psnr {psnr(got_d, want):.1f} dB, "
+          f"vs binary swap {max_abs(got_d, got):.2e}")
+    assert max_abs(got_d, want) <= 1.0 / 255.0 and psnr(got_d, want) >= 45.0
+    assert max_abs(got_d[..., 3], got[..., 3]) < 1e-5   # `over` is associative up to rounding; colours are divided by alpha afterwards
+    # the same blend as a chain of b200vr_composite_over calls: bit-identical
+    acc = layers[order[0]].clone()
+    for k in order[1:]:
+        ref._ck(L.b200vr_composite_over(ref.handle, C.c_void_p(acc.data_ptr()), C.c_void_p(layers[k].data_ptr()), C.c_void_p(acc.data_ptr()), W * H))
+    ref._ck(L.b200vr_finalize_premultiplied(ref.handle, C.c_void_p(acc.data_ptr()), W * H))
+    assert np.array_equal(acc.cpu().numpy().view(np.uint32), direct.cpu().numpy().view(np.uint32))
+    with pytest.raises(RuntimeError):
+        ref._ck(L.b200vr_composite_layers(ref.handle, (C.c_void_p * 1)(layers[0].data_ptr()), 17, C.c_void_p(direct.data_ptr()), 8, 0))
     for b in rs:
         b.close()
     ref.close()
@@ -471,6 +491,65 @@ def test_error_codes_and_state_machine():
     r.close()
 
 
+def test_double_buffer_swap_map_and_async_download():
+    """SURVEY 8 a22 -- the double buffer of Impl::mapframe / swap (device_impl.cpp:102-111,271-281) as the GUI loop uses it
+    (apps/main_app.cpp:244-263: commit -> mapframe -> to_cpu -> swap -> render): swap flips the buffer, frame k-1 stays intact
+    while frame k renders into the other buffer, the copy of k-1 started before the swap delivers k-1, map is non-owning and
+    its pointers stay valid until the next resize."""
+    import torch
+    from ovr_b200 import distributed as D
+    W, H = 160, 96
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    r = make_renderer(sc, W, H)
+    L = capi.lib()
+    cur0 = L.b200vr_current_buffer(r.handle)
+    fb0 = r.mapframe()
+    p0, g0 = fb0.rgba[0], fb0.grad[0]
+    assert p0 and g0 and fb0.rgba[1] == W * H * 16 and fb0.grad[1] == W * H * 12
+    r.render()
+    frame_a, grad_a = r.download()
+    frame_a, grad_a = frame_a.copy(), grad_a.copy()
+    assert (frame_a[..., 3] > 0).any()
+    fb = r.mapframe()
+    assert (fb.rgba[0], fb.grad[0]) == (p0, g0)                       # a render does not move the buffers
+    pi, gi = C.c_void_p(), C.c_void_p()
+    r._ck(L.b200vr_map_index(r.handle, cur0, C.byref(pi), C.byref(gi)))
+    assert (pi.value, gi.value) == (p0, g0)
+    # frame k-1 starts its way to the host on a stream of the caller, then the buffers flip and frame k renders
+    host_rgba = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+    host_grad = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream()
+    r._ck(L.b200vr_download_async(r.handle, C.c_void_p(host_rgba.data_ptr()), C.c_void_p(host_grad.data_ptr()), C.c_void_p(copy_stream.cuda_stream)))
+    r.swap()
+    assert L.b200vr_current_buffer(r.handle) == cur0 ^ 1
+    fb1 = r.mapframe()
+    p1 = fb1.rgba[0]
+    assert p1 != p0 and fb1.grad[0] != g0
+    r.set_camera(S.camera_preset("front", (48, 48, 48)))
+    r.commit()
+    r.render()                                                        # frame k into the other buffer
+    copy_stream.synchronize()
+    assert np.array_equal(host_rgba.numpy().view(np.uint32), frame_a.view(np.uint32))   # the copy delivered frame k-1
+    assert np.array_equal(host_grad.numpy().view(np.uint32), grad_a.view(np.uint32))
+    frame_b = r.download()[0].copy()
+    assert not np.array_equal(frame_b, frame_a)
+    # frame k-1 is still in its buffer, untouched by the render of frame k (read through the pointer mapped before the swap)
+    still = torch.as_tensor(D._DevicePtr(p0, W * H * 4), device="cuda").cpu().numpy().reshape(H, W, 4)
+    assert np.array_equal(still.view(np.uint32), frame_a.view(np.uint32))
+    r.swap()
+    assert L.b200vr_current_buffer(r.handle) == cur0 and r.mapframe().rgba[0] == p0
+    assert np.array_equal(r.download()[0].view(np.uint32), frame_a.view(np.uint32))
+    r.swap()
+    assert np.array_equal(r.download()[0].view(np.uint32), frame_b.view(np.uint32))
+    # a resize is what ends the life of the pointers: new (zeroed) buffers, map still answers
+    r.set_fbsize((W + 64, H))
+    r.commit()
+    fb2 = r.mapframe()
+    assert fb2.rgba[1] == (W + 64) * H * 16 and not r.download()[0].any()
+    assert L.b200vr_map_index(r.handle, 2, None, None) == capi.EINVAL
+    r.close()
+
+
 def test_multi_gpu_paths_over_nccl():
     """Both exchange paths with one process per GPU (torchrun, NCCL); needs >= 2 GPUs on the box."""
     import json
@@ -489,7 +568,7 @@ def test_multi_gpu_paths_over_nccl():
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     res = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("{")][-1])
     print(res)
-    assert res["sort_first_bit_identical"] and res["sort_last_ok"]
+    assert res["sort_first_bit_identical"] and res["sort_last_ok"] and res["direct_send_ok"]
 
 
 EDGE_CASES = [

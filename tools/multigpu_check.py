@@ -106,6 +106,25 @@ def main():
         torch.cuda.synchronize()
         got2 = b.download(want_grad=False)[0]
         out["sort_last_p2p_equals_nccl"] = bool(np.array_equal(got2.view(np.uint32), got.view(np.uint32)))
+    # direct send, fused over peer memory (one kernel per rank, result straight into rank 0's other buffer), and over NCCL send/recv
+    b.render()
+    ptr = p2p.composite_direct(full.camera.frm)
+    if rank == 0:
+        torch.cuda.synchronize()
+        got3 = torch.as_tensor(D._DevicePtr(ptr, W * H * 4), device="cuda").clone().cpu().numpy().reshape(H, W, 4)
+        err3 = float(np.abs(got3 - want).max())
+        mse3 = float(np.mean((got3.astype(np.float64) - want) ** 2))
+        out["direct_send_p2p_max_abs"] = err3
+        out["direct_send_p2p_psnr_db"] = float("inf") if mse3 == 0 else float(10 * np.log10(1.0 / mse3))
+        out["direct_send_ok"] = bool(err3 <= 1.0 / 255.0 and out["direct_send_p2p_psnr_db"] >= 45.0)
+    b.render()
+    ds = D.SortLastDirect(rank, world, full.volume.dims, W * H, handle_renderer=b)
+    img = ds.composite(D.frame_tensor(b), full.camera.frm)
+    if rank == 0:
+        b._ck(L.b200vr_finalize_premultiplied(b.handle, C.c_void_p(img.data_ptr()), W * H))
+        torch.cuda.synchronize()
+        got4 = img.cpu().numpy().reshape(H, W, 4)
+        out["direct_send_p2p_equals_nccl"] = bool(np.array_equal(got4.view(np.uint32), got3.view(np.uint32)))
     dist.barrier()
     p2p.close()
     b.close()
@@ -114,7 +133,7 @@ def main():
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
     if rank == 0 and not (out["sort_first_bit_identical"] and out["sort_first_p2p_bit_identical"] and out["sort_first_vs_queue_kernel_max_abs"] < 1e-3 and out["sort_last_ok"] and
-                          out["sort_last_p2p_equals_nccl"]):
+                          out["sort_last_p2p_equals_nccl"] and out["direct_send_ok"] and out["direct_send_p2p_equals_nccl"]):
         sys.exit(1)
 
 
