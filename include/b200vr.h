@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define B200VR_ABI_VERSION 3
+#define B200VR_ABI_VERSION 4
 
 enum {
   B200VR_OK = 0,
@@ -202,7 +202,7 @@ int b200vr_wait(b200vr_t* h, b200vr_stats* stats);
 const char* b200vr_last_kernel(const b200vr_t* h);
 /* Tuning switches of a handle; none changes what is computed per sample, they pick between kernels / launch orders that
  * render the same frame (A/B runs, tests of every kernel variant). Defaults come from the environment variable
- * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | ring | legacy | sm),
+ * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | qd6 | qg6 | ring | legacy | sm),
  * "tile_order" (-1 auto, 0 rows, 1 centre-out, 2 previous cost, 3 Z-order, 4 | 5 columns, 6 middle rows first, 7 sheets of the
  * light direction), "sheet_px", "max_ctas_per_sm" (0 = all that fit), "ring_high", "occ_smem" (0 = macrocell occupancy mask
  * read from global memory even when it would fit in shared memory), "carveout" (shared-memory carve-out in percent, -1 =
@@ -255,6 +255,23 @@ int b200vr_current_buffer(b200vr_t* h); /* index of the buffer b200vr_map return
  * for the element type the texture has after CreateArray3DScalarOptix7, array.cpp:322-351). */
 int b200vr_host_camera(const float from[3], const float at[3], const float up[3], float fovy, int width, int height, float out[12]);
 float b200vr_host_integer_normalize(float value, int value_type /* B200VR_TYPE_* */);
+/* Device group: several GPUs of ONE process behind one renderer, split sort-first (the reference is single-device,
+ * device_impl.cpp:370-372 -- this is what a MainRenderer plugin needs to use more than one GPU; the route for device-private
+ * options is MainRenderer::init(argc, argv), ovr/renderer.h:252, as the OSPRay device shows, ospray/device_impl.cpp:419).
+ * b200vr_group_create makes one handle per entry of cuda_devices (the same device may be named twice), gives member i the image
+ * tiles of rank i of n and enables peer access to member 0's GPU. The caller applies every setter (volume, transfer function,
+ * camera, params, resize) to EVERY member (b200vr_group_member); b200vr_group_render enqueues the frame on all members -- each
+ * renders its tiles straight into member 0's current frame buffer over NVLink peer memory -- and waits for all of them; stats
+ * are sums over the members (ms: the slowest member). b200vr_map / b200vr_swap / b200vr_download on member 0 then see the
+ * whole frame. Errors of group calls: b200vr_group_last_error (NULL group: the error of a failed b200vr_group_create). */
+typedef struct b200vr_group b200vr_group_t;
+int b200vr_group_create(b200vr_group_t** out, const int* cuda_devices, int n_devices);
+void b200vr_group_destroy(b200vr_group_t* g);
+int b200vr_group_size(const b200vr_group_t* g);
+b200vr_t* b200vr_group_member(b200vr_group_t* g, int i);
+int b200vr_group_render(b200vr_group_t* g, b200vr_stats* stats_or_null);
+const char* b200vr_group_last_error(const b200vr_group_t* g_or_null);
+
 /* fused sort-first exchange: render the owned tiles straight into these buffers (W*H float4 and W*H*3 float, normally the
  * display rank's frame opened with b200vr_ipc_open) -- the kernel's own pixel stores are the transfer, there is no pack /
  * gather / unpack step. Both NULL: back to the handle's own double buffer. */

@@ -6,7 +6,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "libb200vr.so")
+# B200VR_LIB_PATH: another build of the same library (A/B runs of compile-time tuning constants); the product is the in-tree one
+LIB_PATH = os.environ.get("B200VR_LIB_PATH") or os.path.join(_HERE, "libb200vr.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
               "-Xcompiler", "-fPIC"]
@@ -81,6 +82,12 @@ SYMBOLS = {
     "b200vr_ipc_close": (C.c_int, [_P, _P]),
     "b200vr_current_buffer": (C.c_int, [_P]),
     "b200vr_set_frame_target": (C.c_int, [_P, _P, _P]),
+    "b200vr_group_create": (C.c_int, [C.POINTER(_P), _IP, C.c_int]),
+    "b200vr_group_destroy": (None, [_P]),
+    "b200vr_group_size": (C.c_int, [_P]),
+    "b200vr_group_member": (_P, [_P, C.c_int]),
+    "b200vr_group_render": (C.c_int, [_P, C.POINTER(Stats)]),
+    "b200vr_group_last_error": (C.c_char_p, [_P]),
     "b200vr_copy_device": (C.c_int, [_P, _P, _P, C.c_int64]),
     "b200vr_tile_slice_floats": (C.c_int64, [_P, C.c_int, C.c_int]),
     "b200vr_pack_tiles": (C.c_int, [_P, _P]),

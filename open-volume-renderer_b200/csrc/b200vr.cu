@@ -35,7 +35,8 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_RING, KERNEL_LEGACY, KERNEL_SM };
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
+       KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
 struct Tuning {
@@ -186,13 +187,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -822,6 +823,7 @@ struct KernelChoice {
   int threads;
   size_t smem;
   bool ring = false; // march_ring.cuh: needs the task ring, one launch per sample + resolve_kernel
+  bool cta_sync = false; // march_qc.cuh SYNC: the warps of a CTA take consecutive tiles of the (sheet) launch order and shade in lockstep
   const char* name = "";
 };
 
@@ -838,6 +840,8 @@ struct KernelChoice {
 #define B200VR_K_QC4(a, b, c) raymarch_qc_kernel<a, b, c, 4>
 #define B200VR_K_QC6(a, b, c) raymarch_qc_kernel<a, b, c, 6>
 #define B200VR_K_QC8(a, b, c) raymarch_qc_kernel<a, b, c, 8>
+#define B200VR_K_QG6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 3>
+#define B200VR_K_QD6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 1>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
 #define B200VR_K_NS(a, b, c) raymarch_ns_kernel<a, b, c>
 
@@ -901,6 +905,14 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       else if (force == KERNEL_QC8) {
         k.fn = B200VR_PICK(B200VR_K_QC8, skip, pow2, occs);
         k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel<J=8>";
+      }
+      else if (force == KERNEL_QG6) {
+        k.fn = B200VR_PICK(B200VR_K_QG6, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel<J=6,SYNC=3>", k.cta_sync = true;
+      }
+      else if (force == KERNEL_QD6) {
+        k.fn = B200VR_PICK(B200VR_K_QD6, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel<J=6,SYNC>", k.cta_sync = true;
       }
       else {
         k.fn = B200VR_PICK(B200VR_K_Q, skip, pow2, occs);
@@ -1377,7 +1389,7 @@ static int render_enqueue(b200vr_t* h)
     // the critical path whenever it starts (tools/partition_probe.py), so "expensive first" buys nothing. 7: warp tiles in
     // sheet order (build_sheet_order), for shaded frames of volumes much larger than L2.
     const int n_owned = P.n_warp_tiles / WARP_TILES_PER_SUPER;
-    int order_mode = h->tune.tile_order == TILE_ORDER_AUTO ? TILE_ORDER_ROWS : h->tune.tile_order;
+    int order_mode = h->tune.tile_order == TILE_ORDER_AUTO ? (kc.cta_sync ? TILE_ORDER_SHEET : TILE_ORDER_ROWS) : h->tune.tile_order;
     const bool shaded_march = h->prm.mode == B200VR_MODE_RAYMARCH && h->prm.shading == B200VR_SHADING_REF;
     if (order_mode == TILE_ORDER_SHEET && (!shaded_march || P.sparse_xy)) order_mode = TILE_ORDER_ROWS;
     if (!h->cost_valid) CK(cudaMemsetAsync(h->tile_cost[h->cost_cur ^ 1], 0, (size_t)h->tile_slots * sizeof(unsigned int), h->stream));
@@ -1518,6 +1530,122 @@ extern "C" int b200vr_wait(b200vr_t* h, b200vr_stats* stats)
 {
   if (!h) return B200VR_EINVAL;
   return render_wait(h, stats);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// device group: several GPUs of one process behind one renderer (sort-first). The host layer that the plugin
+// (device/device_b200.cpp) drives when OVR_B200_GPUS / --b200-gpus names more than one device: every member holds the whole
+// scene (the caller applies each setter to every member), owns the image tiles rank i of n (b200vr_set_tile_partition) and
+// renders them STRAIGHT INTO member 0's current frame buffer through a peer mapping -- the kernels' own pixel stores are the
+// transfer over NVLink; map / swap / download then address member 0 alone. One host thread enqueues on all members' streams
+// and waits for all of them, as DeviceOptix7::render waits for its one device (device.cpp:34-43).
+// ---------------------------------------------------------------------------------------------------------------------
+struct b200vr_group {
+  std::vector<b200vr_t*> member;
+  std::string error;
+};
+
+extern "C" int b200vr_group_create(b200vr_group_t** out, const int* cuda_devices, int n_devices)
+{
+  if (!out) return B200VR_EINVAL;
+  *out = nullptr;
+  if (!cuda_devices || n_devices < 1 || n_devices > 64) {
+    g_create_error = "group_create: 1 to 64 devices";
+    return B200VR_EINVAL;
+  }
+  b200vr_group_t* g = new b200vr_group();
+  for (int i = 0; i < n_devices; i++) {
+    b200vr_t* h = nullptr;
+    const int rc = b200vr_create(&h, cuda_devices[i]);
+    if (rc != B200VR_OK) {
+      for (b200vr_t* m : g->member) b200vr_destroy(m);
+      delete g;
+      return rc; // g_create_error was set by b200vr_create
+    }
+    g->member.push_back(h);
+    b200vr_set_tile_partition(h, i, n_devices);
+  }
+  // members 1.. store into member 0's frame: peer access from their device to its device (the same device twice is allowed:
+  // several members on one GPU, which is how a one-GPU box exercises this path)
+  const int dev0 = g->member[0]->device;
+  for (int i = 1; i < n_devices; i++) {
+    const int dev = g->member[i]->device;
+    if (dev == dev0) continue;
+    int can = 0;
+    cudaError_t e = cudaDeviceCanAccessPeer(&can, dev, dev0);
+    if (e == cudaSuccess && can) {
+      e = cudaSetDevice(dev);
+      if (e == cudaSuccess) e = cudaDeviceEnablePeerAccess(dev0, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) e = cudaSuccess, (void)cudaGetLastError();
+    }
+    if (e != cudaSuccess || !can) {
+      g_create_error = "group_create: device " + std::to_string(dev) + " cannot access device " + std::to_string(dev0) +
+                       " as a peer" + (e != cudaSuccess ? std::string(": ") + cudaGetErrorString(e) : std::string());
+      for (b200vr_t* m : g->member) b200vr_destroy(m);
+      delete g;
+      return B200VR_ECUDA;
+    }
+  }
+  *out = g;
+  return B200VR_OK;
+}
+
+extern "C" void b200vr_group_destroy(b200vr_group_t* g)
+{
+  if (!g) return;
+  for (size_t i = g->member.size(); i-- > 0;) b200vr_destroy(g->member[i]); // member 0 (whose frame the others store into) last
+  delete g;
+}
+
+extern "C" int b200vr_group_size(const b200vr_group_t* g) { return g ? (int)g->member.size() : 0; }
+
+extern "C" b200vr_t* b200vr_group_member(b200vr_group_t* g, int i)
+{
+  return g && i >= 0 && i < (int)g->member.size() ? g->member[i] : nullptr;
+}
+
+extern "C" const char* b200vr_group_last_error(const b200vr_group_t* g) { return g ? g->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int b200vr_group_render(b200vr_group_t* g, b200vr_stats* stats)
+{
+  if (!g) return B200VR_EINVAL;
+  const int n = (int)g->member.size();
+  b200vr_t* h0 = g->member[0];
+  if (h0->width <= 0 || h0->height <= 0) {
+    g->error = "group_render: framebuffer size not set";
+    return B200VR_ESTATE;
+  }
+  for (int i = 1; i < n; i++) {
+    b200vr_t* h = g->member[i];
+    if (h->width != h0->width || h->height != h0->height) {
+      g->error = "group_render: members have different framebuffer sizes (apply every setter to every member)";
+      return B200VR_ESTATE;
+    }
+    // not through b200vr_set_frame_target: the target flips with every swap of member 0, which is no reason to restart a
+    // progressive accumulation (the sums live in the member's own accum buffer)
+    h->target_rgba = h0->rgba[h0->current];
+    h->target_grad = h0->grad[h0->current];
+  }
+  int rc = B200VR_OK;
+  int enq = 0;
+  for (; enq < n && rc == B200VR_OK; enq++) {
+    rc = render_enqueue(g->member[enq]);
+    if (rc != B200VR_OK) g->error = "member " + std::to_string(enq) + ": " + g->member[enq]->error;
+  }
+  b200vr_stats sum;
+  std::memset(&sum, 0, sizeof(sum));
+  for (int i = 0; i < n; i++) { // every member that has a frame in flight is waited for, also after an error
+    b200vr_stats st;
+    std::memset(&st, 0, sizeof(st));
+    const int rw = render_wait(g->member[i], &st);
+    if (rw != B200VR_OK && rc == B200VR_OK) rc = rw, g->error = "member " + std::to_string(i) + ": " + g->member[i]->error;
+    sum.ms = std::max(sum.ms, st.ms);
+    sum.primary_samples += st.primary_samples, sum.shadow_samples += st.shadow_samples, sum.gradient_fetches += st.gradient_fetches;
+    sum.delta_samples += st.delta_samples, sum.rays += st.rays, sum.kernel_launches += st.kernel_launches;
+    sum.frame_index = st.frame_index;
+  }
+  if (stats) *stats = sum;
+  return rc;
 }
 
 extern "C" const char* b200vr_last_kernel(const b200vr_t* h) { return h ? h->last_kernel.c_str() : ""; }

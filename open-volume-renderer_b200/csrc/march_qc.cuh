@@ -31,11 +31,25 @@ constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
 // slot layout (32 bytes): [0] p.x  [4] p.y  [8] p.z  [12] s  [16] w  [20] log2-transmittance of an off-lattice task  [24] [28] -
 // after shading:          [0] C.x  [4] C.y  [8] C.z  [12] G.x [16] G.y [20] G.z
 
-template<bool SKIP, bool POW2, bool OCCS, int J>
+// SYNC != 0 -- an experiment that LOST, kept selectable for the record (profiles/r2k_*). The eight warps of
+// a CTA take eight CONSECUTIVE warp tiles of the launch order -- in sheet order (build.cuh sheet_key_kernel) a strip of tiles along
+// the screen projection of the light direction -- so that the shadow samples of step k of the eight tiles form one block of the
+// volume that slides along the strip by one shadow step (10 voxels) per iteration: what a warp fetches at step k, a neighbour
+// fetched at step k - 1. Without it every L1 miss of a shadow fetch goes to DRAM (profiles/r2h_ncu_full_raymarch_qc6_C3.txt: 753 M
+// sector misses from L1, 620 M sectors read from DRAM).
+//   SYNC = 1 (option qd6): passes start together and the shadow lattice is walked in CTA-wide lockstep, one barrier per step;
+//   SYNC = 3 (option qg6): only the tile groups start together, no barrier inside a group.
+// Measured on C3 against 6.16 ms / 19.8 GB read from DRAM for the unsynchronised kernel: 14.9 ms / 13.0 GB (SYNC 1), 12.3 ms /
+// 12.4 GB (barrier per pass only), 7.7 ms / 9.7 GB (SYNC 3). The traffic does fall -- by half with nothing but a common start -- and
+// the frame gets slower every time: at 3.2 of 6.5 TB/s the kernel is not waiting for DRAM bandwidth but for latency, and every
+// barrier takes independent warps away from the four a scheduler has. Which warp shades which task and the order of every sum are
+// unchanged: frames are bit-identical to the other queue kernels (test_every_shading_kernel_variant_matches_the_oracle).
+template<bool SKIP, bool POW2, bool OCCS, int J, int SYNC = 0>
 __global__ void __launch_bounds__(QC_THREADS, QC_MIN_CTAS)
 raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 {
   extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ int s_tile_base;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float2* const s_apair = reinterpret_cast<float2*>(smem);
   unsigned int* const s_occ = reinterpret_cast<unsigned int*>(smem + q_alpha_bytes(P.n_alpha));
@@ -58,13 +72,26 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 
   for (;;) {
     int k = 0;
-    if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
-    k = __shfl_sync(0xffffffffu, k, 0);
-    if (k >= P.n_warp_tiles) break;
+    bool have_tile = true;
+    if (SYNC) {
+      __syncthreads(); // every warp has left the previous group (s_tile_base may be overwritten)
+      if (threadIdx.x == 0) s_tile_base = (int)atomicAdd(P.tile_counter, (unsigned int)(QC_THREADS / 32));
+      __syncthreads();
+      const int base = s_tile_base;
+      if (base >= P.n_warp_tiles) break; // CTA-uniform
+      k = base + warp;
+      have_tile = k < P.n_warp_tiles;    // the last group may be short: its spare warps only take part in the barriers
+      k = min(k, P.n_warp_tiles - 1);
+    }
+    else {
+      if (lane == 0) k = (int)atomicAdd(P.tile_counter, 1u);
+      k = __shfl_sync(0xffffffffu, k, 0);
+      if (k >= P.n_warp_tiles) break;
+    }
     int ix, iy;
     const int tile_slot = warp_tile_pixel(P, k, lane, ix, iy);
     const long long tile_t0 = clock64();
-    const bool inside = ix < P.width && iy < P.height;
+    const bool inside = have_tile && ix < P.width && iy < P.height;
     const unsigned int pixel_index = (unsigned)ix + (unsigned)iy * (unsigned)P.width;
 
     for (int sidx = 0; sidx < P.spp; sidx++) {
@@ -97,7 +124,14 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 
       for (;;) {
         const bool any_alive = __any_sync(0xffffffffu, alive);
-        if (count >= J * 32 || (!any_alive && count > 0)) {
+        if (count >= J * 32 || !any_alive) {
+          // a warp arrives here with a full queue or with all its rays finished
+          if (SYNC == 1 || SYNC == 2) {
+            // all warps of the CTA start their passes together; a warp without tasks goes through the pass for its barriers
+            // only, and the tile group ends when no warp has anything left
+            if (!__syncthreads_or(count > 0)) break;
+          }
+          else if (count == 0) break;
           // =================== shading pass: lane takes tasks lane, lane + 32, ... ===================
           const int n = min(count, J * 32);
           __syncwarp();
@@ -147,19 +181,21 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
             float sv0[J], sv1[J];
             unsigned int f0, f1;
             issue(stx, sty, live, sv0, f0);
-            while (live != 0u) {
+            // one lattice step: the fetches of the NEXT interval go out (into `nxt`), then the current one (`cur`, issued one
+            // step earlier) is classified
+            auto lattice_step = [&](float (&cur)[J], unsigned int fcur, float (&nxt)[J], unsigned int& fnxt) {
               const float nsty = sty + P.sstep;
               unsigned int geo = 0u; // tasks whose ray has a next interval [sty, min(st1, nsty)]
 #pragma unroll
               for (int j = 0; j < J; j++) geo |= fminf(st1[j], nsty) > sty ? (1u << j) : 0u;
               geo &= live;
-              issue(sty, nsty, geo, sv1, f1); // in flight while the current step is classified; unused if the ray ends here
-              const unsigned int cls = live & f0;
+              issue(sty, nsty, geo, nxt, fnxt); // in flight while the current step is classified; unused if the ray ends here
+              const unsigned int cls = live & fcur;
               c_shadow += (unsigned int)__popc(cls);
               unsigned int ert = 0u;
 #pragma unroll
               for (int j = 0; j < J; j++) {
-                const float a = alpha_lookup<POW2>(P, apair_base, sv0[j]);
+                const float a = alpha_lookup<POW2>(P, apair_base, cur[j]);
                 // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
                 const float v = __fmaf_rn(P.base * (fminf(st1[j], sty) - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog[j]);
                 slog[j] = ((cls >> j) & 1u) ? v : slog[j];
@@ -167,9 +203,18 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               }
               live = geo & ert;
               stx = sty, sty = nsty;
-              f0 = f1;
-#pragma unroll
-              for (int j = 0; j < J; j++) sv0[j] = sv1[j];
+            };
+            // SYNC == 1: one CTA barrier per lattice step, as many steps as the CTA's longest ray needs; a warp whose rays have
+            // all ended skips the body (live stays 0)
+            auto more = [&]() { return SYNC == 1 ? (__syncthreads_or(live != 0u) != 0) : (live != 0u); };
+            // The loop is unrolled by two so that the two value arrays swap ROLES instead of contents: with `sv0 = sv1` at the end
+            // of a step the moves waited for the fetches issued at the top of the same step (profiles/r2h: 20 % of all stall
+            // samples sat on those MOVs), which made the pipeline one step shallower than written.
+            for (;;) {
+              if (!more()) break;
+              if (!(SYNC == 1 && live == 0u)) lattice_step(sv0, f0, sv1, f1);
+              if (!more()) break;
+              if (!(SYNC == 1 && live == 0u)) lattice_step(sv1, f1, sv0, f0);
             }
           }
           // ---- C. tasks off the shared lattice, one at a time (rare): result through the task's slot ----
@@ -266,7 +311,6 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
           count = rest;
           continue;
         }
-        if (!any_alive) break;
 
         // =================== one primary sample per live ray (raymarching, shaders_raymarching.cu:87-171) ===================
         bool want = false;
@@ -304,7 +348,10 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
             if (have_pre) s = s_pre;
             else s = tex3D<float>(P.tex, p.x, p.y, p.z);
             {
-              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
+              // (Measured and rejected on C3 / C2: batches of four -- this sample and the next three fetched together, consumed
+              // over the following steps -- 6.41 vs 6.14 ms / 2.47 vs 2.28 ms: the speculative fetches past early termination and
+              // cell exits cost more than the waits they save.)
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
@@ -375,7 +422,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
         g[2] = G.z;
       }
     }
-    if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
+    if (lane == 0 && have_tile) tile_cost_add(P, tile_slot, tile_t0);
   }
 
   // executed-sample counters: one atomic set per warp

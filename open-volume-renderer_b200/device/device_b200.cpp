@@ -8,6 +8,7 @@
 
 #include <ovr/common/dylink/ObjectFactory.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -42,11 +43,39 @@ env_int(const char* name, int fallback)
   return v ? std::atoi(v) : fallback;
 }
 
+// "0,1,2,3" or "4" (= devices 0..3) -> CUDA device indices; empty / unparsable -> {fallback}
+std::vector<int>
+parse_devices(const std::string& text, int fallback)
+{
+  std::vector<int> out;
+  if (text.find(',') == std::string::npos) {
+    const int n = text.empty() ? 0 : std::atoi(text.c_str());
+    if (n > 1) {
+      for (int i = 0; i < n; i++) out.push_back(i);
+      return out;
+    }
+    return { fallback };
+  }
+  size_t pos = 0;
+  while (pos <= text.size()) {
+    const size_t end = std::min(text.find(',', pos), text.size());
+    if (end > pos) out.push_back(std::atoi(text.substr(pos, end - pos).c_str()));
+    pos = end + 1;
+  }
+  if (out.empty()) out.push_back(fallback);
+  return out;
+}
+
 } // namespace
 
 struct DeviceB200::Impl {
   DeviceB200* parent = nullptr;
-  b200vr_t* handle = nullptr;
+  // One handle of the C ABI per GPU. With several GPUs (OVR_B200_GPUS / --b200-gpus) they form a b200vr group: every setter
+  // goes to every member, the frame is split sort-first and assembled in member 0's buffers over NVLink (include/b200vr.h).
+  b200vr_group_t* group = nullptr;
+  std::vector<b200vr_t*> members;
+  b200vr_t* handle = nullptr; // members[0]: the display GPU (map / swap / download)
+  std::vector<int> devices;
   b200vr_params prm;
   bool initialized = false;
   bool prm_dirty = false;
@@ -61,7 +90,17 @@ struct DeviceB200::Impl {
 
   ~Impl()
   {
-    if (handle) b200vr_destroy(handle);
+    if (group) b200vr_group_destroy(group);
+  }
+
+  // applies one C-ABI setter to every member of the group
+  template<typename F>
+  void each(const char* what, F&& call) const
+  {
+    for (b200vr_t* m : members) {
+      const int rc = call(m);
+      if (rc != B200VR_OK) throw std::runtime_error(std::string("b200: ") + what + ": " + b200vr_last_error(m));
+    }
   }
 
   void check(int rc, const char* what) const
@@ -70,12 +109,25 @@ struct DeviceB200::Impl {
       throw std::runtime_error(std::string("b200: ") + what + ": " + b200vr_last_error(handle));
   }
 
-  void init(DeviceB200* p)
+  // Device-private options arrive the way the reference passes them to its devices: the raw command line handed to
+  // MainRenderer::init (ovr/renderer.h:252; the OSPRay device forwards it to ospInit, ospray/device_impl.cpp:419).
+  // --b200-gpus <n | i,j,k> (or OVR_B200_GPUS, which wins when the host program rejects unknown flags): the GPUs to render on.
+  void init(DeviceB200* p, int argc, const char** argv)
   {
     if (initialized) throw std::runtime_error("b200: device already initialized!"); // device_impl.cpp:73-75
     parent = p;
-    const int rc = b200vr_create(&handle, env_int("OVR_B200_CUDA_DEVICE", 0));
-    if (rc != B200VR_OK) throw std::runtime_error(std::string("b200: cannot create device: ") + b200vr_last_error(nullptr));
+    std::string gpus;
+    for (int i = 1; argv && i < argc; i++) {
+      const std::string a = argv[i] ? argv[i] : "";
+      if (a == "--b200-gpus" && i + 1 < argc && argv[i + 1]) gpus = argv[i + 1];
+      else if (a.rfind("--b200-gpus=", 0) == 0) gpus = a.substr(12);
+    }
+    if (const char* e = std::getenv("OVR_B200_GPUS")) gpus = e;
+    devices = parse_devices(gpus, env_int("OVR_B200_CUDA_DEVICE", 0));
+    const int rc = b200vr_group_create(&group, devices.data(), (int)devices.size());
+    if (rc != B200VR_OK) throw std::runtime_error(std::string("b200: cannot create device: ") + b200vr_group_last_error(nullptr));
+    for (int i = 0; i < b200vr_group_size(group); i++) members.push_back(b200vr_group_member(group, i));
+    handle = members[0];
     b200vr_default_params(&prm);
     // device-private switches that MainRenderer has no setter for (they default to the reference's behaviour)
     prm.shading = env_int("OVR_B200_SHADING", B200VR_SHADING_REF);
@@ -93,9 +145,10 @@ struct DeviceB200::Impl {
     const vec3f scale = v.grid_spacing * vec3f(v.data->dims);
     const vec3f translate = v.grid_origin;
     const float otw[12] = { scale.x, 0.f, 0.f, translate.x, 0.f, scale.y, 0.f, translate.y, 0.f, 0.f, scale.z, translate.z };
-    check(b200vr_set_volume(handle, v.data->data(), to_b200vr_type(v.data->type), v.data->dims.x, v.data->dims.y,
-                            v.data->dims.z, otw, /*on_device=*/0),
-          "set_volume");
+    each("set_volume", [&](b200vr_t* m) {
+      return b200vr_set_volume(m, v.data->data(), to_b200vr_type(v.data->type), v.data->dims.x, v.data->dims.y, v.data->dims.z, otw,
+                               /*on_device=*/0);
+    });
     prm.sampling_rate = scene.volume_sampling_rate;
     prm_dirty = true;
   }
@@ -119,7 +172,7 @@ struct DeviceB200::Impl {
     while ((size_t)(tile + 1) * (tile + 1) * 64 <= table.size()) tile++;
     if (tile == 0 || (size_t)tile * tile * 64 != table.size())
       throw std::runtime_error(std::string("b200: noise table is not tile x tile x 64 floats: ") + path);
-    check(b200vr_set_sparse_noise(handle, table.data(), tile, 64), "set_sparse_noise");
+    each("set_sparse_noise", [&](b200vr_t* m) { return b200vr_set_sparse_noise(m, table.data(), tile, 64); });
   }
 
   void swap() { check(b200vr_swap(handle), "swap"); }
@@ -132,20 +185,21 @@ struct DeviceB200::Impl {
     bool size_changed = false;
     if (pp.fbsize.update()) {
       fbsize = pp.fbsize.ref();
-      if (fbsize.x > 0 && fbsize.y > 0) check(b200vr_resize(handle, fbsize.x, fbsize.y), "resize");
+      if (fbsize.x > 0 && fbsize.y > 0) each("resize", [&](b200vr_t* m) { return b200vr_resize(m, fbsize.x, fbsize.y); });
       size_changed = true;
     }
     if (pp.camera.update() || size_changed) {
       const Camera& c = pp.camera.ref();
       const float from[3] = { c.from.x, c.from.y, c.from.z }, at[3] = { c.at.x, c.at.y, c.at.z }, up[3] = { c.up.x, c.up.y, c.up.z };
-      check(b200vr_set_camera_lookat(handle, from, at, up, c.perspective.fovy), "set_camera");
+      each("set_camera", [&](b200vr_t* m) { return b200vr_set_camera_lookat(m, from, at, up, c.perspective.fovy); });
     }
     if (pp.tfn.update()) {
       const auto& t = pp.tfn.ref();
       if (!t.tfn_colors.empty() && !t.tfn_alphas.empty())
-        check(b200vr_set_transfer_function(handle, t.tfn_colors.data(), (int)(t.tfn_colors.size() / 3), t.tfn_alphas.data(),
-                                           (int)(t.tfn_alphas.size() / 2), t.tfn_value_range.x, t.tfn_value_range.y),
-              "set_transfer_function");
+        each("set_transfer_function", [&](b200vr_t* m) {
+          return b200vr_set_transfer_function(m, t.tfn_colors.data(), (int)(t.tfn_colors.size() / 3), t.tfn_alphas.data(),
+                                              (int)(t.tfn_alphas.size() / 2), t.tfn_value_range.x, t.tfn_value_range.y);
+        });
     }
     if (pp.sample_per_pixel.update()) {
       prm.spp = pp.sample_per_pixel.ref();
@@ -173,10 +227,12 @@ struct DeviceB200::Impl {
     if (sparse_dirty) {
       if (sparse_sampling && !noise_loaded) load_noise_table();
       const float fc[2] = { focus_center.x, focus_center.y };
-      check(b200vr_set_sparse_sampling(handle, sparse_sampling ? 1 : 0, fc, focus_scale, base_noise), "set_sparse_sampling");
+      if (sparse_sampling && members.size() > 1)
+        throw std::runtime_error("b200: sparse sampling is a single-device mode (the reference's too): run with one GPU");
+      each("set_sparse_sampling", [&](b200vr_t* m) { return b200vr_set_sparse_sampling(m, sparse_sampling ? 1 : 0, fc, focus_scale, base_noise); });
     }
     if (prm_dirty) {
-      check(b200vr_set_params(handle, &prm), "set_params");
+      each("set_params", [&](b200vr_t* m) { return b200vr_set_params(m, &prm); });
       prm_dirty = false;
     }
   }
@@ -184,7 +240,14 @@ struct DeviceB200::Impl {
   void render()
   {
     if (fbsize.x <= 0 || fbsize.y <= 0) return; // device_impl.cpp:215-216
-    check(b200vr_render(handle, nullptr), "render"); // synchronous, like DeviceOptix7::render (device.cpp:34-43)
+    // synchronous, like DeviceOptix7::render (device.cpp:34-43); with several GPUs every member renders its image tiles
+    // straight into member 0's frame (b200vr_group_render)
+    if (members.size() > 1) {
+      if (b200vr_group_render(group, nullptr) != B200VR_OK)
+        throw std::runtime_error(std::string("b200: render: ") + b200vr_group_last_error(group));
+    }
+    else
+      check(b200vr_render(handle, nullptr), "render");
     parent->variance = 0.f;                          // device_impl.cpp:266
   }
 
@@ -214,9 +277,9 @@ DeviceB200::~DeviceB200()
 DeviceB200::DeviceB200() : MainRenderer(), pimpl(new Impl()) {}
 
 void
-DeviceB200::init(int /*argc*/, const char** /*argv*/)
+DeviceB200::init(int argc, const char** argv)
 {
-  pimpl->init(this);
+  pimpl->init(this, argc, argv);
   pimpl->commit();
 }
 

@@ -57,8 +57,8 @@ def build(force=False):
             "ovr_oracle.h")
     if force or _stale(so, srcs):
         subprocess.run(["make", "-C", _HERE, "liboracle.so"], check=True, capture_output=True)
-    refs = ("libovr_ref_kat.so", "libovr_ref_tfn.so", "libovr_ref_march.so")
-    ref_srcs = ("ref_shim.cpp", "ref_tfn_shim.cpp", "ref_march_shim.cpp", "extract_march.py", "Makefile", "liboracle.so")
+    refs = ("libovr_ref_kat.so", "libovr_ref_tfn.so", "libovr_ref_march.so", "libovr_ref_majorant.so")
+    ref_srcs = ("ref_shim.cpp", "ref_tfn_shim.cpp", "ref_march_shim.cpp", "ref_majorant_shim.cu", "extract_march.py", "Makefile", "liboracle.so")
     if os.path.isdir("/root/reference/ovr") and (force or any(_stale(os.path.join(_HERE, "_ref", r), ref_srcs) for r in refs)):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
     build_scenedump(force)
@@ -96,6 +96,17 @@ def lib():
         L.ovr_oracle_clip.restype = C.c_int
         _LIB = L
     return _LIB
+
+
+def ref_majorant_lib():
+    """The reference's majorant_kernel compiled for the GPU (oracle/ref_majorant_shim.cu); None where oracle/_ref was not built."""
+    so = os.path.join(_HERE, "_ref", "libovr_ref_majorant.so")
+    if not os.path.exists(so):
+        return None
+    L = C.CDLL(so)
+    L.ref_majorant_kernel_run.restype = C.c_int
+    L.ref_majorant_kernel_run.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_float, C.c_float, C.c_void_p]
+    return L
 
 
 def ref_kat_lib():

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/b200vr.h but not exported"
     assert sorted(capi.SYMBOLS) == names, "ctypes table and header drifted apart"
-    assert capi.lib().b200vr_abi_version() == 3
+    assert capi.lib().b200vr_abi_version() == 4
 
 
 def test_struct_layouts_match_header():
