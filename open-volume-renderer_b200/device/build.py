@@ -97,5 +97,33 @@ def build(force=False):
     return exe
 
 
+def build_c1_fixture():
+    """BASELINE.json configs[0] literally: a scratch copy of the reference's data/configs directory entry scene_vorts1.json
+    (copied at build time into the git-ignored build/ovr/c1/, never into the repository) next to a SYNTHESISED payload
+    data/data/vorts1.data -- the reference ships the scene description but not the 8 MiB volume it names. The
+    payload is a smooth analytic field of the file's dimensions (128^3 fp32) spanning the scene's scalarMappingRange."""
+    src = os.path.join(REF, "data", "configs", "scene_vorts1.json")
+    if not os.path.exists(src):
+        return None
+    import shutil
+    import numpy as np
+    root = os.path.join(OUT, "c1")
+    os.makedirs(os.path.join(root, "data", "configs"), exist_ok=True)
+    os.makedirs(os.path.join(root, "data", "data"), exist_ok=True)
+    shutil.copyfile(src, os.path.join(root, "data", "configs", "scene_vorts1.json"))
+    payload = os.path.join(root, "data", "data", "vorts1.data")
+    if not os.path.exists(payload):
+        n = 128
+        g = np.linspace(0.0, 1.0, n, dtype=np.float64)
+        z, y, x = np.meshgrid(g, g, g, indexing="ij")
+        f = (np.sin(6.3 * x + 1.0) * np.cos(4.1 * y) + np.sin(5.2 * z + 2.0 * x) * np.cos(3.3 * y * z + 0.5) +
+             0.7 * np.cos(9.0 * (x - 0.5) * (y - 0.5)) * np.sin(7.0 * z))
+        f = (f - f.min()) / (f.max() - f.min())
+        lo, hi = 0.0070086014457046986, 12.139389038085938   # scalarMappingRange of the scene file
+        (lo + (hi - lo) * f ** 3).astype("<f4").tofile(payload)   # cubed: most of the volume stays in the transparent foot of the TF
+    return root
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(build_c1_fixture())
