@@ -424,11 +424,17 @@ def run_b200(args):
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+    per_rank_kernel = None
+    if world > 1:   # every rank's own kernel time: tells load imbalance between the ranks from a common floor (the heaviest tile)
+        mine = torch.tensor([kernel_ms], dtype=torch.float64, device="cuda")
+        allk = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allk, mine)
+        per_rank_kernel = [float(k.item()) / (args.steps * F) for k in allk]
     t_ms, samples, fetches, kernel_ms = float(t_ms.item()), float(tot[0].item()), float(tot[1].item()), float(kms.item())
     value = samples / (t_ms * 1e-3) / 1e6
     return dict(r=r, wl=wl, scene=full_scene if sortlast else scene, value=value, t_ms=t_ms, samples=samples, fetches=fetches, kernel_ms=kernel_ms, clk=clk,
                 gpu_launches=gpu_launches, step=step, barrier=barrier, stream=stream, world=world, rank=rank, local_rank=local_rank,
-                F=F, frames=args.steps * F, kernel=r.last_kernel)
+                F=F, frames=args.steps * F, kernel=r.last_kernel, per_rank_kernel=per_rank_kernel)
 
 
 def run_e2e(ctx, args):
@@ -512,7 +518,7 @@ def run_e2e(ctx, args):
 
 
 KERNEL_OPTION = {"raymarch_q_kernel": "q", "raymarch_ring_kernel": "ring", "raymarch_qc_kernel<J=4>": "qc4", "raymarch_qc_kernel<J=6>": "qc6",
-                 "raymarch_qc_kernel<J=8>": "qc8"}
+                 "raymarch_qc_kernel<J=8>": "qc8", "raymarch_qc_kernel<J=6,AHEAD=3>": "qa6"}
 
 
 def parity_march(rgba, grad, pix):
@@ -696,18 +702,19 @@ def run_sort_last_record(args, ctx):
         for _ in range(warm):
             fn()
         barrier()
-        samples = 0
+        samples, own_ms = 0, 0.0
         ev0.record(stream)
         for _ in range(frames):
             fn()
             samples += b.last_stats["primary_samples"]
+            own_ms += b.last_stats["ms"]
         ev1.record(stream)
         barrier()
         t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
-        s = torch.tensor([samples], dtype=torch.float64, device="cuda")
+        s = torch.tensor([samples, own_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
-        return float(t.item()) / frames, float(s.item()) / frames
+        return float(t.item()) / frames, float(s[0].item()) / frames, float(s[1].item()) / frames
 
     def f_march():
         b.render()
@@ -722,9 +729,9 @@ def run_sort_last_record(args, ctx):
         b.render()
         ex.composite_direct(eye)
 
-    ms_march, samples = timed(f_march)
-    ms_swap, _ = timed(f_swap)
-    ms_direct, _ = timed(f_direct)
+    ms_march, samples, seq_ms = timed(f_march)   # seq_ms: sum over the ranks of their own march-kernel time per frame
+    ms_swap, _, _ = timed(f_swap)
+    ms_direct, _, _ = timed(f_direct)
     # one brick alone on one GPU: the same voxels as a whole volume of their own, framed by the same camera preset
     b._ck(L.b200vr_set_brick(b.handle, None, None, None, None))
     b.premultiplied = False
@@ -763,10 +770,12 @@ def run_sort_last_record(args, ctx):
                         "rounds": 1, "launches_per_rank": 1, "barriers": 2},
         "one_brick_one_gpu": {"ms_per_frame": t1, "samples_per_frame": s1, "msamples_s": s1 / t1 / 1e3,
                               "what": "rank 0's brick as a volume of its own, same camera preset, same kernel"},
-        "weak_scaling": {"speedup_msamples": (samples / best / 1e3) / (s1 / t1 / 1e3) if t1 > 0 and s1 > 0 else None,
-                         "efficiency": ((samples / best / 1e3) / (s1 / t1 / 1e3) / world) if t1 > 0 and s1 > 0 else None,
-                         "frame_time_ratio_one_brick_over_n": t1 / best if best > 0 else None,
-                         "note": "throughput of N GPUs on N bricks over one GPU on one brick (executed Msamples/s); north_star: >= 6x at 8"},
+        "weak_scaling": {"one_gpu_sequential_ms": seq_ms, "speedup": seq_ms / best if best > 0 else None,
+                         "efficiency": seq_ms / best / world if best > 0 else None,
+                         "note": "the volume does not fit on one GPU, so the one-GPU time is what one GPU with enough memory would need to march "
+                                 "the same N bricks one after the other (sum over the ranks of their own march-kernel time, compositing "
+                                 "excluded), over the N-GPU frame time including the exchange; north_star: >= 6x at 8. one_brick_one_gpu is "
+                                 "the other view: a brick as a volume of its own filling the frame (more pixels hit, more samples)"},
     })
     return rec
 
@@ -846,6 +855,8 @@ def main():
                            "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                            "samples_per_frame": ctx["samples"] / n_frames, "fetches_per_frame": ctx["fetches"] / n_frames},
                 "clocks": ctx["clk"], "e2e": e2e, "gpu_launches": ctx["gpu_launches"], "roofline": roofline}
+        if ctx["per_rank_kernel"] is not None:
+            roofline["kernel_ms_per_launch_by_rank"] = ctx["per_rank_kernel"]
         if sf_rec is not None:
             line["sort_first_check"] = sf_rec
         parity_frame = None

@@ -35,7 +35,7 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QA6, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
        KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
@@ -187,13 +187,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qa6", KERNEL_QA6 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qa6, qd6, qg6, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -834,12 +834,14 @@ struct KernelChoice {
    : (occs) ? ((pow2) ? KERNEL(true, true, true) : KERNEL(true, false, true))                                                     \
             : ((pow2) ? KERNEL(true, true, false) : KERNEL(true, false, false)))
 #define B200VR_K_Q(a, b, c) raymarch_q_kernel<a, b, c>
+#define B200VR_K_QM(a, b, c) raymarch_q_kernel<a, b, c, SAMPLER_MANUAL>
 #define B200VR_K_QB2(a, b, c) raymarch_qb_kernel<a, b, c, 2>
 #define B200VR_K_QB4(a, b, c) raymarch_qb_kernel<a, b, c, 4>
 #define B200VR_K_QB8(a, b, c) raymarch_qb_kernel<a, b, c, 8>
 #define B200VR_K_QC4(a, b, c) raymarch_qc_kernel<a, b, c, 4>
 #define B200VR_K_QC6(a, b, c) raymarch_qc_kernel<a, b, c, 6>
 #define B200VR_K_QC8(a, b, c) raymarch_qc_kernel<a, b, c, 8>
+#define B200VR_K_QA6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 0, 3>
 #define B200VR_K_QG6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 3>
 #define B200VR_K_QD6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 1>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
@@ -869,6 +871,16 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   if (p.mode == B200VR_MODE_PATHTRACE) {
     k.fn = p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
     k.name = "pathtrace_kernel";
+    return k;
+  }
+  if (p.sampler == B200VR_SAMPLER_MANUAL && !legacy && !sm && p.shading == B200VR_SHADING_REF) {
+    // the software sampler (eight global loads + the unit's integer weights, sampling.cuh) inside the current queue kernel: the
+    // like-for-like side of the tex3D-versus-manual comparison; sort-first partitions included
+    const bool pow2 = (h->n_alpha & (h->n_alpha - 1)) == 0 && h->n_alpha >= 2 && h->n_alpha <= 4096;
+    const bool occs = p.skip_empty && h->tune.occ_smem != 0 && q_occ_in_smem(h->occ_words);
+    k.fn = B200VR_PICK(B200VR_K_QM, p.skip_empty != 0, pow2, occs);
+    k.threads = Q_THREADS, k.smem = q_alpha_bytes(h->n_alpha) + (occs ? q_occ_bytes(h->occ_words) : 0) + q_queue_bytes();
+    k.name = "raymarch_q_kernel<SAMPLER_MANUAL>";
     return k;
   }
   if (p.sampler == B200VR_SAMPLER_TEX3D && !legacy) {
@@ -905,6 +917,10 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       else if (force == KERNEL_QC8) {
         k.fn = B200VR_PICK(B200VR_K_QC8, skip, pow2, occs);
         k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel<J=8>";
+      }
+      else if (force == KERNEL_QA6) {
+        k.fn = B200VR_PICK(B200VR_K_QA6, skip, pow2, occs);
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel<J=6,AHEAD=3>";
       }
       else if (force == KERNEL_QG6) {
         k.fn = B200VR_PICK(B200VR_K_QG6, skip, pow2, occs);

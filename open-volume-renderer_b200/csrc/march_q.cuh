@@ -164,10 +164,20 @@ __device__ __forceinline__ f3 color_global(const LaunchParams& P, float s)
   return mk3(__fmaf_rn(w, c1.x - c0.x, c0.x), __fmaf_rn(w, c1.y - c0.y, c0.y), __fmaf_rn(w, c1.z - c0.z, c0.z));
 }
 
+// One trilinear fetch through the unit (the default everywhere) or through the software filter of sampling.cuh (eight global
+// loads from the linear copy of the volume, integer weights as the unit applies them): the same queue kernel with either sampler
+// is what the tex3D-versus-manual comparison of DESIGN.md section 5.6 runs (ncu captures under profiles/).
+template<int SAMPLER>
+__device__ __forceinline__ float fetch3(const LaunchParams& P, float x, float y, float z)
+{
+  if (SAMPLER == SAMPLER_TEX3D) return tex3D<float>(P.tex, x, y, z);
+  return sample_volume<SAMPLER_MANUAL>(P, mk3(x, y, z));
+}
+
 // Shading of one deferred sample (position p in object space, scalar s, compositing weight w): colour lookup, forward-
 // difference gradient, shadow march toward the light, Phong-less "0.5 + cos * transmittance" shading of the reference
 // (shaders_raymarching.cu:126-169, 205-229, 44-85). Returns the colour and normal-layer contributions of the sample.
-template<bool SKIP, bool POW2, bool OCCS>
+template<bool SKIP, bool POW2, bool OCCS, int SAMPLER = SAMPLER_TEX3D>
 __device__ __forceinline__ void shade_task(const LaunchParams& P, unsigned int apair_base, unsigned int occ_base, f3 p, float s, float w,
                                            unsigned int& c_shaded, unsigned int& c_shadow, f3& cC, f3& cG)
 {
@@ -177,9 +187,9 @@ __device__ __forceinline__ void shade_task(const LaunchParams& P, unsigned int a
   if (p.x + stp.x > 1.f) stp.x = -stp.x;
   if (p.y + stp.y > 1.f) stp.y = -stp.y;
   if (p.z + stp.z > 1.f) stp.z = -stp.z;
-  const float gx = tex3D<float>(P.tex, p.x + stp.x, p.y, p.z) - s;
-  const float gy = tex3D<float>(P.tex, p.x, p.y + stp.y, p.z) - s;
-  const float gz = tex3D<float>(P.tex, p.x, p.y, p.z + stp.z) - s;
+  const float gx = fetch3<SAMPLER>(P, p.x + stp.x, p.y, p.z) - s;
+  const float gy = fetch3<SAMPLER>(P, p.x, p.y + stp.y, p.z) - s;
+  const float gz = fetch3<SAMPLER>(P, p.x, p.y, p.z + stp.z) - s;
   c_shaded++;
   // shadow ray from the sample toward the light (__closesthit__volume_shadow + raymarching_shadow,
   // shaders_raymarching.cu:205-229,44-85), transmittance accumulated as a sum of logs
@@ -196,7 +206,7 @@ __device__ __forceinline__ void shade_task(const LaunchParams& P, unsigned int a
                                                                __fmaf_rn(tm, P.sh_d.z, p.z))));
     };
     auto fetch = [&](float tm) {
-      return tex3D<float>(P.tex, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
+      return fetch3<SAMPLER>(P, __fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
     };
     auto classify = [&](float sv, float dt) {
       c_shadow++;
@@ -240,7 +250,7 @@ __device__ __forceinline__ void shade_task(const LaunchParams& P, unsigned int a
   cG = clamp01(normal_c) * w;
 }
 
-template<bool SKIP, bool POW2, bool OCCS>
+template<bool SKIP, bool POW2, bool OCCS, int SAMPLER = SAMPLER_TEX3D>
 __global__ void __launch_bounds__(Q_THREADS, Q_MIN_CTAS)
 raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 {
@@ -316,7 +326,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
             const float4 q0 = lds_f32x4(queue_base + 32u * (unsigned)(lane)), q1 = lds_f32x4(queue_base + 32u * (unsigned)(lane) + 16u);
             const f3 p = mk3(q0.x, q0.y, q0.z);
             const float s = q0.w, w = q1.x;
-            shade_task<SKIP, POW2, OCCS>(P, apair_base, occ_base, p, s, w, c_shaded, c_shadow, cC, cG);
+            shade_task<SKIP, POW2, OCCS, SAMPLER>(P, apair_base, occ_base, p, s, w, c_shaded, c_shadow, cC, cG);
           }
           __syncwarp();
           if (lane < n) {
@@ -385,13 +395,13 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
 #endif
             float s;
             if (B200VR_Q_PRIMARY_PREFETCH && have_pre) s = s_pre;
-            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+            else s = fetch3<SAMPLER>(P, p.x, p.y, p.z);
             if (B200VR_Q_PRIMARY_PREFETCH) {
               // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
               // (speculative past early termination): its latency overlaps the classification and the queue traffic
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
-              if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
+              if (have_pre) s_pre = fetch3<SAMPLER>(P, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
             }
             c_primary++;
             float a = alpha_lookup<POW2>(P, apair_base, s);

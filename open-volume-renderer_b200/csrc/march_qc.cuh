@@ -44,7 +44,7 @@ constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
 // the frame gets slower every time: at 3.2 of 6.5 TB/s the kernel is not waiting for DRAM bandwidth but for latency, and every
 // barrier takes independent warps away from the four a scheduler has. Which warp shades which task and the order of every sum are
 // unchanged: frames are bit-identical to the other queue kernels (test_every_shading_kernel_variant_matches_the_oracle).
-template<bool SKIP, bool POW2, bool OCCS, int J, int SYNC = 0>
+template<bool SKIP, bool POW2, bool OCCS, int J, int SYNC = 0, int AHEAD = 1>
 __global__ void __launch_bounds__(QC_THREADS, QC_MIN_CTAS)
 raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 {
@@ -117,6 +117,14 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
       bool cell_empty = false;
       float s_pre = 0.f;     // prefetched value of the sample at (tx, ty), valid while have_pre
       bool have_pre = false;
+      // AHEAD > 1 (option qa6, chosen for small partitions of a frame): primary samples are fetched in batches -- when a lane has no
+      // prefetched value left, the sample at (tx, ty) and the next AHEAD lattice samples that stay in this (live) macrocell go out
+      // together and the following steps consume them. With few tiles per warp (an eighth of a frame on each of 8 GPUs) the launch
+      // is as long as the primary march of its longest tile, a chain of ~1700 dependent steps that each wait for one fetch; on a
+      // whole frame the speculative fetches past early termination and cell exits cost more than the waits they save
+      // (C3 6.41 vs 6.14 ms, C2 2.47 vs 2.28 ms).
+      float pb1 = 0.f, pb2 = 0.f; // values of the samples after s_pre
+      int n_pre = 0;              // AHEAD > 1: how many prefetched values are valid (s_pre first)
       unsigned int mine[J + 1]; // queue slots holding this pixel's tasks, 32 per word
 #pragma unroll
       for (int g = 0; g <= J; g++) mine[g] = 0u;
@@ -345,13 +353,34 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               }
             }
             float s;
-            if (have_pre) s = s_pre;
-            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-            {
-              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
-              // (Measured and rejected on C3 / C2: batches of four -- this sample and the next three fetched together, consumed
-              // over the following steps -- 6.41 vs 6.14 ms / 2.47 vs 2.28 ms: the speculative fetches past early termination and
-              // cell exits cost more than the waits they save.)
+            if (AHEAD > 1) {
+              if (n_pre > 0) {
+                s = s_pre, s_pre = pb1, pb1 = pb2;
+                n_pre--;
+              }
+              else {
+                s = tex3D<float>(P.tex, p.x, p.y, p.z);
+                float a_ty = ty; // the lattice beyond this sample: a_ty reproduces ty = fminf(tx + step, t1) step by step
+                bool ok = true;
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                  if (i < AHEAD) {
+                    const float nty = fminf(a_ty + step, t1), ntm = 0.5f * (a_ty + nty);
+                    ok = ok && nty > a_ty && (!SKIP || ntm < cell_exit);
+                    const float v = tex3d_if(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z), ok);
+                    if (i == 0) s_pre = v;
+                    if (i == 1) pb1 = v;
+                    if (i == 2) pb2 = v;
+                    n_pre += ok ? 1 : 0;
+                    a_ty = nty;
+                  }
+                }
+              }
+            }
+            else {
+              if (have_pre) s = s_pre;
+              else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));

@@ -9,6 +9,9 @@
                                 into this repo. `renderbatch --device b200 ...` then loads the plugin through
                                 create_renderer (ovr/renderer.cpp:42-61).
 
+  build/ovr/renderloop          device/renderloop.cpp: the render loop of the reference's GUI (apps/main_app.cpp:233-263: commit ->
+                                mapframe -> to_cpu -> swap -> render) without a window, linked against the same host objects
+
 The reference's CMake build is not used (it needs OptiX / OSPRay / TBB / GLFW); this is the short recipe the task allows.
 """
 import os
@@ -94,6 +97,11 @@ def build(force=False):
         run(["ar", "rcs", hostlib] + [o for o in objs if "main_batch" not in o])
         for o in objs:
             os.remove(o)
+    # renderloop: the GUI's render loop (apps/main_app.cpp:233-263) without a window, against the same host objects
+    loop, loop_src = os.path.join(OUT, "renderloop"), os.path.join(HERE, "renderloop.cpp")
+    if force or not newer(loop, [loop_src, hostlib]):
+        run(CXX + ["-O1", "-rdynamic", "-o", loop, loop_src, "-Wl,--whole-archive", hostlib, "-Wl,--no-whole-archive",
+                   "-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread", "-Wl,-rpath,$ORIGIN:/usr/local/cuda/lib64"])
     return exe
 
 

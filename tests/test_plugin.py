@@ -242,3 +242,52 @@ def test_renderbatch_on_a_device_group(tmp_path):
     # a device that does not exist fails loudly at init
     r = run_batch(path, str(tmp_path / "bad_"), (W, H), env_extra={"OVR_B200_GPUS": "0,99"})
     assert r.returncode != 0 and "cuda_device out of range" in (r.stderr + r.stdout)
+
+
+LOOP = os.path.join(OVR, "renderloop")
+
+
+@needs_build
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(LOOP), reason="build/ovr/renderloop missing")
+def test_gui_render_loop_through_the_plugin(tmp_path):
+    """SURVEY 8f-f2, the windowless interactive loop: the call sequence of the reference's GUI thread (apps/main_app.cpp:233-263:
+    commit -> mapframe -> to_cpu -> swap -> render) driven through libdevice_b200.so by build/ovr/renderloop, which is compiled
+    against the reference's unchanged headers and host objects. The frame mapped in iteration k must be the frame rendered in
+    iteration k - 1 (the double buffer of device_impl.cpp:102-111,271-281), copied out by the reference's own CrossDeviceBuffer
+    ::to_cpu, and must be what the Python host mirror renders for the camera of iteration k - 1 (bit for bit: same C ABI) and what
+    the oracle renders (1/255)."""
+    import re
+    W, H, n, frames = 160, 96, 40, 3
+    path, vol = write_scene(tmp_path, n=n, tf="ramp")
+    out = str(tmp_path / "loop_")
+    env = dict(os.environ, LD_LIBRARY_PATH=OVR + os.pathsep + os.environ.get("LD_LIBRARY_PATH", ""))
+    cmd = [LOOP, "--scene", path, "--device", "b200", "--fbsize", str(W), str(H), "--frames", str(frames), "--out", out]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    cams = []
+    for ln in r.stdout.splitlines():
+        m = re.match(r"iteration (\d+) camera (\S+) (\S+) (\S+) at (\S+) (\S+) (\S+) up (\S+) (\S+) (\S+) fovy (\S+)", ln)
+        if m:
+            v = [float(x) for x in m.groups()[1:]]
+            cams.append(S.Camera(tuple(v[0:3]), tuple(v[3:6]), tuple(v[6:9]), v[9]))
+    assert len(cams) == frames + 1
+    got = [np.fromfile(out + f"{k:03d}.rgba", np.float32).reshape(H, W, 4) for k in range(frames + 1)]
+    assert not got[0].any()                      # iteration 0 maps the cleared buffer: nothing has been rendered yet
+    sc = ovr_b200.scene_io.read_vidi3d_scene(path)
+    mirror = ovr_b200.create_renderer("b200")
+    mirror.set_fbsize((W, H))
+    mirror.init(sc, cams[0])
+    for k in range(1, frames + 1):
+        mirror.set_camera(cams[k - 1])
+        mirror.commit()
+        mirror.render()
+        want = mirror.download(want_grad=False)[0]
+        assert np.array_equal(got[k].view(np.uint32), want.view(np.uint32)), f"iteration {k} did not map the frame of iteration {k - 1}"
+        assert k == 1 or not np.array_equal(got[k], got[k - 1])
+    mirror.close()
+    sc.camera = cams[frames - 1]
+    o_rgba = pyoracle.OracleScene(oracle_desc(sc, W, H), skip_empty=False).render_march()[0]
+    e, p = max_abs(got[frames], o_rgba), psnr(got[frames], o_rgba)
+    print(f"GUI loop through the plugin: frame {frames - 1} vs oracle max-abs {e:.2e} psnr {p:.1f} dB; " + r.stdout.splitlines()[-1].split("|")[-1])
+    assert e <= 1.0 / 255.0 and p >= 45.0 and (o_rgba[..., 3] > 0).mean() > 0.05

@@ -49,6 +49,9 @@ def main():
             if kv:
                 k, v = kv.split("=")
                 opts[k] = v
+        sampler = opts.pop("sampler", "tex3d")   # not a tuning option: the sampler of b200vr_params (tex3d | manual)
+        r.sampler = capi.SAMPLER_MANUAL if sampler == "manual" else capi.SAMPLER_TEX3D
+        r.apply_device_options()
         for k, v in opts.items():
             r.set_option(k, v)
         ms = []
@@ -67,7 +70,7 @@ def main():
         line = {"set": spec, "ms_median": med, "ms_min": float(min(ms)), "samples": samples, "fetches": fetches,
                 "primary": st["primary_samples"], "shadow": st["shadow_samples"], "shaded": st["gradient_fetches"] // 3,
                 "msamples_s": samples / med / 1e3, "frac_fetch_roof": fetches / (med * 1e-3) / p_fetch if p_fetch else None,
-                "max_abs_vs_first": float(np.abs(rgba - base).max()), "launches": st["kernel_launches"]}
+                "max_abs_vs_first": float(np.abs(rgba - base).max()), "launches": st["kernel_launches"], "kernel_name": r.last_kernel}
         print(json.dumps(line), flush=True)
         lines.append(line)
     if args.out:
