@@ -19,7 +19,10 @@
 
 namespace b200k {
 
-constexpr int QB_THREADS = 256;
+#ifndef B200VR_QBC_THREADS
+#define B200VR_QBC_THREADS 256
+#endif
+constexpr int QB_THREADS = B200VR_QBC_THREADS; // threads per CTA of the depth-blocked kernels (march_qb.cuh, march_qc.cuh): A/B builds
 #ifndef B200VR_QB_MIN_CTAS
 #define B200VR_QB_MIN_CTAS 2
 #endif

@@ -25,7 +25,7 @@ namespace b200k {
 #ifndef B200VR_QC_MIN_CTAS
 #define B200VR_QC_MIN_CTAS 2
 #endif
-constexpr int QC_THREADS = 256;
+constexpr int QC_THREADS = QB_THREADS;
 constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
 
 // slot layout (32 bytes): [0] p.x  [4] p.y  [8] p.z  [12] s  [16] w  [20] log2-transmittance of an off-lattice task  [24] [28] -
