@@ -202,7 +202,7 @@ int b200vr_wait(b200vr_t* h, b200vr_stats* stats);
 const char* b200vr_last_kernel(const b200vr_t* h);
 /* Tuning switches of a handle; none changes what is computed per sample, they pick between kernels / launch orders that
  * render the same frame (A/B runs, tests of every kernel variant). Defaults come from the environment variable
- * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | qa6 | qd6 | qg6 | ring | legacy | sm),
+ * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | qd6 | qg6 | ring | legacy | sm),
  * "tile_order" (-1 auto, 0 rows, 1 centre-out, 2 previous cost, 3 Z-order, 4 | 5 columns, 6 middle rows first, 7 sheets of the
  * light direction), "sheet_px", "max_ctas_per_sm" (0 = all that fit), "ring_high", "occ_smem" (0 = macrocell occupancy mask
  * read from global memory even when it would fit in shared memory), "carveout" (shared-memory carve-out in percent, -1 =

@@ -35,7 +35,7 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QA6, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
        KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
@@ -187,13 +187,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qa6", KERNEL_QA6 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qa6, qd6, qg6, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -841,7 +841,6 @@ struct KernelChoice {
 #define B200VR_K_QC4(a, b, c) raymarch_qc_kernel<a, b, c, 4>
 #define B200VR_K_QC6(a, b, c) raymarch_qc_kernel<a, b, c, 6>
 #define B200VR_K_QC8(a, b, c) raymarch_qc_kernel<a, b, c, 8>
-#define B200VR_K_QA6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 0, 3>
 #define B200VR_K_QG6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 3>
 #define B200VR_K_QD6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 1>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
@@ -917,10 +916,6 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       else if (force == KERNEL_QC8) {
         k.fn = B200VR_PICK(B200VR_K_QC8, skip, pow2, occs);
         k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<8>(), k.name = "raymarch_qc_kernel<J=8>";
-      }
-      else if (force == KERNEL_QA6) {
-        k.fn = B200VR_PICK(B200VR_K_QA6, skip, pow2, occs);
-        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_qc_kernel<J=6,AHEAD=3>";
       }
       else if (force == KERNEL_QG6) {
         k.fn = B200VR_PICK(B200VR_K_QG6, skip, pow2, occs);
@@ -1504,6 +1499,22 @@ static int render_wait(b200vr_t* h, b200vr_stats* stats)
     h->ring_cap = 0; // rebuilt on the next render
     return fail(h, B200VR_ECUDA, "render: the deferred-shading ring timed out (internal error)");
   }
+#if B200VR_PHASE_STATS
+  if (h->tune.debug_tiles && had_frame) { // diagnostic build -DB200VR_PHASE_STATS=1: where the warps of march_qc.cuh spend their clocks
+    const double tot = (double)(c.tile_clocks_sum + c.drain_clocks_sum + c.blocks_published + c.blocks_stolen + c.tile_clocks_max);
+    const int warps = h->last_grid * h->last_warps_per_cta;
+    std::fprintf(stderr, "[b200] phases (%s, %d warps, %.0f kclk per warp): primary march %.1f %%, pass: clip %.1f %%, lattice loop %.1f %%, "
+                         "gradient + shade + hand-back %.1f %%, other %.1f %%\n", h->last_kernel.c_str(), warps, tot * 1e-3 / warps,
+                 100.0 * c.tile_clocks_sum / tot, 100.0 * c.drain_clocks_sum / tot, 100.0 * c.blocks_published / tot, 100.0 * c.blocks_stolen / tot,
+                 100.0 * c.tile_clocks_max / tot);
+    const double iters = (double)(c.warp_clocks_max >> 40), lanes = (double)(c.warp_clocks_max & ((1ull << 40) - 1));
+    const double passes = (double)(c.delta_samples >> 40), steps = (double)(c.delta_samples & ((1ull << 40) - 1));
+    std::fprintf(stderr, "[b200] primary: %.0f k iterations per warp, %.0f clocks each, %.1f live lanes, %.1f samples executed per iteration; passes: %.0f per "
+                         "warp, %.1f lattice steps each, %.0f clocks per step\n", iters * 1e-3 / warps, c.tile_clocks_sum / std::max(iters, 1.0), lanes / std::max(iters, 1.0),
+                 (double)c.primary_samples / std::max(iters, 1.0), passes / warps, steps / std::max(passes, 1.0), c.blocks_published / std::max(steps, 1.0));
+    c.delta_samples = 0;
+  }
+#endif
   if (B200VR_TILE_STATS && h->tune.debug_tiles && had_frame) { // build with -DB200VR_TILE_STATS=1
     float ms = 0.f;
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);

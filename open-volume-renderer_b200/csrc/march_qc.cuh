@@ -27,6 +27,17 @@ namespace b200k {
 #endif
 constexpr int QC_THREADS = QB_THREADS;
 constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
+// -DB200VR_PHASE_STATS=1 (diagnostic builds only): every warp adds up the SM clocks it spends marching primary samples, in the
+// clip / lattice / gradient + shade + hand-back parts of its shading passes and in everything else; the sums come back through the
+// debug fields of Counters and b200vr_wait prints them (option debug_tiles). DESIGN.md section 5.1b quotes one such run.
+#ifndef B200VR_PHASE_STATS
+#define B200VR_PHASE_STATS 0
+#endif
+#if B200VR_PHASE_STATS
+#define QC_PHASE(var) do { const unsigned int now_ = (unsigned int)clock(); var += now_ - ph_t; ph_t = now_; } while (0)
+#else
+#define QC_PHASE(var) do { } while (0)
+#endif
 
 // slot layout (32 bytes): [0] p.x  [4] p.y  [8] p.z  [12] s  [16] w  [20] log2-transmittance of an off-lattice task  [24] [28] -
 // after shading:          [0] C.x  [4] C.y  [8] C.z  [12] G.x [16] G.y [20] G.z
@@ -44,7 +55,7 @@ constexpr int QC_MIN_CTAS = B200VR_QC_MIN_CTAS;
 // the frame gets slower every time: at 3.2 of 6.5 TB/s the kernel is not waiting for DRAM bandwidth but for latency, and every
 // barrier takes independent warps away from the four a scheduler has. Which warp shades which task and the order of every sum are
 // unchanged: frames are bit-identical to the other queue kernels (test_every_shading_kernel_variant_matches_the_oracle).
-template<bool SKIP, bool POW2, bool OCCS, int J, int SYNC = 0, int AHEAD = 1>
+template<bool SKIP, bool POW2, bool OCCS, int J, int SYNC = 0>
 __global__ void __launch_bounds__(QC_THREADS, QC_MIN_CTAS)
 raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 {
@@ -69,6 +80,10 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
   unsigned int c_primary = 0, c_shadow = 0, c_shaded = 0, c_rays = 0; // per lane, over all tiles of this warp
   const unsigned int lt_mask = (1u << lane) - 1u;
   const unsigned int my_slot0 = queue_base + 32u * (unsigned)lane; // task j of this lane: slot j * 32 + lane
+#if B200VR_PHASE_STATS
+  unsigned int ph_t = (unsigned int)clock(), ph_other = 0, ph_primary = 0, ph_clip = 0, ph_lattice = 0, ph_shade = 0;
+  unsigned int ph_iters = 0, ph_lanes = 0, ph_passes = 0, ph_steps = 0; // primary iterations, live lanes in them, passes, lattice steps
+#endif
 
   for (;;) {
     int k = 0;
@@ -117,18 +132,11 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
       bool cell_empty = false;
       float s_pre = 0.f;     // prefetched value of the sample at (tx, ty), valid while have_pre
       bool have_pre = false;
-      // AHEAD > 1 (option qa6, chosen for small partitions of a frame): primary samples are fetched in batches -- when a lane has no
-      // prefetched value left, the sample at (tx, ty) and the next AHEAD lattice samples that stay in this (live) macrocell go out
-      // together and the following steps consume them. With few tiles per warp (an eighth of a frame on each of 8 GPUs) the launch
-      // is as long as the primary march of its longest tile, a chain of ~1700 dependent steps that each wait for one fetch; on a
-      // whole frame the speculative fetches past early termination and cell exits cost more than the waits they save
-      // (C3 6.41 vs 6.14 ms, C2 2.47 vs 2.28 ms).
-      float pb1 = 0.f, pb2 = 0.f; // values of the samples after s_pre
-      int n_pre = 0;              // AHEAD > 1: how many prefetched values are valid (s_pre first)
       unsigned int mine[J + 1]; // queue slots holding this pixel's tasks, 32 per word
 #pragma unroll
       for (int g = 0; g <= J; g++) mine[g] = 0u;
       int count = 0;            // tasks waiting (warp-uniform)
+      QC_PHASE(ph_other);
 
       for (;;) {
         const bool any_alive = __any_sync(0xffffffffu, alive);
@@ -143,6 +151,10 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
           // =================== shading pass: lane takes tasks lane, lane + 32, ... ===================
           const int n = min(count, J * 32);
           __syncwarp();
+          QC_PHASE(ph_primary);
+#if B200VR_PHASE_STATS
+          ph_passes++;
+#endif
           // ---- A. exit parameter st1 of every task's shadow ray (__closesthit__volume_shadow, shaders_raymarching.cu:205-229);
           //         tasks whose clip entry is not exactly 0 do not sit on the shared lattice and are set aside ----
           float st1[J], slog[J];
@@ -160,6 +172,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               }
             }
           }
+          QC_PHASE(ph_clip);
           // ---- B. lockstep shadow march on the shared lattice (raymarching_shadow, shaders_raymarching.cu:44-85) ----
           // The body is straight-line code: every task's arithmetic is done for all J tasks, finished ones included, and only
           // the texture fetch and the updates are predicated. With per-task branches ptxas keeps the J chains apart and a warp
@@ -214,7 +227,12 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
             };
             // SYNC == 1: one CTA barrier per lattice step, as many steps as the CTA's longest ray needs; a warp whose rays have
             // all ended skips the body (live stays 0)
-            auto more = [&]() { return SYNC == 1 ? (__syncthreads_or(live != 0u) != 0) : (live != 0u); };
+            auto more = [&]() {
+#if B200VR_PHASE_STATS
+              ph_steps++;
+#endif
+              return SYNC == 1 ? (__syncthreads_or(live != 0u) != 0) : (live != 0u);
+            };
             // The loop is unrolled by two so that the two value arrays swap ROLES instead of contents: with `sv0 = sv1` at the end
             // of a step the moves waited for the fetches issued at the top of the same step (profiles/r2h: 20 % of all stall
             // samples sat on those MOVs), which made the pipeline one step shallower than written.
@@ -225,6 +243,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               if (!(SYNC == 1 && live == 0u)) lattice_step(sv1, f1, sv0, f0);
             }
           }
+          QC_PHASE(ph_lattice);
           // ---- C. tasks off the shared lattice, one at a time (rare): result through the task's slot ----
           const unsigned int was_odd = odd;
           while (odd != 0u) {
@@ -317,10 +336,14 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
           for (int g = 0; g <= J; g++) mine[g] = 0u;
           mine[0] = carried;
           count = rest;
+          QC_PHASE(ph_shade);
           continue;
         }
 
         // =================== one primary sample per live ray (raymarching, shaders_raymarching.cu:87-171) ===================
+#if B200VR_PHASE_STATS
+        ph_iters++, ph_lanes += (unsigned int)__popc(__ballot_sync(0xffffffffu, alive));
+#endif
         bool want = false;
         f3 tp = mk3(0.f);
         float ts = 0.f, tw = 0.f;
@@ -353,34 +376,14 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               }
             }
             float s;
-            if (AHEAD > 1) {
-              if (n_pre > 0) {
-                s = s_pre, s_pre = pb1, pb1 = pb2;
-                n_pre--;
-              }
-              else {
-                s = tex3D<float>(P.tex, p.x, p.y, p.z);
-                float a_ty = ty; // the lattice beyond this sample: a_ty reproduces ty = fminf(tx + step, t1) step by step
-                bool ok = true;
-#pragma unroll
-                for (int i = 0; i < 3; i++) {
-                  if (i < AHEAD) {
-                    const float nty = fminf(a_ty + step, t1), ntm = 0.5f * (a_ty + nty);
-                    ok = ok && nty > a_ty && (!SKIP || ntm < cell_exit);
-                    const float v = tex3d_if(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z), ok);
-                    if (i == 0) s_pre = v;
-                    if (i == 1) pb1 = v;
-                    if (i == 2) pb2 = v;
-                    n_pre += ok ? 1 : 0;
-                    a_ty = nty;
-                  }
-                }
-              }
-            }
-            else {
-              if (have_pre) s = s_pre;
-              else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+            if (have_pre) s = s_pre;
+            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+            {
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
+              // Measured and rejected (profiles/r2n_*, r2x_*): this sample and the next three fetched
+              // together and consumed over the following steps (C3 6.41 vs 6.14 ms), and four samples fetched, classified and
+              // corrected as independent chains with only the compositing recurrence and the queue stores in order (6.93 ms;
+              // C2 3.54 vs 2.29) -- neither shortens a small partition's launch either (1/8 of C3: 2.26 ms all three ways).
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
@@ -414,6 +417,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
         }
         count += __popc(m);
       }
+      QC_PHASE(ph_primary);
       // render_raymarching (shaders_raymarching.cu:260-321): background is always 0 -> alpha_blend = C / A
       if (!P.premultiplied) { // un-premultiply; A == 0 adds nothing, as alpha_blend does
         C = A > 0.f ? C / A : mk3(0.f);
@@ -452,7 +456,20 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
       }
     }
     if (lane == 0 && have_tile) tile_cost_add(P, tile_slot, tile_t0);
+    QC_PHASE(ph_other);
   }
+#if B200VR_PHASE_STATS
+  if (lane == 0) {
+    atomicAdd(&P.counters->tile_clocks_sum, (unsigned long long)ph_primary);
+    atomicAdd(&P.counters->drain_clocks_sum, (unsigned long long)ph_clip);
+    atomicAdd(&P.counters->blocks_published, (unsigned long long)ph_lattice);
+    atomicAdd(&P.counters->blocks_stolen, (unsigned long long)ph_shade);
+    atomicAdd(&P.counters->tile_clocks_max, (unsigned long long)ph_other);
+    // four more sums packed into two words: iterations | live lanes, passes | lattice steps (each < 2^32 per launch at these sizes)
+    atomicAdd(&P.counters->warp_clocks_max, ((unsigned long long)ph_iters << 40) + (unsigned long long)ph_lanes);
+    atomicAdd(&P.counters->delta_samples, ((unsigned long long)ph_passes << 40) + (unsigned long long)ph_steps);
+  }
+#endif
 
   // executed-sample counters: one atomic set per warp
   const unsigned int n_primary = __reduce_add_sync(0xffffffffu, c_primary), n_shadow = __reduce_add_sync(0xffffffffu, c_shadow);

@@ -185,7 +185,7 @@ VARIANT_OPTIONS = [
     {"kernel": "qb2"}, {"kernel": "qb4"}, {"kernel": "qb4", "occ_smem": 0}, {"kernel": "qb4", "occ_smem": 0, "tile_order": 7, "sheet_px": 16},
     {"kernel": "qb8"}, {"kernel": "qb8", "occ_smem": 0, "max_ctas_per_sm": 1},
     {"kernel": "qc4"}, {"kernel": "qc4", "occ_smem": 0}, {"kernel": "qc6"}, {"kernel": "qc8"}, {"kernel": "qc8", "occ_smem": 0, "tile_order": 7},
-    {"kernel": "qa6"}, {"kernel": "qa6", "occ_smem": 0}, {"kernel": "qg6"}, {"kernel": "qd6"}, {"kernel": "qd6", "occ_smem": 0}, {"kernel": "qd6", "occ_smem": 0, "tile_order": 0}, {"kernel": "qg6", "max_ctas_per_sm": 1},
+    {"kernel": "qg6"}, {"kernel": "qd6"}, {"kernel": "qd6", "occ_smem": 0}, {"kernel": "qd6", "occ_smem": 0, "tile_order": 0}, {"kernel": "qg6", "max_ctas_per_sm": 1},
     {"kernel": "ring"}, {"kernel": "ring", "occ_smem": 0}, {"kernel": "ring", "occ_smem": 0, "tile_order": 7},
 ]
 
