@@ -826,13 +826,18 @@ def main():
         hbm_ach = hbm_bytes * n_frames / kernel_s / 1e9 if kernel_s > 0 else 0.0
         kernel_name = ctx["kernel"]   # b200vr_last_kernel: what pick_kernel (csrc/b200vr.cu) chose for the timed frames
         # dram__bytes_read.sum + dram__bytes_write.sum of that kernel for this workload, from the committed `ncu --set full` capture
-        traffic, traffic_src = None, None
+        traffic, traffic_src, l1_miss = None, None, None
         if world == 1:
             try:
                 with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                     t = json.load(f).get(f"{args.workload}:{kernel_name}")
                 if t:
                     traffic, traffic_src = t["dram_bytes_per_launch"], t["source"]
+                    if t.get("l1_miss_bytes_per_launch"):
+                        # what bounds the 1024^3 kernel: bytes that miss L1 (l1tex__m_xbar2l1tex_read_bytes of the committed
+                        # capture) over this run's kernel time; the fetch probe sustains 3.55 TB/s of them at its DRAM roof
+                        l1_miss = {"bytes_per_launch": t["l1_miss_bytes_per_launch"], "source": t["l1_miss_source"],
+                                   "achieved_gbs": t["l1_miss_bytes_per_launch"] / (ctx["kernel_ms"] / n_frames * 1e-3) / 1e9}
             except (OSError, ValueError):
                 pass
         roofline = {"achieved_tex": ach / peak if peak else None, "achieved_hbm": hbm_ach / pk["hbm_gbs"],   # fractions of both roofs
@@ -840,7 +845,7 @@ def main():
                     "traffic": traffic, "traffic_source": traffic_src, "kernel": kernel_name,
                     "note": "texture/L1 sampling roofline: 32 B x executed trilinear fetches / mean kernel time (CUDA events on the launch "
                             "stream); peak = best b200vr_bench_fetch rate x 32 B measured in this run",
-                    "kernel_ms_per_launch": ctx["kernel_ms"] / n_frames, "fetch_bench": fetch_rows,
+                    "kernel_ms_per_launch": ctx["kernel_ms"] / n_frames, "fetch_bench": fetch_rows, "l1_miss_path": l1_miss,
                     "hbm": {"achieved": hbm_ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_ach / pk["hbm_gbs"],
                             "bytes_per_launch": hbm_bytes, "live_macrocells": live_cells, "macrocells": n_cells,
                             "bytes_per_launch_whole_volume": hbm_bytes_whole, "peak_source": pk["source"]}}
