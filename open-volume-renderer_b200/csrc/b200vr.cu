@@ -425,8 +425,8 @@ static int finish_volume(b200vr_t* h, const float obj_to_world[12], const void* 
   CK(cudaMemsetAsync(h->occ_bits, 0, (size_t)h->occ_words * sizeof(unsigned int), h->stream));
   const int init[2] = { 0x7fffffff, (int)0x80000000 };
   CK(cudaMemcpyAsync(h->minmax, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
-  macrocell_range_kernel<<<(unsigned)n_cells, RANGE_THREADS, 0, h->stream>>>(h->lin, h->nx, h->ny, h->nz, h->mc.x, h->mc.y,
-                                                                              h->mc.z, h->ranges, h->minmax);
+  macrocell_range_kernel<<<(unsigned)(h->mc.y * h->mc.z), RANGE_THREADS, 2 * (size_t)h->mc.x * sizeof(int), h->stream>>>(
+    h->lin, h->nx, h->ny, h->nz, h->mc.x, h->mc.y, h->mc.z, h->ranges, h->minmax);
   CK(cudaGetLastError());
   int mm[2];
   CK(cudaMemcpyAsync(mm, h->minmax, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));

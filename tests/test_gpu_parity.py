@@ -719,6 +719,41 @@ def _sparse_case_body(name, shading, path, sampler, W, H, tile, sc):
     r.close()
 
 
+def test_sparse_accumulation_reset_clears_the_unsampled_pixels():
+    """Sparse sampling while accumulating (device_impl.cpp:225-239): sampled pixels accumulate from frame to frame and unsampled
+    ones are left alone -- until a camera / TF / focus change resets the accumulation: framebuffer.reset() then zeroes both buffers
+    (optix7_common.h:250-253,409-413), so pixels the new view has not sampled yet must be 0, not the previous view's content."""
+    from helpers import sparse_noise_table
+    W, H, tile = 160, 96, 16
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    r = make_renderer(sc, W, H, accumulate=True)
+    r.set_sparse_noise(sparse_noise_table(tile), tile, 64)
+    r.set_focus((0.5, 0.5), 0.25, 0.02)
+    r.set_sparse_sampling(True)
+    r.commit()
+    seen = np.zeros((H, W), bool)
+    for _ in range(6):   # six time slices of the noise table: most pixels near the focus get sampled at least once
+        r.render()
+        seen |= _mask_from_list(r.sparse_samples(), W, H)
+    assert r.last_stats["frame_index"] == 6
+    before = r.download()[0].copy()
+    assert (before[seen][:, 3] > 0).any() and (before[~seen] == 0).all() and 0.2 < seen.mean() < 0.98
+    r.set_camera(S.camera_preset("front", (48, 48, 48)))   # resets the accumulation
+    r.commit()
+    r.render()
+    assert r.last_stats["frame_index"] == 1
+    now = _mask_from_list(r.sparse_samples(), W, H)
+    after, grad = r.download()
+    stale = seen & ~now
+    assert stale.sum() > 100                       # pixels that held the old view and are not sampled by this frame
+    assert (after[~now] == 0).all() and (grad[~now] == 0).all(), "unsampled pixels kept the previous view after an accumulation reset"
+    assert (after[now][:, 3] > 0).any()
+    # both buffers of the double buffer were cleared, not just the current one
+    r.swap()
+    assert not r.download()[0].any()
+    r.close()
+
+
 def test_sparse_sampling_golden_cases_and_frame_index():
     """The five golden cases of the reference's mask kernels (incl. the empty list and p == 1), through the C ABI; the noise
     time slice follows frame_index, which advances by one per render (device_impl.cpp:241)."""
