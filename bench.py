@@ -546,9 +546,10 @@ def parity_march(rgba, grad, pix):
         out["worst_pixel"] = {"xy": [int(ix) * s, int(iy) * s], "gpu": [float(v) for v in g[iy, ix]], "oracle": [float(v) for v in o[iy, ix]]}
         out["alpha_of_pixels_over_tolerance"] = {"min": float(o[over][:, 3].min()), "median": float(np.median(o[over][:, 3])), "max": float(o[over][:, 3].max())}
     # The bar, pixel for pixel, on the stored (un-premultiplied) frame; and the same bar where it is meaningful: a pixel whose
-    # opacity is below 1e-3 is invisible (it displays as 0.001 x colour at most) while alpha_blend's C / A turns a one-quantum
-    # difference of ONE sample's opacity -- the residual of the oracle's texture-unit model, >= 99.7 % of the fetches bit-exact,
-    # the rest 1-2 ulp -- into a full-scale colour there. Both are reported; `ok` is the second.
+    # opacity is below 1e-3 is invisible (it displays as 0.001 x colour at most) while alpha_blend's C / A turns a difference of
+    # a few 1e-6 of ONE sample's opacity -- the last-bit rounding of a sample position, which the kernel (object-space ray) and the
+    # host-compiled reference code (world position transformed per sample) do differently, DESIGN.md sections 4 and 7.1 -- into a
+    # full-scale colour there. Both are reported; `ok` is the second.
     vis = o[..., 3] >= 1e-3
     out["max_abs_where_alpha_ge_1e-3"] = float(np.abs(g - o)[vis].max()) if vis.any() else 0.0
     out["ok_every_pixel_as_stored"] = bool(e <= 1.0 / 255.0 and p >= 45.0)
