@@ -518,7 +518,7 @@ def run_e2e(ctx, args):
 
 
 KERNEL_OPTION = {"raymarch_q_kernel": "q", "raymarch_ring_kernel": "ring", "raymarch_qc_kernel<J=4>": "qc4", "raymarch_qc_kernel<J=6>": "qc6",
-                 "raymarch_qc_kernel<J=8>": "qc8"}
+                 "raymarch_qc_kernel<J=8>": "qc8", "raymarch_rq_kernel<J=6>": "rq6"}
 
 
 def parity_march(rgba, grad, pix):

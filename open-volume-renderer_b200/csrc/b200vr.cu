@@ -12,6 +12,7 @@
 #include "march_qb.cuh"
 #include "march_qc.cuh"
 #include "march_ring.cuh"
+#include "march_rq.cuh"
 #include "march_ns.cuh"
 #include "sparse.cuh"
 
@@ -35,7 +36,7 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RING, KERNEL_LEGACY,
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RQ6, KERNEL_RING, KERNEL_LEGACY,
        KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
@@ -121,7 +122,7 @@ struct b200vr {
   unsigned int* ring_ctrl = nullptr;
   unsigned int* ring_seq = nullptr;
   float4* ring_data = nullptr;
-  int ring_cap = 0, ring_count = 0;
+  int ring_cap = 0, ring_count = 0, ring_block = 0; // slots per ring, rings, float4 per slot
   unsigned long long* acc = nullptr; // per pixel fixed-point sums (allocated with the frame)
   float* ray_alpha = nullptr;
   Counters* counters = nullptr;
@@ -187,13 +188,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "rq6", KERNEL_RQ6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, rq6, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -822,7 +823,8 @@ struct KernelChoice {
   render_kernel_t fn;
   int threads;
   size_t smem;
-  bool ring = false; // march_ring.cuh: needs the task ring, one launch per sample + resolve_kernel
+  bool ring = false; // march_ring.cuh / march_rq.cuh: needs the task rings, one launch per sample + resolve_kernel
+  int ring_block = RING_BLOCK_FLOAT4; // float4 per ring slot
   bool cta_sync = false; // march_qc.cuh SYNC: the warps of a CTA take consecutive tiles of the (sheet) launch order and shade in lockstep
   const char* name = "";
 };
@@ -844,6 +846,7 @@ struct KernelChoice {
 #define B200VR_K_QG6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 3>
 #define B200VR_K_QD6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 1>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
+#define B200VR_K_RQ6(a, b, c) raymarch_rq_kernel<a, b, c, 6>
 #define B200VR_K_NS(a, b, c) raymarch_ns_kernel<a, b, c>
 
 static KernelChoice pick_kernel(const b200vr_t* h)
@@ -851,19 +854,22 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   const b200vr_params& p = h->prm;
   const int force = h->tune.kernel;
   const bool legacy = force == KERNEL_LEGACY, sm = force == KERNEL_SM;
-  // Per-warp queue kernels or queue + work-sharing rings (march_ring.cuh). Measured on C2: the whole frame on one GPU 2.29 vs
-  // 2.65 ms (the rings cost ~8 % more instructions), an eighth of its tiles 1.06-1.50 vs 0.80-1.13 ms (the heaviest warp tile
-  // alone takes ~1 ms with the queue kernel): rings when the frame is split sort-first, queue otherwise.
-  // Sparse (foveated) frames keep the heavy tiles around the focus and drop most of the light ones: the launch is as long as
-  // its heaviest warp tile with the queue kernel (C2-sparse 1.59 ms for a quarter of the samples), so they take the rings too.
-  // Not while accumulating: resolve_kernel rewrites every pixel, the reference leaves unsampled pixels untouched then.
+  // Whole frames: per-warp queue kernels. march_q.cuh (one task per lane and pass) while the macrocell occupancy mask fits into
+  // shared memory; beyond that (edge > 704 voxels: far beyond the 126 MB L2) the frame is bound by the shadow rays' L1 misses
+  // and the depth-blocked passes of march_qc.cuh win (C3: 6.2 ms against 10.7 ms, profiles/r2g_ab_C3_qc.json).
+  // Sort-first partitions: a launch lasts about its mean load plus its heaviest warp tile, and the heaviest tile is the same
+  // however many devices share the frame. The work-sharing rings take the shading off that chain; with depth-blocked passes
+  // (march_rq.cuh) they beat both the queue kernels and the one-task-per-lane rings (march_ring.cuh) from two devices on, for
+  // both volume classes (profiles/r3a_partition_rq.jsonl: an eighth of C3 1.38 against 2.23 ms, of C2 0.68 against 1.03 ms).
+  // Sparse (foveated) frames keep the heavy tiles around the focus and drop most of the light ones, so they take the rings too
+  // (C2-sparse: 1.25 ms a frame against 1.46 ms with march_ring.cuh and 1.59 ms with the queue kernel) -- not while
+  // accumulating: resolve_kernel rewrites every pixel, the reference leaves unsampled pixels untouched then.
   const bool sparse_ring = h->sparse && !p.accumulate;
-  // Volumes whose occupancy mask does not fit into shared memory (edge > 704 voxels: far beyond the 126 MB L2) are bound by the
-  // shadow rays' DRAM / L2 misses, not by the heaviest tile: the depth-blocked passes of march_qc.cuh win on the whole frame
-  // (C3: 6.2 ms against 10.7 ms for the queue kernel and 11.0 ms for the rings, profiles/r2g_ab_C3_qc.json) and on its partitions.
   const bool large = p.skip_empty && !q_occ_in_smem(h->occ_words);
-  const bool ring = force == KERNEL_RING || (force == KERNEL_AUTO && ((h->nranks != 1 && !large) || sparse_ring));
-  const bool auto_qc6 = force == KERNEL_AUTO && large && !ring;
+  const bool ring = force == KERNEL_RING;
+  const bool rq6 = force == KERNEL_RQ6 || (force == KERNEL_AUTO && (h->nranks != 1 || sparse_ring) &&
+                                           (size_t)h->width * h->height <= (size_t)RQ_PIXEL_MASK);
+  const bool auto_qc6 = force == KERNEL_AUTO && large && !ring && !rq6;
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
@@ -892,6 +898,11 @@ static KernelChoice pick_kernel(const b200vr_t* h)
         k.fn = B200VR_PICK(B200VR_K_RING, skip, pow2, occs);
         k.ring = true;
         k.threads = Q_THREADS, k.smem = tables + q_queue_bytes(), k.name = "raymarch_ring_kernel";
+      }
+      else if (rq6) {
+        k.fn = B200VR_PICK(B200VR_K_RQ6, skip, pow2, occs);
+        k.ring = true, k.ring_block = rq_block_float4<6>();
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>() + rq_acc_bytes(), k.name = "raymarch_rq_kernel<J=6>";
       }
       else if (force == KERNEL_QB2) {
         k.fn = B200VR_PICK(B200VR_K_QB2, skip, pow2, occs);
@@ -1378,6 +1389,8 @@ static int render_enqueue(b200vr_t* h)
     const int rc = build_sparse_list(h, P, extra_launches);
     if (rc != B200VR_OK) return rc;
   }
+  if (kc.ring_block != RING_BLOCK_FLOAT4 && (size_t)h->width * h->height > (size_t)RQ_PIXEL_MASK)
+    return fail(h, B200VR_EINVAL, "render: kernel rq6 takes frames of up to 2^27 - 1 pixels");
   const render_kernel_t kernel = kc.fn;
   const size_t smem = kc.smem;
   int per_sm = 0;
@@ -1428,16 +1441,16 @@ static int render_enqueue(b200vr_t* h)
     P.ring_high = h->tune.ring_high;
     int cap = 32;
     while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
-    if (cap != h->ring_cap || grid != h->ring_count) {
+    if (cap != h->ring_cap || grid != h->ring_count || kc.ring_block != h->ring_block) {
       CK(cudaStreamSynchronize(h->stream));
       cudaFree(h->ring_ctrl);
       cudaFree(h->ring_seq);
       cudaFree(h->ring_data);
-      h->ring_ctrl = nullptr, h->ring_seq = nullptr, h->ring_data = nullptr, h->ring_cap = 0, h->ring_count = 0;
+      h->ring_ctrl = nullptr, h->ring_seq = nullptr, h->ring_data = nullptr, h->ring_cap = 0, h->ring_count = 0, h->ring_block = 0;
       CK(cudaMalloc(&h->ring_ctrl, ring_ctrl_words(grid) * sizeof(unsigned int)));
       CK(cudaMalloc(&h->ring_seq, (size_t)cap * grid * sizeof(unsigned int)));
-      CK(cudaMalloc(&h->ring_data, (size_t)cap * grid * RING_BLOCK_FLOAT4 * sizeof(float4)));
-      h->ring_cap = cap, h->ring_count = grid;
+      CK(cudaMalloc(&h->ring_data, (size_t)cap * grid * kc.ring_block * sizeof(float4)));
+      h->ring_cap = cap, h->ring_count = grid, h->ring_block = kc.ring_block;
       ring_init_kernel<<<64, 256, 0, h->stream>>>(h->ring_seq, cap, grid, h->ring_ctrl, (int)ring_ctrl_words(grid));
       CK(cudaGetLastError());
       extra_launches++;

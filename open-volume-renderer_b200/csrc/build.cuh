@@ -365,6 +365,7 @@ __global__ void ring_start_kernel(unsigned int* ctrl, int stride, int rings, int
   }
   if (r == 0) {
     ctrl[(size_t)rings * 3 * stride] = (unsigned int)(rings * warps_per_cta);
+    ctrl[(size_t)rings * 3 * stride + 1] = 0u; // march_rq.cuh: blocks published and not yet taken
     ctrl[(size_t)rings * 3 * stride + stride] = 0u;
   }
 }

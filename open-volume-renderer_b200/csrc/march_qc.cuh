@@ -155,159 +155,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
 #if B200VR_PHASE_STATS
           ph_passes++;
 #endif
-          // ---- A. exit parameter st1 of every task's shadow ray (__closesthit__volume_shadow, shaders_raymarching.cu:205-229);
-          //         tasks whose clip entry is not exactly 0 do not sit on the shared lattice and are set aside ----
-          float st1[J], slog[J];
-          unsigned int live = 0u, odd = 0u; // bit j: task j of this lane marches in lockstep / is marched on its own afterwards
-#pragma unroll
-          for (int j = 0; j < J; j++) {
-            st1[j] = 0.f;
-            slog[j] = 0.f;
-            if (j * 32 + lane < n) {
-              const float4 q0 = lds_f32x4(my_slot0 + 1024u * (unsigned)j);
-              float t0;
-              if (clip_shadow_p(P, mk3(q0.x, q0.y, q0.z), t0, st1[j])) {
-                if (t0 != 0.f) odd |= 1u << j;
-                else if (fminf(st1[j], P.sstep) > 0.f) live |= 1u << j; // first interval [0, min(st1, 0 + sstep)] is not empty
-              }
-            }
-          }
-          QC_PHASE(ph_clip);
-          // ---- B. lockstep shadow march on the shared lattice (raymarching_shadow, shaders_raymarching.cu:44-85) ----
-          // The body is straight-line code: every task's arithmetic is done for all J tasks, finished ones included, and only
-          // the texture fetch and the updates are predicated. With per-task branches ptxas keeps the J chains apart and a warp
-          // issues one dependent chain after the other (profiles/r2f: 25 % of the stall samples "wait", 0.5 eligible warps per
-          // scheduler and cycle with 4 resident warps); as selects the J independent chains interleave.
-          // fetches of the interval [a, min(st1, b)] for the tasks in `mask`
-          auto issue = [&](float a, float b, unsigned int mask, float (&sv)[J], unsigned int& fetched) {
-            fetched = 0u;
-#pragma unroll
-            for (int j = 0; j < J; j++) {
-              const float tm = 0.5f * (a + fminf(st1[j], b));
-              const float4 q0 = lds_f32x4_nv(my_slot0 + 1024u * (unsigned)j);
-              const f3 q = mk3(__fmaf_rn(tm, P.sh_d.x, q0.x), __fmaf_rn(tm, P.sh_d.y, q0.y), __fmaf_rn(tm, P.sh_d.z, q0.z));
-              bool on = ((mask >> j) & 1u) != 0u;
-              // a sample in an empty macrocell has alpha == 0 exactly and adds 0 to the log sum: cell test only
-              // (pad_index_floor clamps the index, so the test is harmless for the garbage position of a finished task)
-              if (SKIP) {
-                const bool occ = occ_bit<OCCS>(P, occ_base, pad_index_floor(P, q)); // evaluated for every task: no branch
-                on = on & occ;
-              }
-              sv[j] = tex3d_if(P.tex, q.x, q.y, q.z, on);
-              fetched |= on ? (1u << j) : 0u;
-            }
-          };
-          {
-            float stx = 0.f, sty = P.sstep; // running fp32 sums of the reference: stx += sstep from the clip entry 0
-            float sv0[J], sv1[J];
-            unsigned int f0, f1;
-            issue(stx, sty, live, sv0, f0);
-            // one lattice step: the fetches of the NEXT interval go out (into `nxt`), then the current one (`cur`, issued one
-            // step earlier) is classified
-            auto lattice_step = [&](float (&cur)[J], unsigned int fcur, float (&nxt)[J], unsigned int& fnxt) {
-              const float nsty = sty + P.sstep;
-              unsigned int geo = 0u; // tasks whose ray has a next interval [sty, min(st1, nsty)]
-#pragma unroll
-              for (int j = 0; j < J; j++) geo |= fminf(st1[j], nsty) > sty ? (1u << j) : 0u;
-              geo &= live;
-              issue(sty, nsty, geo, nxt, fnxt); // in flight while the current step is classified; unused if the ray ends here
-              const unsigned int cls = live & fcur;
-              c_shadow += (unsigned int)__popc(cls);
-              unsigned int ert = 0u;
-#pragma unroll
-              for (int j = 0; j < J; j++) {
-                const float a = alpha_lookup<POW2>(P, apair_base, cur[j]);
-                // (1 - A) *= (1 - a)^(base * dt): opacity correction + compositing of the reference, in the log domain
-                const float v = __fmaf_rn(P.base * (fminf(st1[j], sty) - stx), lg2_fast(fmaxf(1.f - a, 0.f)), slog[j]);
-                slog[j] = ((cls >> j) & 1u) ? v : slog[j];
-                ert |= slog[j] > P.log_ert ? (1u << j) : 0u;
-              }
-              live = geo & ert;
-              stx = sty, sty = nsty;
-            };
-            // SYNC == 1: one CTA barrier per lattice step, as many steps as the CTA's longest ray needs; a warp whose rays have
-            // all ended skips the body (live stays 0)
-            auto more = [&]() {
-#if B200VR_PHASE_STATS
-              ph_steps++;
-#endif
-              return SYNC == 1 ? (__syncthreads_or(live != 0u) != 0) : (live != 0u);
-            };
-            // The loop is unrolled by two so that the two value arrays swap ROLES instead of contents: with `sv0 = sv1` at the end
-            // of a step the moves waited for the fetches issued at the top of the same step (profiles/r2h: 20 % of all stall
-            // samples sat on those MOVs), which made the pipeline one step shallower than written.
-            for (;;) {
-              if (!more()) break;
-              if (!(SYNC == 1 && live == 0u)) lattice_step(sv0, f0, sv1, f1);
-              if (!more()) break;
-              if (!(SYNC == 1 && live == 0u)) lattice_step(sv1, f1, sv0, f0);
-            }
-          }
-          QC_PHASE(ph_lattice);
-          // ---- C. tasks off the shared lattice, one at a time (rare): result through the task's slot ----
-          const unsigned int was_odd = odd;
-          while (odd != 0u) {
-            const int j = __ffs(odd) - 1;
-            odd &= odd - 1u;
-            const unsigned int slot = my_slot0 + 1024u * (unsigned)j;
-            const float4 q0 = lds_f32x4(slot);
-            const f3 p = mk3(q0.x, q0.y, q0.z);
-            float sl = 0.f, stx, st;
-            if (clip_shadow_p(P, p, stx, st)) {
-              float sty = fminf(st, stx + P.sstep);
-              while (sty > stx && sl > P.log_ert) {
-                const float tm = 0.5f * (stx + sty);
-                const f3 q = mk3(__fmaf_rn(tm, P.sh_d.x, p.x), __fmaf_rn(tm, P.sh_d.y, p.y), __fmaf_rn(tm, P.sh_d.z, p.z));
-                if (!SKIP || occ_bit<OCCS>(P, occ_base, pad_index_floor(P, q))) {
-                  c_shadow++;
-                  const float a = alpha_lookup<POW2>(P, apair_base, tex3D<float>(P.tex, q.x, q.y, q.z));
-                  sl = __fmaf_rn(P.base * (sty - stx), lg2_fast(fmaxf(1.f - a, 0.f)), sl);
-                }
-                stx = sty;
-                sty = fminf(st, sty + P.sstep);
-              }
-            }
-            asm volatile("st.shared.f32 [%0], %1;" : : "r"(slot + 20u), "f"(sl) : "memory");
-          }
-          // ---- D. gradient, normals, shading (shaders_raymarching.cu:126-169): the 3 J gradient fetches first, then the arithmetic ----
-          float gx[J], gy[J], gz[J];
-#pragma unroll
-          for (int j = 0; j < J; j++) {
-            gx[j] = gy[j] = gz[j] = 0.f;
-            if (j * 32 + lane < n) {
-              const float4 q0 = lds_f32x4(my_slot0 + 1024u * (unsigned)j);
-              // compute_volume_gradient_object_space (shaders_common.h:195-215): forward differences, step 1/dims
-              const float sx_ = q0.x + P.rdim.x > 1.f ? -P.rdim.x : P.rdim.x;
-              const float sy_ = q0.y + P.rdim.y > 1.f ? -P.rdim.y : P.rdim.y;
-              const float sz_ = q0.z + P.rdim.z > 1.f ? -P.rdim.z : P.rdim.z;
-              gx[j] = tex3D<float>(P.tex, q0.x + sx_, q0.y, q0.z);
-              gy[j] = tex3D<float>(P.tex, q0.x, q0.y + sy_, q0.z);
-              gz[j] = tex3D<float>(P.tex, q0.x, q0.y, q0.z + sz_);
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < J; j++) {
-            if (j * 32 + lane < n) {
-              const unsigned int slot = my_slot0 + 1024u * (unsigned)j;
-              const float4 q0 = lds_f32x4(slot), q1 = lds_f32x4(slot + 16u);
-              const float s = q0.w, w = q1.x;
-              const float sl = ((was_odd >> j) & 1u) ? q1.y : slog[j];
-              c_shaded++;
-              const f3 rgb = color_global<POW2>(P, s);
-              const float sx_ = q0.x + P.rdim.x > 1.f ? -P.rdim.x : P.rdim.x;
-              const float sy_ = q0.y + P.rdim.y > 1.f ? -P.rdim.y : P.rdim.y;
-              const float sz_ = q0.z + P.rdim.z > 1.f ? -P.rdim.z : P.rdim.z;
-              // shading normals: v * rsqrt.approx(|v|^2) as in shade_task(); the zero-gradient case gives NaN -> clamp -> 0
-              const f3 normal_o = -normalize3_fast(mk3((gx[j] - s) * rcp_fast(sx_), (gy[j] - s) * rcp_fast(sy_), (gz[j] - s) * rcp_fast(sz_)));
-              const f3 normal_w = normalize3_fast(xfm_vector(P.wto_t, normal_o));
-              const f3 normal_c = normalize3_fast(xfm_vector(P.wtc, normal_w));
-              const float cosNL = fabsf(dot3(P.light_dir, normal_w));
-              const float k_sh = 0.5f + ((0.5f * cosNL) * 2.f) * ex2_fast(sl); // light_rgb = 2; 1 - shadow.alpha = 2^slog
-              const f3 cC = clamp01(rgb * k_sh) * w, cG = clamp01(normal_c) * w; // shaders_raymarching.cu:156-165
-              sts_f32x4(slot, make_float4(cC.x, cC.y, cC.z, cG.x));
-              sts_f32x4(slot + 16u, make_float4(cG.y, cG.z, 0.f, 0.f));
-            }
-          }
+#include "march_qc_pass.inc"
           __syncwarp();
           // every pixel adds its own samples' contributions in march order (= slot order)
 #pragma unroll

@@ -188,6 +188,7 @@ VARIANT_OPTIONS = [
     {"kernel": "qc4"}, {"kernel": "qc4", "occ_smem": 0}, {"kernel": "qc6"}, {"kernel": "qc8"}, {"kernel": "qc8", "occ_smem": 0, "tile_order": 7},
     {"kernel": "qg6"}, {"kernel": "qd6"}, {"kernel": "qd6", "occ_smem": 0}, {"kernel": "qd6", "occ_smem": 0, "tile_order": 0}, {"kernel": "qg6", "max_ctas_per_sm": 1},
     {"kernel": "ring"}, {"kernel": "ring", "occ_smem": 0}, {"kernel": "ring", "occ_smem": 0, "tile_order": 7},
+    {"kernel": "rq6"}, {"kernel": "rq6", "occ_smem": 0}, {"kernel": "rq6", "occ_smem": 0, "ring_high": 1}, {"kernel": "rq6", "ring_high": 64},
 ]
 
 
@@ -203,8 +204,8 @@ def test_every_shading_kernel_variant_matches_the_oracle(scene):
     o_rgba, o_grad, o_cnt = pyoracle.OracleScene(d, skip_empty=True).render_march()
     base = None
     for opts in VARIANT_OPTIONS:
-        for k in ("kernel", "occ_smem", "tile_order", "sheet_px", "max_ctas_per_sm"):
-            r.set_option(k, opts.get(k, {"kernel": "auto", "occ_smem": -1, "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0}[k]))
+        for k in ("kernel", "occ_smem", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high"):
+            r.set_option(k, opts.get(k, {"kernel": "auto", "occ_smem": -1, "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0, "ring_high": 4}[k]))
         r.render()
         rgba, grad = r.download()
         st = dict(r.last_stats)
@@ -216,7 +217,7 @@ def test_every_shading_kernel_variant_matches_the_oracle(scene):
             continue
         for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
             assert st[k] == base[2][k], (opts, k)
-        if opts["kernel"] == "ring":
+        if opts["kernel"] in ("ring", "rq6"):
             assert max_abs(rgba, base[0]) < 1e-4 and max_abs(grad, base[1]) < 1e-4, opts
         else:
             assert np.array_equal(rgba.view(np.uint32), base[0].view(np.uint32)), opts
@@ -274,22 +275,24 @@ def test_path_tracing_matches_oracle_statistically():
     r.close()
 
 
-def test_sort_first_tiles_reassemble_bit_exact():
-    """Partitioned launches use the work-sharing ring kernel (integer per-pixel sums: independent of who shades what and in
-    which order), the undivided frame the queue kernel (float sums in march order). Against the ring kernel on the whole
-    frame the reassembled tiles are bit-identical; against the queue kernel they differ by summation rounding only."""
+@pytest.mark.parametrize("ring_kernel", ["ring", "rq6", "auto"])
+def test_sort_first_tiles_reassemble_bit_exact(ring_kernel):
+    """Partitioned launches use a work-sharing ring kernel (integer per-pixel sums: independent of who shades what and in
+    which order; by default march_rq.cuh), the undivided frame the queue kernel (float sums in march order). Against the same ring
+    kernel on the whole frame the reassembled tiles are bit-identical; against the queue kernel they differ by summation rounding
+    only."""
     import torch
     W, H = 200, 120
     sc = S.noise_scene(48, tf="sparse", camera="oblique")
     r = make_renderer(sc, W, H)
     r.render()
     full_q = r.download()[0].copy()
-    r.set_option("kernel", "ring")
+    r.set_option("kernel", "rq6" if ring_kernel == "auto" else ring_kernel)
     r.render()
     full = r.download()[0].copy()
     r.render()
     assert np.array_equal(r.download()[0].view(np.uint32), full.view(np.uint32))   # deterministic run to run
-    r.set_option("kernel", "auto")
+    r.set_option("kernel", ring_kernel)   # auto: what a partition gets by default
     # 30-bit fixed-point contributions, then C / A: pixels with a tiny opacity amplify the 2^-31 quantisation
     assert max_abs(full, full_q) < 1e-4
     L = capi.lib()
@@ -298,6 +301,7 @@ def test_sort_first_tiles_reassemble_bit_exact():
     for rank in range(nranks):
         L.b200vr_set_tile_partition(r.handle, rank, nranks)
         r.render()
+        assert r.last_kernel.startswith("raymarch_ring_kernel" if ring_kernel == "ring" else "raymarch_rq_kernel"), r.last_kernel
         n = L.b200vr_tile_slice_floats(r.handle, rank, nranks)
         buf = torch.empty(n, dtype=torch.float32, device="cuda")
         r._ck(L.b200vr_pack_tiles(r.handle, C.c_void_p(buf.data_ptr())))
@@ -311,6 +315,31 @@ def test_sort_first_tiles_reassemble_bit_exact():
     r.close(), disp.close()
 
 
+def test_rq_kernel_is_identical_whoever_shades():
+    """march_rq.cuh (rings carrying depth-blocked passes): the frame does not depend on who shades which block -- run to run, with
+    the rings always full (ring_high = 1: nearly everything shaded by the marching warp) or always hungry (64: everything
+    published). Partitions: test_sort_first_tiles_reassemble_bit_exact[rq6]."""
+    W, H = 200, 120
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    r = make_renderer(sc, W, H)
+    r.set_option("kernel", "ring")
+    r.render()
+    ring = r.download()[0].copy()
+    r.set_option("kernel", "rq6")
+    frames = []
+    for high in (4, 4, 1, 64):
+        r.set_option("ring_high", high)
+        r.render()
+        assert r.last_kernel.startswith("raymarch_rq_kernel")
+        frames.append(tuple(a.copy() for a in r.download()))
+    for f in frames[1:]:
+        assert np.array_equal(f[0].view(np.uint32), frames[0][0].view(np.uint32))
+        assert np.array_equal(f[1].view(np.uint32), frames[0][1].view(np.uint32))
+    # same fixed-point sums as the one-task-per-lane rings; the per-task arithmetic is march_qc.cuh's (a few ulp apart)
+    assert max_abs(frames[0][0], ring) < 1e-4
+    r.close()
+
+
 @pytest.mark.parametrize("spp,accumulate", [(1, False), (3, True)])
 def test_ring_kernel_matches_queue_kernel(spp, accumulate):
     """Same frames through both shading kernels: samples, counters and images agree (images up to summation rounding),
@@ -318,7 +347,7 @@ def test_ring_kernel_matches_queue_kernel(spp, accumulate):
     W, H = 192, 108
     sc = S.noise_scene(64, tf="sparse", camera="oblique")
     frames = {}
-    for kern in ("q", "ring"):
+    for kern in ("q", "ring", "rq6"):
         os.environ["B200VR_KERNEL"] = kern
         try:
             r = make_renderer(sc, W, H, spp=spp, accumulate=accumulate)
@@ -329,10 +358,11 @@ def test_ring_kernel_matches_queue_kernel(spp, accumulate):
         finally:
             del os.environ["B200VR_KERNEL"]
     (a_rgba, a_grad), a_st = frames["q"]
-    (b_rgba, b_grad), b_st = frames["ring"]
-    for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
-        assert a_st[k] == b_st[k], k
-    assert max_abs(a_rgba, b_rgba) < 1e-4 and max_abs(a_grad, b_grad) < 1e-4   # 2^-31 quantisation / tiny pixel opacity
+    for kern in ("ring", "rq6"):
+        (b_rgba, b_grad), b_st = frames[kern]
+        for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
+            assert a_st[k] == b_st[k], (kern, k)
+        assert max_abs(a_rgba, b_rgba) < 1e-4 and max_abs(a_grad, b_grad) < 1e-4, kern   # 2^-31 quantisation / tiny pixel opacity
 
 
 def test_sort_last_bricks_composite_to_the_full_image():
@@ -581,6 +611,8 @@ EDGE_CASES = [
     ("tf-100-entries-none", (48, 48, 48), 100, (1.0, 1.0, 1.0), capi.SHADING_NONE, None),
     ("anisotropic-ref", (40, 64, 24), 256, (1.0, 0.5, 2.0), capi.SHADING_REF, None),
     ("ring-kernel-ref", (64, 40, 56), 1024, (1.0, 1.0, 1.0), capi.SHADING_REF, "ring"),
+    ("rq-kernel-ref", (64, 40, 56), 1024, (1.0, 1.0, 1.0), capi.SHADING_REF, "rq6"),
+    ("rq-kernel-tf-100", (48, 48, 48), 100, (1.0, 1.0, 1.0), capi.SHADING_REF, "rq6"),
 ]
 
 
@@ -648,7 +680,9 @@ def _check_mask_against_oracle(got, want, p, table, tile, fi, w, h):
 
 
 SPARSE_GPU_CASES = [
-    # name, shading, path tracing, sampler  ("ref-ring": the default for shaded sparse frames; "ref-queue": B200VR_KERNEL=q)
+    # name, shading, path tracing, sampler  ("ref-rq": the default for shaded sparse frames, march_rq.cuh; "ref-ring" / "ref-queue":
+    # B200VR_KERNEL=ring / q)
+    ("ref-rq", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
     ("ref-ring", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
     ("ref-queue", capi.SHADING_REF, False, capi.SAMPLER_TEX3D),
     ("none-lean", capi.SHADING_NONE, False, capi.SAMPLER_TEX3D),
@@ -665,9 +699,9 @@ def test_sparse_sampling_renders_exactly_the_masked_pixels(case):
     name, shading, path, sampler = case
     W, H, tile = 203, 117, 16  # ragged: not multiples of the 8x4 / 64x32 tiles
     sc = S.noise_scene(48, tf="pt" if path else "sparse", camera="front" if path else "oblique")
-    # shaded sparse frames go through the work-sharing ring kernel (fixed-point per-pixel sums: bit-identical for any split of
+    # shaded sparse frames go through a work-sharing ring kernel (fixed-point per-pixel sums: bit-identical for any split of
     # the work, within 1e-3 of the queue kernel); the dense frame to compare with comes from the same kernel
-    force = {"ref-ring": "ring", "ref-queue": "q"}.get(name)
+    force = {"ref-rq": "rq6", "ref-ring": "ring", "ref-queue": "q"}.get(name)
     if force:
         os.environ["B200VR_KERNEL"] = force
     try:

@@ -218,8 +218,8 @@ def test_renderbatch_on_a_device_group(tmp_path):
     """Multi-GPU behind the plugin (OVR_B200_GPUS, read the way the reference hands device-private options to its devices:
     MainRenderer::init(argc, argv), ovr/renderer.h:252): a group of two members -- the same GPU twice on a one-GPU box, GPUs 0 and 1
     where there are two -- splits the frame sort-first and assembles it in member 0's buffers. With the same kernel on both sides
-    the PNG is byte-identical to the single-device one; with the default kernels (work-sharing rings for a partition of a small
-    volume) it differs by summation rounding only."""
+    the PNG is byte-identical to the single-device one; with the default kernels (work-sharing rings for a partition) it
+    differs by summation rounding only."""
     import torch
     W, H, n = 200, 120, 48
     path, vol = write_scene(tmp_path, n=n)

@@ -1,7 +1,7 @@
 """Run under torchrun with N >= 2 GPUs (one rank per GPU, NCCL): checks both multi-GPU paths against a single-GPU render
 of the same scene on rank 0 and prints one JSON line.
 
-  sort-first  gathered frame must be BIT-IDENTICAL to the single-GPU frame of the same (ring) kernel, and within 1e-3 of the
+  sort-first  gathered frame must be BIT-IDENTICAL to the single-GPU frame of the same (ring, march_rq.cuh) kernel, and within 1e-3 of the
               queue kernel's frame (2^-31 fixed-point contributions, amplified by 1 / A at nearly transparent pixels)
   sort-last   N brick volumes (own voxels + ghosts), global sample lattice, binary swap over NCCL, un-premultiplied on rank 0:
               max-abs <= 1/255 and PSNR >= 45 dB against the single-GPU render of the whole volume
@@ -47,7 +47,7 @@ def main():
     if rank == 0:
         r.render()
         want_q = r.download(want_grad=False)[0].copy()     # undivided frame, queue kernel (float sums in march order)
-        r.set_option("kernel", "ring")                     # undivided frame, ring kernel: what the partitions must reproduce bit for bit
+        r.set_option("kernel", "rq6")                      # undivided frame, ring kernel: what the partitions must reproduce bit for bit
         r.render()
         want = r.download(want_grad=False)[0].copy()
         r.set_option("kernel", "auto")
