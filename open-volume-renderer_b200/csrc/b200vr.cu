@@ -46,6 +46,8 @@ struct Tuning {
   int sheet_px = 8;         // width of a sheet strip in pixels (TILE_ORDER_SHEET)
   int max_ctas_per_sm = 0;  // 0: as many as fit
   int ring_high = 4;        // blocks kept ready per CTA for warps that have run out of tiles (march_ring.cuh)
+  int rq_self = 1;          // march_rq.cuh: blocks of one tile its warp shades itself before it only publishes
+  int rq_cap = 128;          // march_rq.cuh: slots per ring (power of two)
   int occ_smem = -1;        // macrocell occupancy mask in shared memory: -1 when it fits (march_q.cuh Q_OCC_SMEM_WORDS), 0 never
   int carveout = -1;        // cudaFuncAttributePreferredSharedMemoryCarveout in percent; -1: just what the launch needs
   int tex_native8 = 1;      // 8-bit volumes stay 8-bit 3-D arrays
@@ -180,7 +182,7 @@ static int grid_for(size_t n, int threads, int sm_count)
 }
 
 // ---- tuning options -------------------------------------------------------------------------------------------------
-static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "occ_smem", "carveout",
+static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap", "occ_smem", "carveout",
                                             "tex_native8", "debug_tiles" };
 
 static int apply_option(b200vr_t* h, const std::string& name, const char* value)
@@ -211,6 +213,11 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   }
   else if (name == "max_ctas_per_sm") t.max_ctas_per_sm = (int)std::max(0l, v);
   else if (name == "ring_high") t.ring_high = (int)std::max(1l, v);
+  else if (name == "rq_self") t.rq_self = (int)std::max(0l, v);
+  else if (name == "rq_cap") {
+    if (v < 32 || v > 1024 || (v & (v - 1))) return fail(h, B200VR_EINVAL, "set_option: rq_cap is a power of two in 32..1024");
+    t.rq_cap = (int)v;
+  }
   else if (name == "occ_smem") t.occ_smem = v == 0 ? 0 : -1;
   else if (name == "carveout") {
     if (v < -1 || v > 100) return fail(h, B200VR_EINVAL, "set_option: carveout is -1 or a percentage");
@@ -902,7 +909,7 @@ static KernelChoice pick_kernel(const b200vr_t* h)
       else if (rq6) {
         k.fn = B200VR_PICK(B200VR_K_RQ6, skip, pow2, occs);
         k.ring = true, k.ring_block = rq_block_float4<6>();
-        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>() + rq_acc_bytes(), k.name = "raymarch_rq_kernel<J=6>";
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<6>(), k.name = "raymarch_rq_kernel<J=6>";
       }
       else if (force == KERNEL_QB2) {
         k.fn = B200VR_PICK(B200VR_K_QB2, skip, pow2, occs);
@@ -1390,7 +1397,7 @@ static int render_enqueue(b200vr_t* h)
     if (rc != B200VR_OK) return rc;
   }
   if (kc.ring_block != RING_BLOCK_FLOAT4 && (size_t)h->width * h->height > (size_t)RQ_PIXEL_MASK)
-    return fail(h, B200VR_EINVAL, "render: kernel rq6 takes frames of up to 2^27 - 1 pixels");
+    return fail(h, B200VR_EINVAL, "render: kernel rq6 takes frames of up to 2^31 - 1 pixels");
   const render_kernel_t kernel = kc.fn;
   const size_t smem = kc.smem;
   int per_sm = 0;
@@ -1439,7 +1446,8 @@ static int render_enqueue(b200vr_t* h)
   if (kc.ring && P.n_warp_tiles > 0) {
     // one ring per CTA: high-water mark + one block in flight per warp of the CTA + slack, as a power of two
     P.ring_high = h->tune.ring_high;
-    int cap = 32;
+    P.rq_self = h->tune.rq_self;
+    int cap = kc.ring_block != RING_BLOCK_FLOAT4 ? h->tune.rq_cap : 32;
     while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
     if (cap != h->ring_cap || grid != h->ring_count || kc.ring_block != h->ring_block) {
       CK(cudaStreamSynchronize(h->stream));
@@ -1536,6 +1544,12 @@ static int render_wait(b200vr_t* h, b200vr_stats* stats)
                  c.tile_clocks_max * 1e-3, c.tile_clocks_sum * 1e-6, warps, c.tile_clocks_sum * 1e-3 / warps);
     std::fprintf(stderr, "[b200] ring: longest warp %.0f kclk, after the last tile %.0f kclk per warp, blocks published %llu, taken by draining warps %llu\n",
                  c.warp_clocks_max * 1e-3, c.drain_clocks_sum * 1e-3 / warps, c.blocks_published, c.blocks_stolen);
+    if (h->last_kernel.rfind("raymarch_rq_kernel", 0) == 0) {
+      std::fprintf(stderr, "[b200] rq: longest tile %.0f kclk, started %.0f kclk into the launch: %llu march iterations, %llu blocks published (%.0f kclk), "
+                           "%llu shaded by itself (%.0f kclk)\n", c.dbg[0] * 1e-3, c.dbg[7] * 1e-3, c.dbg[1], c.dbg[2], c.dbg[5] * 1e-3, c.dbg[3], c.dbg[6] * 1e-3);
+      std::fprintf(stderr, "[b200] rq: of the time after the last tile, waiting for blocks %.0f kclk per warp\n", c.delta_samples * 1e-3 / warps);
+      c.delta_samples = 0;
+    }
   }
   if (stats) {
     float ms = 0.f;

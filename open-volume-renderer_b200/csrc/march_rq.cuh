@@ -1,49 +1,44 @@
 // Ray-march kernel with gradient + shadow shading, seventh generation: the work-sharing rings of march_ring.cuh carrying the
-// depth-blocked shading passes of march_qc.cuh -- for sort-first partitions of volumes far larger than L2.
+// depth-blocked shading passes of march_qc.cuh -- for sort-first partitions and sparse (foveated) frames.
 //
-// Why (profiles/r2s_partition_C3.jsonl, r2y_phase_stats.txt): a launch lasts about its mean load plus its longest tile, and a tile is
-// one serial chain of ~2000-clock steps -- 25 primary iterations to fill the queue, then a pass of 28 lattice steps, a dozen times for
-// the heavy tiles of C3: ~1.1 ms. An eighth of the C3 frame is worth 0.77 ms of fetches and took 2.3 ms, with march_qc.cuh and with
-// the one-task-per-lane rings alike (the latter move the shading off the chain but shade at 10.96 instead of 6.14 ms per frame).
-// Here a marching warp that has J x 32 tasks staged publishes them as ONE block of J KB to its CTA's ring when fewer than
-// `ring_high` blocks wait there, and keeps marching; otherwise it shades them itself with the pass of march_qc.cuh (included
-// textually: the same statements). Warps that have run out of tiles take blocks from any ring, copy them into their own (idle)
-// staging slots and run the same pass. In the bulk of the launch the rings stay full and every warp works for itself; at the tail
-// the heavy tiles cost their primary march only.
+// Why (profiles/r2s_partition_C3.jsonl, r2y_phase_stats.txt): a launch lasts about its mean load plus its longest tile, and a tile
+// is one serial chain of ~2000-clock steps -- 25 march iterations to fill the queue, then a pass of 28 lattice steps, a dozen
+// times and more for the heavy tiles of C3. An eighth of the C3 frame is worth 0.77 ms of fetches and took 2.23 ms with
+// march_qc.cuh, and as long with the one-task-per-lane rings (they move the shading off the chain but shade at 10.96 instead of
+// 6.14 ms per frame). Here a marching warp that has J x 32 tasks staged either shades them itself with the pass of march_qc.cuh
+// (included textually: the same statements) or publishes them as ONE block of J KB to its CTA's ring and keeps marching. Warps
+// that have run out of tiles take blocks from any ring, copy them into their own (idle) staging slots and run the same pass.
+// Who shades: the warp itself while `ring_high` blocks are ready in its ring (nobody is short of work), but only the first
+// `rq_self` blocks of a tile -- a tile that goes on filling blocks is one of the heavy ones, the launch ends when the heaviest has
+// marched AND shaded, and its later blocks are better left in the ring (`rq_cap` slots) for the first warp that runs dry.
+// Measured, an eighth of C3 / of C2 on one B200 (profiles/r3a_*): 1.18 / 0.67 ms, against 2.23 (march_qc.cuh) / 1.03 ms (rings of
+// single tasks). What is left is the march of the longest tile itself: ~600 iterations of one memory round trip each.
 //
-// As in march_ring.cuh a consumer does not know the pixel's other samples: contributions go to per-pixel fixed-point sums with
-// fire-and-forget 64-bit reductions (order-independent: the frame is deterministic and identical for every partition) and
-// resolve_kernel finishes the pixel. A warp that shades its own tile's tasks adds them, in the same fixed point, to six words per
-// pixel in shared memory first and sends three reductions per pixel when the tile ends: one reduction per task and word was
-// 1 ms of L2 atomics on a whole C3 frame (7.18 against 6.15 ms for march_qc.cuh). Integer sums: the frame stays bit-identical
-// whoever shades what. The ring protocol (tickets, per-slot sequence words, bounded waits, error word) is march_ring.cuh's; only
-// the block size differs. Task slot: [0] p.xyz [12] s [16] w [28] pixel index | owning lane << 27.
+// As in march_ring.cuh a consumer does not know the pixel's other samples: every task's contribution goes to per-pixel fixed-point
+// sums with fire-and-forget 64-bit reductions (integers: the frame is deterministic, identical whoever shades what and for every
+// partition) and resolve_kernel finishes the pixel. The ring protocol (tickets, per-slot sequence words, bounded waits, error
+// word) is march_ring.cuh's with blocks of J KB; warps without work watch one word pair (blocks available anywhere, warps still
+// marching) instead of scanning every ring. Task slot: [0] p.xyz [12] s [16] w [28] pixel index.
+//
+// Measured and not kept (profiles/r3a_rq_experiments.md): per-pixel sums of a warp's own tile in shared memory with one reduction
+// set per tile (the 6 KB push the carve-out up a step, L1 shrinks: 7.55 against 7.18 ms per C3 frame) or in registers as in
+// march_qc.cuh (102 B of spills: 8.80 ms) -- the reductions themselves cost 0.16 ms; only two helper warps per CTA; four lattice
+// samples of a ray fetched together once the tiles have run out or for heavy tiles (2.1 useful steps per iteration on C3's cells,
+// 25 % more time where it is used, no shorter launch); the march step as one more branch of the state machine instead of a loop
+// of its own (ptxas then waits for the prefetched sample at the back edge: 3400 instead of 2100 clocks per iteration).
 #pragma once
 #include "march_qc.cuh"
 #include "march_ring.cuh"
 
-// How a marching warp adds the contributions of the tasks it shaded itself to the pixels' sums (consumers of published blocks
-// always send one reduction per task and word pair). 0: reductions per task as well; 1: fixed-point sums per pixel in shared
-// memory, three reductions per pixel at the end of the tile; 2: nothing (timing experiments only: wrong image); 3: the owning
-// lane collects its tasks' results in registers as in march_qc.cuh, three reductions per pixel at the end of the tile.
-#ifndef B200VR_RQ_ACC
-#define B200VR_RQ_ACC 0
-#endif
-
 namespace b200k {
 
 template<int J> __host__ __device__ constexpr int rq_block_float4() { return J * RING_BLOCK_FLOAT4; }
-constexpr int RQ_LANE_SHIFT = 27;                                   // task word [28]: pixel index | owning lane << 27
-constexpr unsigned int RQ_PIXEL_MASK = (1u << RQ_LANE_SHIFT) - 1u;  // frames of up to 2^27 - 1 pixels
-// Warps per CTA that stay to shade published blocks once they have run out of tiles; the others leave. At the tail of a launch
-// the supply of blocks is what the few warps still marching publish -- about one block per pass time each -- plus the backlog
-// of ring_high blocks per ring.
+constexpr unsigned int RQ_PIXEL_MASK = 0x7fffffffu; // task word [28]: pixel index; RING_NO_PIXEL marks an empty slot of a block
+// Warps per CTA that stay to shade published blocks once they have run out of tiles; the others leave (8 = all: measured best)
 #ifndef B200VR_RQ_HELPERS
 #define B200VR_RQ_HELPERS 8
 #endif
 constexpr int RQ_HELPERS = B200VR_RQ_HELPERS;
-constexpr int RQ_ACC_WORDS = 6;                                     // C.xyz, G.xyz
-__host__ __device__ constexpr size_t rq_acc_bytes() { return B200VR_RQ_ACC == 1 ? (size_t)(QC_THREADS / 32) * 32 * RQ_ACC_WORDS * sizeof(unsigned int) : 0; }
 
 template<bool SKIP, bool POW2, bool OCCS, int J>
 __global__ void __launch_bounds__(QC_THREADS, QC_MIN_CTAS)
@@ -58,21 +53,12 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
   const unsigned int occ_base = pin_u32(apair_base + (unsigned int)q_alpha_bytes(P.n_alpha));
   const unsigned int queue_base = pin_u32(occ_base + (unsigned int)(OCCS ? q_occ_bytes(P.occ_words) : 0) +
                                           (unsigned int)warp * (unsigned int)(qb_slots<J>() * Q_SLOT_FLOATS * sizeof(float)));
-  // this warp's per-pixel sums of the tile in flight: word k of lane l at [k * 32 + l]
-  unsigned int* const s_lacc = reinterpret_cast<unsigned int*>(smem + q_alpha_bytes(P.n_alpha) + (OCCS ? q_occ_bytes(P.occ_words) : 0) +
-                                                               (size_t)(QC_THREADS / 32) * qb_slots<J>() * Q_SLOT_FLOATS * sizeof(float)) +
-                               warp * 32 * RQ_ACC_WORDS;
-  (void)s_lacc;
   if (SKIP && OCCS)
     for (int i = threadIdx.x; i < P.occ_words; i += blockDim.x) s_occ[i] = P.occ_bits[i];
   for (int i = threadIdx.x; i <= P.n_alpha; i += blockDim.x) {
     const float v0 = P.tf_alpha[min(i, P.n_alpha - 1)], v1 = P.tf_alpha[min(i + 1, P.n_alpha - 1)];
     s_apair[i] = make_float2(v0, (v1 - v0) * (1.f / 256.f));
   }
-#if B200VR_RQ_ACC == 1
-#pragma unroll
-  for (int k = 0; k < RQ_ACC_WORDS; k++) s_lacc[k * 32 + lane] = 0u;
-#endif
   __syncthreads();
   const int my_ring = (int)blockIdx.x, n_rings = (int)gridDim.x;
   unsigned int* const r_head = P.ring_ctrl + my_ring * RING_CTRL_PER_RING, * const r_tail = r_head + RING_CTRL_STRIDE;
@@ -101,14 +87,14 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
   f3 od = mk3(0.f);
   float tx = 0.f, ty = 0.f, t1 = 0.f, A = 0.f, cell_exit = -1.f, s_pre = 0.f;
   int count = 0; // tasks staged (warp-uniform)
+  int self_blocks = 0; // blocks of the tile in flight this warp shaded itself
   unsigned int idle_spins = 0, idle_ns = 256u;
-#if B200VR_RQ_ACC == 3
-  unsigned int mine[J + 1]; // staging slots holding this pixel's tasks, 32 per word
-  unsigned int lacc[RQ_ACC_WORDS]; // this pixel's sums over the tasks its own warp shaded
-#pragma unroll
-  for (int g = 0; g <= J; g++) mine[g] = 0u;
-#pragma unroll
-  for (int k = 0; k < RQ_ACC_WORDS; k++) lacc[k] = 0u;
+#if B200VR_TILE_STATS // diagnostic builds: where the tail of the launch goes (render_wait prints the sums)
+  const long long warp_t0 = clock64();
+  long long drain_t0 = warp_t0, idle_t0 = 0, idle_clk = 0;
+  unsigned int n_pub = 0, n_stolen = 0;
+  unsigned int t_iters = 0, t_pubs = 0, t_local = 0; // of the tile in flight: march iterations, blocks published / shaded here
+  long long t_pub_clk = 0, t_local_clk = 0, t_mark = 0;
 #endif
 
   for (;;) {
@@ -119,6 +105,9 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
       k = __shfl_sync(0xffffffffu, k, 0);
       if (k >= P.n_warp_tiles) {
         marching = false; // everything this warp published is ordered before the decrement by the fence
+#if B200VR_TILE_STATS
+        drain_t0 = idle_t0 = clock64();
+#endif
         if (lane == 0) {
           __threadfence();
           atomicSub(r_head + 2 * RING_CTRL_STRIDE, 1u);
@@ -153,7 +142,11 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
       cell_empty = false;
       have_pre = false;
       count = 0;
+      self_blocks = 0;
       have_tile = true;
+#if B200VR_TILE_STATS
+      t_iters = t_pubs = t_local = 0, t_pub_clk = t_local_clk = 0;
+#endif
       QC_PHASE(ph_other);
       continue;
     }
@@ -163,8 +156,11 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
       // ---- primary samples until J x 32 tasks are staged or every ray of the tile has ended. A loop of its own: with the march
       // step as one more branch of the state machine below, ptxas waited for the prefetched sample at the loop's back edge and an
       // iteration took 3400 instead of 2000 clocks.
-      bool any_alive;
+      bool any_alive = true;
       while ((any_alive = __any_sync(0xffffffffu, alive)) && count < J * 32) {
+#if B200VR_TILE_STATS
+        t_iters++;
+#endif
 #if B200VR_PHASE_STATS
         ph_iters++, ph_lanes += (unsigned int)__popc(__ballot_sync(0xffffffffu, alive));
 #endif
@@ -231,12 +227,7 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
         if (want) {
           const int slot = count + __popc(m & lt_mask);
           sts_f32x4(queue_base + 32u * (unsigned)slot, make_float4(tp.x, tp.y, tp.z, ts));
-          sts_f32x4(queue_base + 32u * (unsigned)slot + 16u, make_float4(tw, 0.f, 0.f, __uint_as_float(pixel_index | ((unsigned)lane << RQ_LANE_SHIFT))));
-#if B200VR_RQ_ACC == 3
-          const unsigned int bit = 1u << (slot & 31);
-#pragma unroll
-          for (int g = 0; g <= J; g++) mine[g] |= (slot >> 5) == g ? bit : 0u; // selects, not a dynamic index: the words stay in registers
-#endif
+          sts_f32x4(queue_base + 32u * (unsigned)slot + 16u, make_float4(tw, 0.f, 0.f, __uint_as_float(pixel_index)));
         }
         __syncwarp();
         count += __popc(m);
@@ -244,9 +235,17 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
       QC_PHASE(ph_primary);
       if (count >= J * 32 || (!any_alive && count > 0)) {
         unsigned int fill = 0;
+#if B200VR_TILE_STATS
+        t_mark = clock64();
+#endif
         if (lane == 0) fill = ld_relaxed_u32(r_head) - ld_relaxed_u32(r_tail);
         fill = __shfl_sync(0xffffffffu, fill, 0);
-        if ((int)fill >= P.ring_high) consume = true; // nobody is waiting for work: shade the staged tasks here
+        // Shade the staged tasks here when nobody is waiting for work (ring_high blocks ready) -- but only the first rq_self blocks
+        // of a tile: a tile that goes on producing blocks is one of the heavy ones, and the launch ends when the heaviest has
+        // marched AND shaded (the longest tile of an eighth of C3: 1.2 Mclk of marching, 1.05 Mclk for the seven of its 21
+        // blocks it shaded itself, of a launch of 2.6 Mclk). Its later blocks wait in the ring for the first warp without a tile.
+        const int room = P.ring_cap - (QC_THREADS / 32) - 8; // every warp of the CTA may hold a ticket
+        if ((int)fill >= room || ((int)fill >= P.ring_high && self_blocks < P.rq_self)) consume = true, self_blocks++;
         else {
           // =================== publish the J x 32 oldest staged tasks as one block ===================
           const int n = min(count, J * 32);
@@ -275,6 +274,10 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
             st_release_u32(my_seq + (t & cap_mask), t + 1u);
             atomicAdd(r_avail, 1u);
           }
+#if B200VR_TILE_STATS
+          n_pub++;
+          t_pubs++;
+#endif
           // move the tasks that did not fit (at most 32) to the front
           const int rest = count - n;
           float4 m0, m1;
@@ -282,39 +285,25 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
           __syncwarp();
           if (lane < rest) sts_f32x4(queue_base + 32u * (unsigned)lane, m0), sts_f32x4(queue_base + 32u * (unsigned)lane + 16u, m1);
           __syncwarp();
-#if B200VR_RQ_ACC == 3
-          {
-            const unsigned int carried = rest > 0 ? mine[J] : 0u;
-#pragma unroll
-            for (int g = 0; g <= J; g++) mine[g] = 0u;
-            mine[0] = carried;
-          }
-#endif
           count = rest;
           QC_PHASE(ph_other);
+#if B200VR_TILE_STATS
+          t_pub_clk += clock64() - t_mark;
+#endif
           continue;
         }
       }
       else if (!any_alive) {
         // ---- tile done: the ray's opacity goes to resolve_kernel directly, colour and normals through the accumulators ----
         if (inside) P.ray_alpha[pixel_index] = A;
-#if B200VR_RQ_ACC == 1 || B200VR_RQ_ACC == 3
-        {
-          // what this warp shaded itself: three reductions per pixel
-          unsigned int v[RQ_ACC_WORDS];
-#pragma unroll
-          for (int k = 0; k < RQ_ACC_WORDS; k++) {
-#if B200VR_RQ_ACC == 1
-            v[k] = s_lacc[k * 32 + lane], s_lacc[k * 32 + lane] = 0u;
-#else
-            v[k] = lacc[k], lacc[k] = 0u;
-#endif
+#if B200VR_TILE_STATS
+        if (lane == 0) {
+          const unsigned long long dt = (unsigned long long)(clock64() - tile_t0);
+          if (dt > atomicMax(&P.counters->dbg[0], dt)) { // the longest so far (last writer wins: good enough for a diagnostic)
+            P.counters->dbg[1] = t_iters, P.counters->dbg[2] = t_pubs, P.counters->dbg[3] = t_local;
+            P.counters->dbg[5] = (unsigned long long)t_pub_clk, P.counters->dbg[6] = (unsigned long long)t_local_clk;
+            P.counters->dbg[7] = (unsigned long long)(tile_t0 - warp_t0);
           }
-          unsigned long long* const acc = P.acc + 3 * (size_t)pixel_index;
-          if (v[0] | v[1]) red_add_u64(acc, (unsigned long long)v[0] | ((unsigned long long)v[1] << 32));
-          if (v[2] | v[3]) red_add_u64(acc + 1, (unsigned long long)v[2] | ((unsigned long long)v[3] << 32));
-          if (v[4] | v[5]) red_add_u64(acc + 2, (unsigned long long)v[4] | ((unsigned long long)v[5] << 32));
-          __syncwarp();
         }
 #endif
         if (lane == 0) tile_cost_add(P, tile_slot, tile_t0);
@@ -406,6 +395,10 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
         __syncwarp();
         if (lane == 0) st_release_u32(c_seq + (t & cap_mask), t + (unsigned int)P.ring_cap);
         QC_PHASE(ph_idle);
+#if B200VR_TILE_STATS
+        n_stolen++;
+        idle_clk += clock64() - idle_t0; // from the end of the previous block (or of the last tile) to having this one
+#endif
       }
       __syncwarp();
       QC_PHASE(ph_other);
@@ -414,50 +407,14 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
 #endif
 #include "march_qc_pass.inc"
       __syncwarp();
-      // every task's contribution to its pixel's fixed-point sums: another warp's tile in global memory, this warp's own as
-      // B200VR_RQ_ACC says
-#if B200VR_RQ_ACC == 3
-      if (marching) {
-        // every pixel collects its own samples' contributions (integers: any order)
-#pragma unroll
-        for (int g = 0; g < J; g++) {
-          unsigned int own = mine[g];
-          const int left = n - g * 32; // slots of this word that were shaded
-          if (left < 32) own = left > 0 ? own & ((1u << left) - 1u) : 0u;
-          while (own) {
-            const int j = __ffs(own) - 1;
-            own &= own - 1u;
-            const unsigned int slot = queue_base + 32u * (unsigned)(g * 32 + j);
-            const float4 r0 = lds_f32x4(slot), r1 = lds_f32x4(slot + 16u);
-            lacc[0] += __float2uint_rn(r0.x * ACC_SCALE), lacc[1] += __float2uint_rn(r0.y * ACC_SCALE), lacc[2] += __float2uint_rn(r0.z * ACC_SCALE);
-            lacc[3] += __float2uint_rn(r0.w * ACC_SCALE), lacc[4] += __float2uint_rn(r1.x * ACC_SCALE), lacc[5] += __float2uint_rn(r1.y * ACC_SCALE);
-          }
-        }
-      }
-      else
-#endif
+      // every task's contribution to its pixel's fixed-point sums
       {
 #pragma unroll
         for (int j = 0; j < J; j++) {
           if (j * 32 + lane < n) {
             const unsigned int slot = my_slot0 + 1024u * (unsigned)j;
             const float4 r0 = lds_f32x4(slot), r1 = lds_f32x4(slot + 16u);
-            const unsigned int pw = __float_as_uint(r1.w);
-#if B200VR_RQ_ACC == 1
-            if (marching) {
-              unsigned int* const a = s_lacc + (pw >> RQ_LANE_SHIFT);
-              atomicAdd(a, __float2uint_rn(r0.x * ACC_SCALE));
-              atomicAdd(a + 32, __float2uint_rn(r0.y * ACC_SCALE));
-              atomicAdd(a + 64, __float2uint_rn(r0.z * ACC_SCALE));
-              atomicAdd(a + 96, __float2uint_rn(r0.w * ACC_SCALE));
-              atomicAdd(a + 128, __float2uint_rn(r1.x * ACC_SCALE));
-              atomicAdd(a + 160, __float2uint_rn(r1.y * ACC_SCALE));
-              continue;
-            }
-#elif B200VR_RQ_ACC == 2
-            if (marching) continue;
-#endif
-            unsigned long long* const acc = P.acc + 3 * (size_t)(pw & RQ_PIXEL_MASK);
+            unsigned long long* const acc = P.acc + 3 * (size_t)__float_as_uint(r1.w);
             red_add_u64(acc, acc_pack(r0.x, r0.y));
             red_add_u64(acc + 1, acc_pack(r0.z, r0.w));
             red_add_u64(acc + 2, acc_pack(r1.x, r1.y));
@@ -472,15 +429,13 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
         __syncwarp();
         if (lane < rest) sts_f32x4(queue_base + 32u * (unsigned)lane, m0), sts_f32x4(queue_base + 32u * (unsigned)lane + 16u, m1);
         __syncwarp();
-#if B200VR_RQ_ACC == 3
-        const unsigned int carried = rest > 0 ? mine[J] : 0u;
-#pragma unroll
-        for (int g = 0; g <= J; g++) mine[g] = 0u;
-        mine[0] = carried;
-#endif
         count = rest;
       }
       QC_PHASE(ph_shade);
+#if B200VR_TILE_STATS
+      idle_t0 = clock64();
+      if (marching) t_local++, t_local_clk += idle_t0 - t_mark;
+#endif
       continue;
     }
   }
@@ -497,6 +452,17 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
   }
 #endif
 
+#if B200VR_TILE_STATS
+  if (lane == 0) {
+    const long long now = clock64();
+    idle_clk += now - idle_t0;
+    atomicAdd(&P.counters->drain_clocks_sum, (unsigned long long)(now - drain_t0));
+    atomicMax(&P.counters->warp_clocks_max, (unsigned long long)(now - warp_t0));
+    atomicAdd(&P.counters->blocks_published, (unsigned long long)n_pub);
+    atomicAdd(&P.counters->blocks_stolen, (unsigned long long)n_stolen);
+    atomicAdd(&P.counters->delta_samples, (unsigned long long)idle_clk); // of the time after the last tile: waiting for blocks
+  }
+#endif
   // executed-sample counters: one atomic set per warp
   const unsigned int n_primary = __reduce_add_sync(0xffffffffu, c_primary), n_shadow = __reduce_add_sync(0xffffffffu, c_shadow);
   const unsigned int n_shaded = __reduce_add_sync(0xffffffffu, c_shaded), n_rays = __reduce_add_sync(0xffffffffu, c_rays);

@@ -18,7 +18,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-DEFAULTS = {"kernel": "auto", "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0, "occ_smem": -1, "carveout": -1, "ring_high": 4}
+DEFAULTS = {"kernel": "auto", "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0, "occ_smem": -1, "carveout": -1, "ring_high": 4, "rq_self": 1, "rq_cap": 128}
 
 
 def main():
