@@ -390,10 +390,18 @@ def run_b200(args):
             launches[0] += sf.launches - n0
             return st
 
+        if isinstance(sf, D.SortFirstP2P) and world > 1:
+            # frames enqueued back to back (b200vr_render_async + the stream-ordered completion all-reduce): the host does not
+            # wait for a frame before it enqueues the next one; the counters of all frames are read once after the timed region
+            step_async = lambda: sf.step(wait=False)   # noqa: E731
+
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if sortlast or not (world > 1 and args.exchange == "p2p"):
+        step_async = None
 
     # ---- device-resident throughput (`value`) ----
     F = max(1, args.frames_per_step)
@@ -408,14 +416,29 @@ def run_b200(args):
     kernel_ms = 0.0
     barrier()
     ev0.record(stream)
-    for _ in range(args.steps * F):
-        st = step()
-        samples += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
-        fetches += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"] + st["gradient_fetches"]
-        kernel_ms += st["ms"]
+    if step_async is None:
+        for _ in range(args.steps * F):
+            st = step()
+            samples += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
+            fetches += st["primary_samples"] + st["shadow_samples"] + st["delta_samples"] + st["gradient_fetches"]
+            kernel_ms += st["ms"]
+    else:
+        for _ in range(args.steps * F):
+            step_async()
     ev1.record(stream)
     barrier()
     clk = clocks.stop()
+    if step_async is not None:
+        st = r.wait()   # counters summed over the frames of the timed region
+        samples = st["primary_samples"] + st["shadow_samples"] + st["delta_samples"]
+        fetches = samples + st["gradient_fetches"]
+        launches[0] = st["kernel_launches"] * args.steps * F
+        # the render kernel's own time per launch (roofline, per-rank table): F more frames, each waited for
+        for _ in range(F):
+            kernel_ms += step()["ms"]
+        kernel_ms *= args.steps
+        launches[0] = st["kernel_launches"] * args.steps * F
+        barrier()
     gpu_launches = launches[0]
     t_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
     tot = torch.tensor([samples, fetches], dtype=torch.float64, device="cuda")
@@ -518,7 +541,7 @@ def run_e2e(ctx, args):
 
 
 KERNEL_OPTION = {"raymarch_q_kernel": "q", "raymarch_ring_kernel": "ring", "raymarch_qc_kernel<J=4>": "qc4", "raymarch_qc_kernel<J=6>": "qc6",
-                 "raymarch_qc_kernel<J=8>": "qc8", "raymarch_rq_kernel<J=6>": "rq6"}
+                 "raymarch_qc_kernel<J=8>": "qc8", "raymarch_rq_kernel<J=6>": "rq6", "raymarch_rq_kernel<J=4>": "rq4", "raymarch_rq_kernel<J=2>": "rq2"}
 
 
 def parity_march(rgba, grad, pix):
@@ -856,7 +879,7 @@ def main():
                 "data": "synthetic",
                 "config": {"workload": workload_name(args, wl), "frames_per_step": F, "sampler": args.sampler, "skip_empty": not args.no_skip,
                            "parallelism": (f"sort-last x{world}: one {n}^3 brick per GPU, binary swap, " + ("blend reads the partner over NVLink peer memory" if args.exchange == "p2p" else "NCCL send/recv") if sortlast_wl else
-                                           f"sort-first x{world}, " + ("tiles stored straight into rank 0's frame over NVLink peer memory" if args.exchange == "p2p"
+                                           f"sort-first x{world}, " + ("tiles stored straight into rank 0's frame over NVLink peer memory, frames enqueued back to back (b200vr_render_async), counters read once after the timed region" if args.exchange == "p2p"
                                                                        else "NCCL gather of tile slices") if world > 1 else "1 GPU"),
                            "l2": f"volume {4 * n ** 3 / 2 ** 20:.0f} MiB > 126 MB L2: inputs larger than L2, no flush",
                            "samples_per_frame": ctx["samples"] / n_frames, "fetches_per_frame": ctx["fetches"] / n_frames},

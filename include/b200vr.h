@@ -190,7 +190,8 @@ int b200vr_sparse_samples_noalloc(b200vr_t* h, const float* noise_dev, int tile_
 /* replaces Impl::render (device_impl.cpp:199-269): one synchronous frame; stats may be NULL */
 int b200vr_render(b200vr_t* h, b200vr_stats* stats);
 /* The same frame without the wait: b200vr_render_async enqueues the frame on the handle's stream and returns;
- * b200vr_wait blocks until the stream is idle and reports the counters of the frame enqueued last (stats may be NULL).
+ * b200vr_wait blocks until the stream is idle and reports the counters summed over the frames enqueued since the last wait
+ * (normally one) and the kernel time and frame index of the last of them (stats may be NULL).
  * b200vr_render == b200vr_render_async + b200vr_wait. For callers that order their own work behind the frame on the same
  * stream (multi-GPU exchange, frame copies) instead of stalling the host once per frame as DeviceOptix7::render does
  * (ovr/devices/optix7/device.cpp:34-43). */
@@ -202,9 +203,9 @@ int b200vr_wait(b200vr_t* h, b200vr_stats* stats);
 const char* b200vr_last_kernel(const b200vr_t* h);
 /* Tuning switches of a handle; none changes what is computed per sample, they pick between kernels / launch orders that
  * render the same frame (A/B runs, tests of every kernel variant). Defaults come from the environment variable
- * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | qd6 | qg6 | ring | legacy | sm),
+ * B200VR_<NAME IN CAPITALS> at b200vr_create. Names: "kernel" (auto | q | qb2 | qb4 | qb8 | qc4 | qc6 | qc8 | qd6 | qg6 | rq2 | rq4 | rq6 | ring | legacy | sm),
  * "tile_order" (-1 auto, 0 rows, 1 centre-out, 2 previous cost, 3 Z-order, 4 | 5 columns, 6 middle rows first, 7 sheets of the
- * light direction), "sheet_px", "max_ctas_per_sm" (0 = all that fit), "ring_high", "occ_smem" (0 = macrocell occupancy mask
+ * light direction), "sheet_px", "max_ctas_per_sm" (0 = all that fit), "ring_high", "rq_self", "rq_cap" (work-sharing rings, csrc/march_rq.cuh), "occ_smem" (0 = macrocell occupancy mask
  * read from global memory even when it would fit in shared memory), "carveout" (shared-memory carve-out in percent, -1 =
  * driver's choice), "tex_native8" (0 = 8-bit volumes held as fp32 arrays), "debug_tiles". Values are decimal integers
  * except for "kernel". */

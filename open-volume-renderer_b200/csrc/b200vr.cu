@@ -36,7 +36,7 @@ thread_local std::string g_create_error;
 
 // Tuning switches of one handle (b200vr_set_option; defaults from the environment at b200vr_create). None of them changes
 // what is computed per sample; they choose between kernels / launch orders that render the same frame.
-enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RQ6, KERNEL_RING, KERNEL_LEGACY,
+enum { KERNEL_AUTO = 0, KERNEL_Q, KERNEL_QB2, KERNEL_QB4, KERNEL_QB8, KERNEL_QC4, KERNEL_QC6, KERNEL_QC8, KERNEL_QG6, KERNEL_QD6, KERNEL_RQ6, KERNEL_RQ2, KERNEL_RQ4, KERNEL_RING, KERNEL_LEGACY,
        KERNEL_SM };
 enum { TILE_ORDER_AUTO = -1, TILE_ORDER_ROWS = 0, TILE_ORDER_CENTRE = 1, TILE_ORDER_COST = 2, TILE_ORDER_Z = 3, TILE_ORDER_COLS_UP = 4,
        TILE_ORDER_COLS_DOWN = 5, TILE_ORDER_MIDDLE_ROWS = 6, TILE_ORDER_SHEET = 7 };
@@ -190,13 +190,13 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   Tuning& t = h->tune;
   if (name == "kernel") {
     static const std::pair<const char*, int> names[] = { { "auto", KERNEL_AUTO }, { "q", KERNEL_Q }, { "qb2", KERNEL_QB2 }, { "qb4", KERNEL_QB4 },
-                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "rq6", KERNEL_RQ6 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
+                                                         { "qb8", KERNEL_QB8 }, { "qc4", KERNEL_QC4 }, { "qc6", KERNEL_QC6 }, { "qc8", KERNEL_QC8 }, { "qg6", KERNEL_QG6 }, { "qd6", KERNEL_QD6 }, { "rq6", KERNEL_RQ6 }, { "rq2", KERNEL_RQ2 }, { "rq4", KERNEL_RQ4 }, { "ring", KERNEL_RING }, { "legacy", KERNEL_LEGACY }, { "sm", KERNEL_SM } };
     for (const auto& n : names)
       if (std::strcmp(value, n.first) == 0) {
         t.kernel = n.second;
         return B200VR_OK;
       }
-    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, rq6, ring, legacy, sm");
+    return fail(h, B200VR_EINVAL, "set_option: kernel is one of auto, q, qb2, qb4, qb8, qc4, qc6, qc8, qd6, qg6, rq2, rq4, rq6, ring, legacy, sm");
   }
   char* end = nullptr;
   const long v = std::strtol(value, &end, 10);
@@ -854,6 +854,8 @@ struct KernelChoice {
 #define B200VR_K_QD6(a, b, c) raymarch_qc_kernel<a, b, c, 6, 1>
 #define B200VR_K_RING(a, b, c) raymarch_ring_kernel<a, b, c>
 #define B200VR_K_RQ6(a, b, c) raymarch_rq_kernel<a, b, c, 6>
+#define B200VR_K_RQ4(a, b, c) raymarch_rq_kernel<a, b, c, 4>
+#define B200VR_K_RQ2(a, b, c) raymarch_rq_kernel<a, b, c, 2>
 #define B200VR_K_NS(a, b, c) raymarch_ns_kernel<a, b, c>
 
 static KernelChoice pick_kernel(const b200vr_t* h)
@@ -874,9 +876,11 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   const bool sparse_ring = h->sparse && !p.accumulate;
   const bool large = p.skip_empty && !q_occ_in_smem(h->occ_words);
   const bool ring = force == KERNEL_RING;
-  const bool rq6 = force == KERNEL_RQ6 || (force == KERNEL_AUTO && (h->nranks != 1 || sparse_ring) &&
-                                           (size_t)h->width * h->height <= (size_t)RQ_PIXEL_MASK);
-  const bool auto_qc6 = force == KERNEL_AUTO && large && !ring && !rq6;
+  // Blocks of 6 x 32 tasks for the large volumes, 4 x 32 for the small ones (half / an eighth of C2: 1.35 / 0.60 against
+  // 1.56 / 0.61 ms; of C3: 3.37 / 1.27 against 3.36 / 1.23 ms; profiles/r3a_partition_c2_kernels.jsonl).
+  const bool auto_rq = force == KERNEL_AUTO && (h->nranks != 1 || sparse_ring) && (size_t)h->width * h->height <= (size_t)RQ_PIXEL_MASK;
+  const bool rq6 = force == KERNEL_RQ6 || (auto_rq && large), rq4 = force == KERNEL_RQ4 || (auto_rq && !large);
+  const bool auto_qc6 = force == KERNEL_AUTO && large && !ring && !rq6 && !rq4;
   KernelChoice k;
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
@@ -905,6 +909,16 @@ static KernelChoice pick_kernel(const b200vr_t* h)
         k.fn = B200VR_PICK(B200VR_K_RING, skip, pow2, occs);
         k.ring = true;
         k.threads = Q_THREADS, k.smem = tables + q_queue_bytes(), k.name = "raymarch_ring_kernel";
+      }
+      else if (force == KERNEL_RQ2) {
+        k.fn = B200VR_PICK(B200VR_K_RQ2, skip, pow2, occs);
+        k.ring = true, k.ring_block = rq_block_float4<2>();
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<2>(), k.name = "raymarch_rq_kernel<J=2>";
+      }
+      else if (rq4) {
+        k.fn = B200VR_PICK(B200VR_K_RQ4, skip, pow2, occs);
+        k.ring = true, k.ring_block = rq_block_float4<4>();
+        k.threads = QC_THREADS, k.smem = tables + qb_queue_bytes<4>(), k.name = "raymarch_rq_kernel<J=4>";
       }
       else if (rq6) {
         k.fn = B200VR_PICK(B200VR_K_RQ6, skip, pow2, occs);
@@ -1412,7 +1426,8 @@ static int render_enqueue(b200vr_t* h)
   int grid = std::max(1, std::min(want, h->sm_count * per_sm)); // persistent: SMs x resident CTAs
   if (kc.ring && P.sparse_xy) grid = h->sm_count * per_sm;      // few tiles, all heavy: warps without a tile shade published blocks
   CK(cudaMemsetAsync(h->tile_counter, 0, sizeof(unsigned int), h->stream));
-  CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
+  // the executed-sample counters add up over the frames enqueued since the last wait
+  if (!h->pending) CK(cudaMemsetAsync(h->counters, 0, sizeof(Counters), h->stream));
   {
     // launch order of the owned tiles. Super-tile orders (tile_order_kernel): 0 row-major (default), 1 centre-out, 2 by the
     // previous frame's cost, 3 Z-order, 4/5 columns, 6 middle rows first. Measured on C2 with the queue kernel: 2.29 / 2.52 /

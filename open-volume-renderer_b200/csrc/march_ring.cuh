@@ -91,6 +91,7 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
   const int my_ring = (int)blockIdx.x, n_rings = (int)gridDim.x;
   unsigned int* const r_head = P.ring_ctrl + my_ring * RING_CTRL_PER_RING, * const r_tail = r_head + RING_CTRL_STRIDE;
   unsigned int* const r_left_all = P.ring_ctrl + (size_t)n_rings * RING_CTRL_PER_RING, * const r_err = r_left_all + RING_CTRL_STRIDE;
+  unsigned int* const r_avail = r_left_all + 1; // blocks published and not yet taken, over all rings (same sector as r_left_all)
   const unsigned int cap_mask = (unsigned int)P.ring_cap - 1u; // per ring
   unsigned int* const my_seq = P.ring_seq + (size_t)my_ring * P.ring_cap;
   float4* const my_data = P.ring_data + (size_t)my_ring * P.ring_cap * RING_BLOCK_FLOAT4;
@@ -110,7 +111,7 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
   int count = 0; // tasks staged (warp-uniform)
   const long long warp_t0 = clock64();
   long long drain_t0 = 0;
-  unsigned int n_pub = 0, n_stolen = 0, idle_spins = 0;
+  unsigned int n_pub = 0, n_stolen = 0, idle_spins = 0, idle_ns = 256u;
 
   for (;;) {
     if (marching && !have_tile) {
@@ -160,7 +161,78 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
 
     bool consume = !marching;
     if (marching) {
-      const bool any_alive = __any_sync(0xffffffffu, alive);
+      // the march as a loop of its own (see march_rq.cuh: as one more branch of this state machine ptxas waited for the
+      // prefetched sample at the back edge)
+      bool any_alive = true;
+      while ((any_alive = __any_sync(0xffffffffu, alive)) && count < 32) {
+        // =================== one primary sample per live ray (raymarching, shaders_raymarching.cu:87-171) ===================
+        bool want = false;
+        f3 tp = mk3(0.f);
+        float ts = 0.f, tw = 0.f;
+        if (alive) {
+          do {
+            const float tm = 0.5f * (tx + ty);
+            const f3 p = mk3(__fmaf_rn(tm, od.x, oo.x), __fmaf_rn(tm, od.y, oo.y), __fmaf_rn(tm, od.z, oo.z));
+            if (SKIP) {
+              if (!(tm < cell_exit)) {
+                i3 c;
+                cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
+                // approximate reciprocals: see march_q.cuh
+                cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od);
+              }
+              if (cell_empty) {
+                // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
+                const float lim = fminf(cell_exit, t1) - 5.f * step;
+                while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
+                  ty += step;
+                  ty += step;
+                  ty += step;
+                  ty += step;
+                }
+                do {
+                  tx = ty;
+                  ty = fminf(tx + step, t1);
+                } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
+                alive = ty > tx;
+                break;
+              }
+            }
+            float s;
+            if (have_pre) s = s_pre;
+            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+            {
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+              const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
+              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
+            }
+            c_primary++;
+            float a = alpha_lookup<POW2>(P, apair_base, s);
+            {
+              const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
+              if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));
+            }
+            if (!SKIP || a != 0.f) {
+              tw = (1.f - A) * a;
+              A += tw;
+              tp = p;
+              ts = s;
+              want = true;
+            }
+            tx = ty;
+            ty = fminf(tx + step, t1);
+            alive = ty > tx && A < 0.9999f;
+          } while (0);
+        }
+        const unsigned int m = __ballot_sync(0xffffffffu, want);
+        if (want) {
+          const int slot = count + __popc(m & lt_mask);
+          sts_f32x4(queue_base + 32u * (unsigned)slot, make_float4(tp.x, tp.y, tp.z, ts));
+          sts_f32x4(queue_base + 32u * (unsigned)slot + 16u, make_float4(tw, __uint_as_float(pixel_index), 0.f, 0.f));
+        }
+        __syncwarp();
+        count += __popc(m);
+      }
       if (count >= 32 || (!any_alive && count > 0)) {
         unsigned int fill = 0;
         if (lane == 0) fill = ld_relaxed_u32(r_head) - ld_relaxed_u32(r_tail);
@@ -190,6 +262,7 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
           if (lane == 0) {
             __threadfence();
             st_release_u32(my_seq + (t & cap_mask), t + 1u);
+            atomicAdd(r_avail, 1u);
           }
           // move the tasks that did not fit (at most 31) to the front
           const int rest = count - n;
@@ -234,28 +307,37 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
       }
       else {
         // ---- remote: a block some marching warp published because the rings were running dry ----
+        // warps without work watch one word pair (blocks available anywhere, warps still marching) and look through the rings
+        // only when there is something to find
+        unsigned int left = 0u, avail = 0u;
+        if (lane == 0) avail = ld_relaxed_u32(r_avail), left = ld_acquire_u32(r_left_all);
+        left = __shfl_sync(0xffffffffu, left, 0);
+        avail = __shfl_sync(0xffffffffu, avail, 0);
         int found = -1;
-        for (int h = 0; h * 32 < n_rings && found < 0; h++) {
-          const int i = lane + 32 * h; // ring my_ring + i, wrapping once around all rings
-          const unsigned int* c = P.ring_ctrl + (size_t)((my_ring + i) % n_rings) * RING_CTRL_PER_RING;
-          const unsigned int avail = __ballot_sync(0xffffffffu, i < n_rings && (int)(ld_relaxed_u32(c) - ld_relaxed_u32(c + RING_CTRL_STRIDE)) > 0);
-          if (avail) found = (my_ring + (__ffs(avail) - 1) + 32 * h) % n_rings;
-        }
+        if ((int)avail > 0 || left == 0u)
+          for (int h = 0; h * 32 < n_rings && found < 0; h++) {
+            const int i = lane + 32 * h; // ring my_ring + i, wrapping once around all rings
+            const unsigned int* c = P.ring_ctrl + (size_t)((my_ring + i) % n_rings) * RING_CTRL_PER_RING;
+            const unsigned int have = __ballot_sync(0xffffffffu, i < n_rings && (int)(ld_relaxed_u32(c) - ld_relaxed_u32(c + RING_CTRL_STRIDE)) > 0);
+            if (have) found = (my_ring + (__ffs(have) - 1) + 32 * h) % n_rings;
+          }
         if (found < 0) {
-          int done = 0;
-          if (lane == 0) {
-            done = ld_acquire_u32(r_left_all) == 0u || ld_relaxed_u32(r_err) != 0u;
-            // bounded like every other wait: r_left_all counts all warps of the grid, also those of CTAs that are not resident
-            // yet -- the launch is cooperative (b200vr.cu), so they are, but a hang must never be the failure mode
-            if (!done && ++idle_spins > RING_SPIN_LIMIT / 16) {
+          // bounded like every other wait: r_left_all counts all warps of the grid, also those of CTAs that are not resident
+          // yet -- the launch is cooperative (b200vr.cu), so they are, but a hang must never be the failure mode
+          int done = left == 0u; // nobody marches any more (acquire: their last blocks are visible) and every block has a taker
+          if (lane == 0 && !done && (++idle_spins & 63u) == 0u) {
+            done = ld_relaxed_u32(r_err) != 0u;
+            if (!done && idle_spins > RING_SPIN_LIMIT / 16) {
               atomicExch(r_err, 1u);
               done = 1;
             }
           }
-          if (__shfl_sync(0xffffffffu, done, 0)) break; // nobody marches any more and every published block was claimed
-          __nanosleep(500);
+          if (__shfl_sync(0xffffffffu, done, 0)) break;
+          __nanosleep(idle_ns);
+          if (idle_ns < 4096u) idle_ns <<= 1;
           continue;
         }
+        idle_ns = 256u;
         idle_spins = 0u;
         unsigned int* const c_ctrl = P.ring_ctrl + (size_t)found * RING_CTRL_PER_RING;
         unsigned int* const c_seq = P.ring_seq + (size_t)found * P.ring_cap;
@@ -289,6 +371,7 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
         t = __shfl_sync(0xffffffffu, t, 0);
         if (got) {
           n_stolen++;
+          if (lane == 0) atomicSub(r_avail, 1u);
           const float4* const src = P.ring_data + ((size_t)found * P.ring_cap + (t & cap_mask)) * RING_BLOCK_FLOAT4 + 2 * lane;
           q0 = __ldcg(src), q1 = __ldcg(src + 1); // L2: the block was written by another SM
           __ballot_sync(0xffffffffu, __float_as_uint(q1.y) != RING_NO_PIXEL); // every lane holds its task: free the slot
@@ -307,73 +390,6 @@ raymarch_ring_kernel(const __grid_constant__ LaunchParams P)
       continue;
     }
 
-    // =================== one primary sample per live ray (raymarching, shaders_raymarching.cu:87-171) ===================
-    bool want = false;
-    f3 tp = mk3(0.f);
-    float ts = 0.f, tw = 0.f;
-    if (alive) {
-      do {
-        const float tm = 0.5f * (tx + ty);
-        const f3 p = mk3(__fmaf_rn(tm, od.x, oo.x), __fmaf_rn(tm, od.y, oo.y), __fmaf_rn(tm, od.z, oo.z));
-        if (SKIP) {
-          if (!(tm < cell_exit)) {
-            i3 c;
-            cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
-            // approximate reciprocals: see march_q.cuh
-            cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od);
-          }
-          if (cell_empty) {
-            // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
-            const float lim = fminf(cell_exit, t1) - 5.f * step;
-            while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
-              ty += step;
-              ty += step;
-              ty += step;
-              ty += step;
-            }
-            do {
-              tx = ty;
-              ty = fminf(tx + step, t1);
-            } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
-            alive = ty > tx;
-            break;
-          }
-        }
-        float s;
-        if (have_pre) s = s_pre;
-        else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-        {
-          // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
-          const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
-          have_pre = nty > ty && (!SKIP || ntm < cell_exit);
-          if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
-        }
-        c_primary++;
-        float a = alpha_lookup<POW2>(P, apair_base, s);
-        {
-          const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
-          if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));
-        }
-        if (!SKIP || a != 0.f) {
-          tw = (1.f - A) * a;
-          A += tw;
-          tp = p;
-          ts = s;
-          want = true;
-        }
-        tx = ty;
-        ty = fminf(tx + step, t1);
-        alive = ty > tx && A < 0.9999f;
-      } while (0);
-    }
-    const unsigned int m = __ballot_sync(0xffffffffu, want);
-    if (want) {
-      const int slot = count + __popc(m & lt_mask);
-      sts_f32x4(queue_base + 32u * (unsigned)slot, make_float4(tp.x, tp.y, tp.z, ts));
-      sts_f32x4(queue_base + 32u * (unsigned)slot + 16u, make_float4(tw, __uint_as_float(pixel_index), 0.f, 0.f));
-    }
-    __syncwarp();
-    count += __popc(m);
   }
 
   // executed-sample counters: one atomic set per warp

@@ -562,14 +562,19 @@ class SortFirstP2P:
                 self.L.b200vr_ipc_close(self.r.handle, C.c_void_p(p))
             self.remote = {}
 
-    def step(self):
+    def step(self, wait=True):
+        """One frame. wait=False: nothing here blocks the host -- the frame and the completion all-reduce are enqueued on the
+        stream (b200vr_render_async) and the caller collects the counters of all frames since with renderer.wait()."""
         import torch.distributed as dist
         r, L = self.r, self.L
         if self.remote:
             cur = int(L.b200vr_current_buffer(r.handle))
             r._ck(L.b200vr_set_frame_target(r.handle, C.c_void_p(self.remote[cur]), C.c_void_p(self.remote[2 + cur])))
-        r.render()
-        self.launches += r.last_stats["kernel_launches"]
+        if wait:
+            r.render()
+            self.launches += r.last_stats["kernel_launches"]
+        else:
+            r.render_async()
         if self.world > 1:
             dist.all_reduce(self._tok, group=self.group)   # stream-ordered: every rank's tiles are in the display rank's frame
-        return r.last_stats
+        return r.last_stats if wait else None

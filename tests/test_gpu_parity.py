@@ -189,6 +189,7 @@ VARIANT_OPTIONS = [
     {"kernel": "qg6"}, {"kernel": "qd6"}, {"kernel": "qd6", "occ_smem": 0}, {"kernel": "qd6", "occ_smem": 0, "tile_order": 0}, {"kernel": "qg6", "max_ctas_per_sm": 1},
     {"kernel": "ring"}, {"kernel": "ring", "occ_smem": 0}, {"kernel": "ring", "occ_smem": 0, "tile_order": 7},
     {"kernel": "rq6"}, {"kernel": "rq6", "occ_smem": 0}, {"kernel": "rq6", "occ_smem": 0, "ring_high": 1}, {"kernel": "rq6", "ring_high": 64},
+    {"kernel": "rq4"}, {"kernel": "rq4", "occ_smem": 0, "rq_self": 0}, {"kernel": "rq2"}, {"kernel": "rq6", "rq_self": 100, "rq_cap": 32},
 ]
 
 
@@ -202,10 +203,11 @@ def test_every_shading_kernel_variant_matches_the_oracle(scene):
     r = make_renderer(sc, W, H)
     d = oracle_desc(sc, W, H, volume=device_volume(r, dims))
     o_rgba, o_grad, o_cnt = pyoracle.OracleScene(d, skip_empty=True).render_march()
-    base = None
+    base = rq_base = None
     for opts in VARIANT_OPTIONS:
-        for k in ("kernel", "occ_smem", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high"):
-            r.set_option(k, opts.get(k, {"kernel": "auto", "occ_smem": -1, "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0, "ring_high": 4}[k]))
+        for k in ("kernel", "occ_smem", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap"):
+            r.set_option(k, opts.get(k, {"kernel": "auto", "occ_smem": -1, "tile_order": -1, "sheet_px": 8, "max_ctas_per_sm": 0, "ring_high": 4,
+                                         "rq_self": 1, "rq_cap": 128}[k]))
         r.render()
         rgba, grad = r.download()
         st = dict(r.last_stats)
@@ -217,8 +219,13 @@ def test_every_shading_kernel_variant_matches_the_oracle(scene):
             continue
         for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
             assert st[k] == base[2][k], (opts, k)
-        if opts["kernel"] in ("ring", "rq6"):
+        if opts["kernel"] in ("ring", "rq2", "rq4", "rq6"):
             assert max_abs(rgba, base[0]) < 1e-4 and max_abs(grad, base[1]) < 1e-4, opts
+            if opts["kernel"] != "ring":   # march_rq.cuh: integer sums of the same per-task results, whatever the block size and policy
+                if rq_base is None:
+                    rq_base = (rgba.copy(), grad.copy())
+                assert np.array_equal(rgba.view(np.uint32), rq_base[0].view(np.uint32)), opts
+                assert np.array_equal(grad.view(np.uint32), rq_base[1].view(np.uint32)), opts
         else:
             assert np.array_equal(rgba.view(np.uint32), base[0].view(np.uint32)), opts
             assert np.array_equal(grad.view(np.uint32), base[1].view(np.uint32)), opts
@@ -287,7 +294,7 @@ def test_sort_first_tiles_reassemble_bit_exact(ring_kernel):
     r = make_renderer(sc, W, H)
     r.render()
     full_q = r.download()[0].copy()
-    r.set_option("kernel", "rq6" if ring_kernel == "auto" else ring_kernel)
+    r.set_option("kernel", "rq4" if ring_kernel == "auto" else ring_kernel)   # auto: a small volume's partitions take rq4
     r.render()
     full = r.download()[0].copy()
     r.render()
@@ -579,6 +586,32 @@ def test_double_buffer_swap_map_and_async_download():
     fb2 = r.mapframe()
     assert fb2.rgba[1] == (W + 64) * H * 16 and not r.download()[0].any()
     assert L.b200vr_map_index(r.handle, 2, None, None) == capi.EINVAL
+    r.close()
+
+
+@pytest.mark.parametrize("kernel", ["auto", "rq6"])
+def test_render_async_frames_queue_up_and_wait_sums_their_counters(kernel):
+    """b200vr_render_async x 3 + b200vr_wait (include/b200vr.h): nothing blocks between the frames, the frame is the same as a
+    synchronous one, the counters are the sum over the frames enqueued since the last wait, and the next synchronous frame counts
+    from zero again."""
+    W, H = 200, 120
+    sc = S.noise_scene(48, tf="sparse", camera="oblique")
+    r = make_renderer(sc, W, H)
+    r.set_option("kernel", kernel)
+    r.render()
+    one = dict(r.last_stats)
+    want = tuple(a.copy() for a in r.download())
+    for _ in range(3):
+        r.render_async()
+    st = r.wait()
+    for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
+        assert st[k] == 3 * one[k], k
+    assert st["frame_index"] == one["frame_index"] + 3
+    got = r.download()
+    assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)) and np.array_equal(got[1].view(np.uint32), want[1].view(np.uint32))
+    r.render()
+    for k in ("primary_samples", "shadow_samples", "gradient_fetches", "rays"):
+        assert r.last_stats[k] == one[k], k
     r.close()
 
 

@@ -47,7 +47,7 @@ def main():
     if rank == 0:
         r.render()
         want_q = r.download(want_grad=False)[0].copy()     # undivided frame, queue kernel (float sums in march order)
-        r.set_option("kernel", "rq6")                      # undivided frame, ring kernel: what the partitions must reproduce bit for bit
+        r.set_option("kernel", "rq4")                      # undivided frame, ring kernel: what the partitions must reproduce bit for bit
         r.render()
         want = r.download(want_grad=False)[0].copy()
         r.set_option("kernel", "auto")
