@@ -885,6 +885,8 @@ static KernelChoice pick_kernel(const b200vr_t* h)
   k.threads = RENDER_THREADS;
   k.smem = tf_shared_bytes(h->n_color, h->n_alpha);
   if (p.mode == B200VR_MODE_PATHTRACE) {
+    // one 8x4 tile per warp. Measured and not kept (profiles/r3d_pathtrace_regen.md): every lane taking the next pixel when its
+    // path ends, as a flat loop of one walk-to-the-next-event per iteration -- bit-identical frames, 1.6 to 2.7 times the time.
     k.fn = p.sampler == B200VR_SAMPLER_MANUAL ? pathtrace_kernel<SAMPLER_MANUAL> : pathtrace_kernel<SAMPLER_TEX3D>;
     k.name = "pathtrace_kernel";
     return k;
