@@ -281,8 +281,8 @@ __global__ void sheet_key_kernel(const SheetParams S, unsigned int* __restrict__
   const int m = k / WARP_TILES_PER_SUPER, r = k % WARP_TILES_PER_SUPER;
   const int s = S.rank + m * S.nranks;
   const int b = r / TILE_CHUNK, i = r % TILE_CHUNK;
-  const int px = (s % S.super_w) * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W;
-  const int py = (s / S.super_w) * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
+  const int px = (s % S.super_w) * SUPER_TILE_W + ((b % SUPER_BLOCKS_X) * 4 + (i & 3)) * WARP_TILE_W;
+  const int py = (s / S.super_w) * SUPER_TILE_H + ((b / SUPER_BLOCKS_X) * 4 + (i >> 2)) * WARP_TILE_H;
   const float sx = ((float)px + 0.5f * WARP_TILE_W) * S.rw, sy = ((float)py + 0.5f * WARP_TILE_H) * S.rh;
   const f3 d = S.cam_dir + (sx - 0.5f) * S.cam_hor + (sy - 0.5f) * S.cam_ver; // centre ray of the tile (unnormalised)
   const float phi = atan2f(dot3(d, S.e2), dot3(d, S.e1));

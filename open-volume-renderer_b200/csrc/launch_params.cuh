@@ -10,8 +10,13 @@ namespace b200k {
 constexpr int MC_SIZE = 16;        // macrocell edge in voxels (accel/spatial_partition.h:24)
 constexpr int WARP_TILE_W = 8;     // pixels per warp tile: 8 x 4
 constexpr int WARP_TILE_H = 4;
-constexpr int SUPER_TILE_W = 64;   // sort-first ownership granule: 64 x 32 pixels = 8 x 8 warp tiles
-constexpr int SUPER_TILE_H = 32;
+#ifndef B200VR_SUPER_W // tuning builds only (multiples of 32 x 16): distributed.py mirrors the two numbers
+#define B200VR_SUPER_W 64
+#define B200VR_SUPER_H 32
+#endif
+constexpr int SUPER_TILE_W = B200VR_SUPER_W;   // sort-first ownership granule: 64 x 32 pixels = 8 x 8 warp tiles
+constexpr int SUPER_TILE_H = B200VR_SUPER_H;
+constexpr int SUPER_BLOCKS_X = SUPER_TILE_W / (4 * WARP_TILE_W); // blocks of 4 x 4 warp tiles per row of a super tile
 constexpr int WARP_TILES_PER_SUPER = (SUPER_TILE_W / WARP_TILE_W) * (SUPER_TILE_H / WARP_TILE_H);
 constexpr int RENDER_THREADS = 128;
 #ifndef B200VR_TILE_STATS
@@ -116,8 +121,8 @@ __device__ __forceinline__ int warp_tile_origin(const LaunchParams& P, int k, in
   const int s = P.rank + m * P.nranks;
   const int sx = s % P.super_w, sy = s / P.super_w;
   const int b = r / TILE_CHUNK, i = r % TILE_CHUNK; // block (2 x 2 per super tile), tile inside the block (4 x 4)
-  px = sx * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W;
-  py = sy * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H;
+  px = sx * SUPER_TILE_W + ((b % SUPER_BLOCKS_X) * 4 + (i & 3)) * WARP_TILE_W;
+  py = sy * SUPER_TILE_H + ((b / SUPER_BLOCKS_X) * 4 + (i >> 2)) * WARP_TILE_H;
   return m;
 }
 // pixel of this lane in the k-th warp tile of the launch; returns the cost-table slot of the tile (-1: none). Dense frames:

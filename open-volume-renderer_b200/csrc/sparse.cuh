@@ -32,8 +32,8 @@ __device__ __forceinline__ bool sparse_entry_pixel(const SparseParams& S, int e,
   const int s = e / (WARP_TILES_PER_SUPER * 32), r = e % (WARP_TILES_PER_SUPER * 32);
   const int t = r >> 5, lane = r & 31;
   const int b = t / TILE_CHUNK, i = t % TILE_CHUNK; // same walk as warp_tile_origin
-  x = (s % S.super_w) * SUPER_TILE_W + ((b & 1) * 4 + (i & 3)) * WARP_TILE_W + (lane & (WARP_TILE_W - 1));
-  y = (s / S.super_w) * SUPER_TILE_H + ((b >> 1) * 4 + (i >> 2)) * WARP_TILE_H + lane / WARP_TILE_W;
+  x = (s % S.super_w) * SUPER_TILE_W + ((b % SUPER_BLOCKS_X) * 4 + (i & 3)) * WARP_TILE_W + (lane & (WARP_TILE_W - 1));
+  y = (s / S.super_w) * SUPER_TILE_H + ((b / SUPER_BLOCKS_X) * 4 + (i >> 2)) * WARP_TILE_H + lane / WARP_TILE_W;
   return x < S.width && y < S.height;
 }
 
