@@ -47,6 +47,7 @@ struct Tuning {
   int max_ctas_per_sm = 0;  // 0: as many as fit
   int ring_high = 4;        // blocks kept ready per CTA for warps that have run out of tiles (march_ring.cuh)
   int rq_self = 1;          // march_rq.cuh: blocks of one tile its warp shades itself before it only publishes
+  int rq_yield = 0;         // march_rq.cuh: see LaunchParams::rq_yield
   int rq_cap = 128;          // march_rq.cuh: slots per ring (power of two)
   int occ_smem = -1;        // macrocell occupancy mask in shared memory: -1 when it fits (march_q.cuh Q_OCC_SMEM_WORDS), 0 never
   int carveout = -1;        // cudaFuncAttributePreferredSharedMemoryCarveout in percent; -1: just what the launch needs
@@ -182,7 +183,7 @@ static int grid_for(size_t n, int threads, int sm_count)
 }
 
 // ---- tuning options -------------------------------------------------------------------------------------------------
-static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap", "occ_smem", "carveout",
+static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap", "rq_yield", "occ_smem", "carveout",
                                             "tex_native8", "debug_tiles" };
 
 static int apply_option(b200vr_t* h, const std::string& name, const char* value)
@@ -214,6 +215,7 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   else if (name == "max_ctas_per_sm") t.max_ctas_per_sm = (int)std::max(0l, v);
   else if (name == "ring_high") t.ring_high = (int)std::max(1l, v);
   else if (name == "rq_self") t.rq_self = (int)std::max(0l, v);
+  else if (name == "rq_yield") t.rq_yield = (int)std::max(0l, v);
   else if (name == "rq_cap") {
     if (v < 32 || v > 1024 || (v & (v - 1))) return fail(h, B200VR_EINVAL, "set_option: rq_cap is a power of two in 32..1024");
     t.rq_cap = (int)v;
@@ -1464,6 +1466,7 @@ static int render_enqueue(b200vr_t* h)
     // one ring per CTA: high-water mark + one block in flight per warp of the CTA + slack, as a power of two
     P.ring_high = h->tune.ring_high;
     P.rq_self = h->tune.rq_self;
+    P.rq_yield = h->tune.rq_yield;
     int cap = kc.ring_block != RING_BLOCK_FLOAT4 ? h->tune.rq_cap : 32;
     while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
     if (cap != h->ring_cap || grid != h->ring_count || kc.ring_block != h->ring_block) {
@@ -1564,6 +1567,8 @@ static int render_wait(b200vr_t* h, b200vr_stats* stats)
     if (h->last_kernel.rfind("raymarch_rq_kernel", 0) == 0) {
       std::fprintf(stderr, "[b200] rq: longest tile %.0f kclk, started %.0f kclk into the launch: %llu march iterations, %llu blocks published (%.0f kclk), "
                            "%llu shaded by itself (%.0f kclk)\n", c.dbg[0] * 1e-3, c.dbg[7] * 1e-3, c.dbg[1], c.dbg[2], c.dbg[5] * 1e-3, c.dbg[3], c.dbg[6] * 1e-3);
+      std::fprintf(stderr, "[b200] rq: its march iterations: macrocell section %.0f kclk, until the sample has arrived %.0f kclk, whole iterations %.0f kclk; "
+                           "%llu lane-entries into new macrocells\n", (c.dbg[4] & 0xffffffffull) * 1e-3, (c.dbg[4] >> 32) * 1e-3, (c.dbg[8] & 0xffffffffull) * 1e-3, c.dbg[8] >> 32);
       std::fprintf(stderr, "[b200] rq: of the time after the last tile, waiting for blocks %.0f kclk per warp\n", c.delta_samples * 1e-3 / warps);
       c.delta_samples = 0;
     }

@@ -27,7 +27,7 @@ struct Counters {
   unsigned long long primary_samples, shadow_samples, gradient_fetches, delta_samples, rays;
   unsigned long long tile_clocks_max, tile_clocks_sum; // longest warp tile / all warp tiles, in SM clocks (B200VR_DEBUG_TILES)
   unsigned long long drain_clocks_sum, warp_clocks_max, blocks_published, blocks_stolen; // ring kernel: after a warp's last tile
-  unsigned long long dbg[8]; // -DB200VR_TILE_STATS=1, march_rq.cuh: the longest warp tile in detail
+  unsigned long long dbg[10]; // -DB200VR_TILE_STATS=1, march_rq.cuh: the longest warp tile in detail
 };
 
 struct LaunchParams {
@@ -105,6 +105,7 @@ struct LaunchParams {
   unsigned int* ring_seq;   // per slot sequence number
   float4* ring_data;        // ring_cap blocks of 64 float4 (32 tasks)
   int ring_cap, ring_high;  // slots (power of two); fill level above which a producer shades a block before publishing
+  int rq_yield;             // march_rq.cuh: helpers leave SMs with marching warps alone once fewer than this many warps march
   int rq_self;              // march_rq.cuh: blocks of a tile its warp shades itself while the ring is above ring_high
   unsigned long long* acc;  // per pixel 3 words of fixed-point sums: (r|g), (b|Gx), (Gy|Gz)
   float* ray_alpha;         // per pixel opacity of the sample being rendered

@@ -132,6 +132,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
       bool cell_empty = false;
       float s_pre = 0.f;     // prefetched value of the sample at (tx, ty), valid while have_pre
       bool have_pre = false;
+      unsigned int pre_widx = 0xffffffffu, pre_word = 0u; // occupancy word requested ahead of the ray (see the march)
       unsigned int mine[J + 1]; // queue slots holding this pixel's tasks, 32 per word
 #pragma unroll
       for (int g = 0; g <= J; g++) mine[g] = 0u;
@@ -202,31 +203,32 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
             if (SKIP) {
               if (!(tm < cell_exit)) {
                 i3 c;
-                cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
+                const unsigned int idx = (unsigned)pad_cell(P, p, c);
+                if (OCCS) cell_empty = !occ_bit<OCCS>(P, occ_base, idx);
+                else {
+                  // the occupancy word of this cell was requested when the ray entered the previous one (below); only when the
+                  // ray came out somewhere else is it loaded now (march_rq.cuh has the measurements)
+                  unsigned int w;
+                  if ((idx >> 5) == pre_widx) w = pre_word;
+                  else w = __ldg(P.occ_bits + (idx >> 5));
+                  cell_empty = ((w >> (idx & 31u)) & 1u) == 0u;
+                }
                 // approximate reciprocals: see march_q.cuh
                 cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od);
-              }
-              if (cell_empty) {
-                // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
-                const float lim = fminf(cell_exit, t1) - 5.f * step;
-                while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
-                  ty += step;
-                  ty += step;
-                  ty += step;
-                  ty += step;
+                if (!OCCS) {
+                  const float tn = cell_exit + 0.5f * step; // about where the first sample behind this cell will be
+                  pre_widx = pad_index_floor(P, mk3(__fmaf_rn(tn, od.x, oo.x), __fmaf_rn(tn, od.y, oo.y), __fmaf_rn(tn, od.z, oo.z))) >> 5;
+                  pre_word = __ldg(P.occ_bits + pre_widx);
                 }
-                do {
-                  tx = ty;
-                  ty = fminf(tx + step, t1);
-                } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
-                alive = ty > tx;
-                break;
               }
             }
-            float s;
-            if (have_pre) s = s_pre;
-            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-            {
+            // the lanes in live cells issue their fetches first, then the lanes in empty cells run their skip arithmetic while
+            // those fetches are in flight, then the live lanes classify
+            const bool skip = SKIP && cell_empty;
+            float s = 0.f;
+            if (!skip) {
+              if (have_pre) s = s_pre;
+              else s = tex3D<float>(P.tex, p.x, p.y, p.z);
               // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
               // Measured and rejected (profiles/r2n_*, r2x_*): this sample and the next three fetched
               // together and consumed over the following steps (C3 6.41 vs 6.14 ms), and four samples fetched, classified and
@@ -235,6 +237,22 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
+            }
+            if (skip) {
+              // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
+              const float lim = fminf(cell_exit, t1) - 5.f * step;
+              while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
+                ty += step;
+                ty += step;
+                ty += step;
+                ty += step;
+              }
+              do {
+                tx = ty;
+                ty = fminf(tx + step, t1);
+              } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
+              alive = ty > tx;
+              break;
             }
             c_primary++;
             float a = alpha_lookup<POW2>(P, apair_base, s);

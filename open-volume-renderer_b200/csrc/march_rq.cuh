@@ -87,6 +87,7 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
   f3 od = mk3(0.f);
   float tx = 0.f, ty = 0.f, t1 = 0.f, A = 0.f, cell_exit = -1.f, s_pre = 0.f;
   int count = 0; // tasks staged (warp-uniform)
+  unsigned int pre_widx = 0xffffffffu, pre_word = 0u; // occupancy word requested ahead of the ray (see the march)
   int self_blocks = 0; // blocks of the tile in flight this warp shaded itself
   unsigned int idle_spins = 0, idle_ns = 256u;
 #if B200VR_TILE_STATS // diagnostic builds: where the tail of the launch goes (render_wait prints the sums)
@@ -95,6 +96,7 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
   unsigned int n_pub = 0, n_stolen = 0;
   unsigned int t_iters = 0, t_pubs = 0, t_local = 0; // of the tile in flight: march iterations, blocks published / shaded here
   long long t_pub_clk = 0, t_local_clk = 0, t_mark = 0;
+  unsigned long long t_sec[4] = { 0, 0, 0, 0 };
 #endif
 
   for (;;) {
@@ -141,11 +143,13 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
       cell_exit = -1.f;
       cell_empty = false;
       have_pre = false;
+      pre_widx = 0xffffffffu;
       count = 0;
       self_blocks = 0;
       have_tile = true;
 #if B200VR_TILE_STATS
       t_iters = t_pubs = t_local = 0, t_pub_clk = t_local_clk = 0;
+      t_sec[0] = t_sec[1] = t_sec[2] = t_sec[3] = 0;
 #endif
       QC_PHASE(ph_other);
       continue;
@@ -169,44 +173,81 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
         bool want = false;
         f3 tp = mk3(0.f);
         float ts = 0.f, tw = 0.f;
+#if B200VR_TILE_STATS
+        const unsigned int it_t0 = (unsigned int)clock();
+        unsigned int it_t1 = it_t0, it_t2 = it_t0;
+        bool it_entry = false;
+#endif
         if (alive) {
           do {
             const float tm = 0.5f * (tx + ty);
             const f3 p = mk3(__fmaf_rn(tm, od.x, oo.x), __fmaf_rn(tm, od.y, oo.y), __fmaf_rn(tm, od.z, oo.z));
+#if B200VR_TILE_STATS
+            it_entry = SKIP && !(tm < cell_exit);
+#endif
             if (SKIP) {
               if (!(tm < cell_exit)) {
                 i3 c;
-                cell_empty = !occ_bit<OCCS>(P, occ_base, (unsigned)pad_cell(P, p, c));
-                cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od); // see march_q.cuh
-              }
-              if (cell_empty) {
-                // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
-                const float lim = fminf(cell_exit, t1) - 5.f * step;
-                while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
-                  ty += step;
-                  ty += step;
-                  ty += step;
-                  ty += step;
+                const unsigned int idx = (unsigned)pad_cell(P, p, c);
+                if (OCCS) cell_empty = !occ_bit<OCCS>(P, occ_base, idx);
+                else {
+                  // The occupancy word of this cell was requested when the ray entered the previous one (below); only when the
+                  // ray came out somewhere else is it loaded now. With the mask in global memory this load, at L2 latency in
+                  // front of the cell's first fetch, was half of a march iteration -- and with 32 rays in a warp some lane
+                  // enters a new macrocell in nearly every iteration (5.6 lanes on the longest tile of C3).
+                  unsigned int w;
+                  if ((idx >> 5) == pre_widx) w = pre_word;
+                  else w = __ldg(P.occ_bits + (idx >> 5));
+                  cell_empty = ((w >> (idx & 31u)) & 1u) == 0u;
                 }
-                do {
-                  tx = ty;
-                  ty = fminf(tx + step, t1);
-                } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
-                alive = ty > tx;
-                break;
+                cell_exit = cell_exit_t(P, c, oo, mk3(rcp_fast(od.x), rcp_fast(od.y), rcp_fast(od.z)), od); // see march_q.cuh
+                if (!OCCS) {
+                  const float tn = cell_exit + 0.5f * step; // about where the first sample behind this cell will be
+                  pre_widx = pad_index_floor(P, mk3(__fmaf_rn(tn, od.x, oo.x), __fmaf_rn(tn, od.y, oo.y), __fmaf_rn(tn, od.z, oo.z))) >> 5;
+                  pre_word = __ldg(P.occ_bits + pre_widx);
+                }
               }
             }
-            float s;
-            if (have_pre) s = s_pre;
-            else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-            {
-              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
+            // Order of the three parts below: the lanes in live cells issue their fetches first, then the lanes in empty cells run
+            // their skip arithmetic (a chain of some twenty dependent additions) while those fetches are in flight, then the live
+            // lanes classify. With the skip in front, every iteration of the warp paid for it before its fetches went out.
+            const bool skip = SKIP && cell_empty;
+#if B200VR_TILE_STATS
+            it_t1 = (unsigned int)clock();
+#endif
+            float s = 0.f;
+            if (!skip) {
+              if (have_pre) s = s_pre;
+              else s = tex3D<float>(P.tex, p.x, p.y, p.z);
+              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
+              // (Fetching it also when it is the first sample of the next cell, whose occupancy is not known yet, and the first
+              // sample behind an empty cell at the end of the skip: slower, an eighth of C3 1.28 against 1.17 ms -- the wait for
+              // it moves in front of the macrocell section.)
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
               have_pre = nty > ty && (!SKIP || ntm < cell_exit);
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
             }
+            if (skip) {
+              // every sample of this cell has alpha == 0 exactly and adds +0: advance t on the reference's lattice
+              const float lim = fminf(cell_exit, t1) - 5.f * step;
+              while (ty < lim) { // four whole steps stay inside the cell and the ray: min(., t1) is the identity
+                ty += step;
+                ty += step;
+                ty += step;
+                ty += step;
+              }
+              do {
+                tx = ty;
+                ty = fminf(tx + step, t1);
+              } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
+              alive = ty > tx;
+              break;
+            }
             c_primary++;
             float a = alpha_lookup<POW2>(P, apair_base, s);
+#if B200VR_TILE_STATS
+            asm volatile("mov.u32 %0, %%clock;" : "=r"(it_t2) : "f"(a)); // after the sample has arrived
+#endif
             {
               const float adj = P.base * (ty - tx); // opacity correction (shaders_raymarching.cu:118-122)
               if (!(fabsf(adj - 1.f) < 1e-7f)) a = clamp01(1.f - __powf(1.f - a, adj));
@@ -231,6 +272,16 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
         }
         __syncwarp();
         count += __popc(m);
+#if B200VR_TILE_STATS
+        {
+          // the slowest lane of each section, and how many lanes entered a new macrocell in this iteration
+          const unsigned int it_t3 = (unsigned int)clock();
+          t_sec[0] += __reduce_max_sync(0xffffffffu, it_t1 - it_t0);
+          t_sec[1] += __reduce_max_sync(0xffffffffu, it_t2 - it_t1);
+          t_sec[2] += it_t3 - it_t0;
+          t_sec[3] += (unsigned int)__popc(__ballot_sync(0xffffffffu, it_entry));
+        }
+#endif
       }
       QC_PHASE(ph_primary);
       if (count >= J * 32 || (!any_alive && count > 0)) {
@@ -303,6 +354,8 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
             P.counters->dbg[1] = t_iters, P.counters->dbg[2] = t_pubs, P.counters->dbg[3] = t_local;
             P.counters->dbg[5] = (unsigned long long)t_pub_clk, P.counters->dbg[6] = (unsigned long long)t_local_clk;
             P.counters->dbg[7] = (unsigned long long)(tile_t0 - warp_t0);
+            P.counters->dbg[4] = t_sec[0] | (t_sec[1] << 32);
+            P.counters->dbg[8] = t_sec[2] | (t_sec[3] << 32);
           }
         }
 #endif
