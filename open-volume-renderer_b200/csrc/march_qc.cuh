@@ -235,7 +235,8 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
               // corrected as independent chains with only the compositing recurrence and the queue stores in order (6.93 ms;
               // C2 3.54 vs 2.29) -- neither shortens a small partition's launch either (1/8 of C3: 2.26 ms all three ways).
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
-              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              // (also when it is the first sample of the next macrocell, whose occupancy is not known yet: march_rq.cuh)
+              have_pre = nty > ty;
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
             }
             if (skip) {
@@ -252,6 +253,7 @@ raymarch_qc_kernel(const __grid_constant__ LaunchParams P)
                 ty = fminf(tx + step, t1);
               } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
               alive = ty > tx;
+              have_pre = false;
               break;
             }
             c_primary++;

@@ -213,18 +213,18 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
             // lanes classify. With the skip in front, every iteration of the warp paid for it before its fetches went out.
             const bool skip = SKIP && cell_empty;
 #if B200VR_TILE_STATS
-            it_t1 = (unsigned int)clock();
+            it_t1 = it_t2 = (unsigned int)clock();
 #endif
             float s = 0.f;
             if (!skip) {
               if (have_pre) s = s_pre;
               else s = tex3D<float>(P.tex, p.x, p.y, p.z);
-              // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified.
-              // (Fetching it also when it is the first sample of the next cell, whose occupancy is not known yet, and the first
-              // sample behind an empty cell at the end of the skip: slower, an eighth of C3 1.28 against 1.17 ms -- the wait for
-              // it moves in front of the macrocell section.)
+              // the next lattice sample is fetched before this one is classified -- also when it is the first one of the next
+              // macrocell, whose occupancy is not known yet: a wasted fetch if that cell turns out empty, instead of a fetch all
+              // lanes of the warp wait for (longest tile of an eighth of C3: 945 -> 650 clocks per iteration until the sample
+              // is there). The first sample behind an EMPTY cell fetched the same way at the end of the skip: slower (1.28 ms).
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
-              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              have_pre = nty > ty;
               if (have_pre) s_pre = tex3D<float>(P.tex, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
             }
             if (skip) {
@@ -241,6 +241,7 @@ raymarch_rq_kernel(const __grid_constant__ LaunchParams P)
                 ty = fminf(tx + step, t1);
               } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
               alive = ty > tx;
+              have_pre = false;
               break;
             }
             c_primary++;
