@@ -387,6 +387,7 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
                   ty = fminf(tx + step, t1);
                 } while (ty > tx && 0.5f * (tx + ty) < cell_exit);
                 alive = ty > tx;
+                have_pre = false;
                 break;
               }
             }
@@ -400,7 +401,8 @@ raymarch_q_kernel(const __grid_constant__ LaunchParams P)
               // the next lattice sample, when it stays in this (live) macrocell, is fetched before this one is classified
               // (speculative past early termination): its latency overlaps the classification and the queue traffic
               const float nty = fminf(ty + step, t1), ntm = 0.5f * (ty + nty);
-              have_pre = nty > ty && (!SKIP || ntm < cell_exit);
+              // (also when it is the first sample of the next macrocell, whose occupancy is not known yet: march_rq.cuh; C2 2.30 -> 2.27 ms)
+              have_pre = nty > ty;
               if (have_pre) s_pre = fetch3<SAMPLER>(P, __fmaf_rn(ntm, od.x, oo.x), __fmaf_rn(ntm, od.y, oo.y), __fmaf_rn(ntm, od.z, oo.z));
             }
             c_primary++;
