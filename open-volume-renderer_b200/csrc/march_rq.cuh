@@ -11,8 +11,8 @@
 // Who shades: the warp itself while `ring_high` blocks are ready in its ring (nobody is short of work), but only the first
 // `rq_self` blocks of a tile -- a tile that goes on filling blocks is one of the heavy ones, the launch ends when the heaviest has
 // marched AND shaded, and its later blocks are better left in the ring (`rq_cap` slots) for the first warp that runs dry.
-// Measured, an eighth of C3 / of C2 on one B200 (profiles/r3a_*): 1.18 / 0.67 ms, against 2.23 (march_qc.cuh) / 1.03 ms (rings of
-// single tasks). What is left is the march of the longest tile itself: ~600 iterations of one memory round trip each.
+// Measured, an eighth of C3 / of C2 on one B200 (profiles/r3a_*, r3h_*): 1.12 / 0.57 ms, against 2.23 (march_qc.cuh) / 1.03 ms (rings
+// of single tasks). What is left is the march of the longest tile itself: ~800 dependent iterations of ~1900 clocks.
 //
 // As in march_ring.cuh a consumer does not know the pixel's other samples: every task's contribution goes to per-pixel fixed-point
 // sums with fire-and-forget 64-bit reductions (integers: the frame is deterministic, identical whoever shades what and for every
