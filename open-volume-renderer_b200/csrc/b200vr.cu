@@ -47,7 +47,6 @@ struct Tuning {
   int max_ctas_per_sm = 0;  // 0: as many as fit
   int ring_high = 4;        // blocks kept ready per CTA for warps that have run out of tiles (march_ring.cuh)
   int rq_self = 1;          // march_rq.cuh: blocks of one tile its warp shades itself before it only publishes
-  int rq_yield = 0;         // march_rq.cuh: see LaunchParams::rq_yield
   int rq_cap = 128;          // march_rq.cuh: slots per ring (power of two)
   int occ_smem = -1;        // macrocell occupancy mask in shared memory: -1 when it fits (march_q.cuh Q_OCC_SMEM_WORDS), 0 never
   int carveout = -1;        // cudaFuncAttributePreferredSharedMemoryCarveout in percent; -1: just what the launch needs
@@ -183,7 +182,7 @@ static int grid_for(size_t n, int threads, int sm_count)
 }
 
 // ---- tuning options -------------------------------------------------------------------------------------------------
-static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap", "rq_yield", "occ_smem", "carveout",
+static const char* const kOptionNames[] = { "kernel", "tile_order", "sheet_px", "max_ctas_per_sm", "ring_high", "rq_self", "rq_cap", "occ_smem", "carveout",
                                             "tex_native8", "debug_tiles" };
 
 static int apply_option(b200vr_t* h, const std::string& name, const char* value)
@@ -215,7 +214,6 @@ static int apply_option(b200vr_t* h, const std::string& name, const char* value)
   else if (name == "max_ctas_per_sm") t.max_ctas_per_sm = (int)std::max(0l, v);
   else if (name == "ring_high") t.ring_high = (int)std::max(1l, v);
   else if (name == "rq_self") t.rq_self = (int)std::max(0l, v);
-  else if (name == "rq_yield") t.rq_yield = (int)std::max(0l, v);
   else if (name == "rq_cap") {
     if (v < 32 || v > 1024 || (v & (v - 1))) return fail(h, B200VR_EINVAL, "set_option: rq_cap is a power of two in 32..1024");
     t.rq_cap = (int)v;
@@ -1466,7 +1464,6 @@ static int render_enqueue(b200vr_t* h)
     // one ring per CTA: high-water mark + one block in flight per warp of the CTA + slack, as a power of two
     P.ring_high = h->tune.ring_high;
     P.rq_self = h->tune.rq_self;
-    P.rq_yield = h->tune.rq_yield;
     int cap = kc.ring_block != RING_BLOCK_FLOAT4 ? h->tune.rq_cap : 32;
     while (cap < P.ring_high + warps_per_cta + 8) cap <<= 1;
     if (cap != h->ring_cap || grid != h->ring_count || kc.ring_block != h->ring_block) {

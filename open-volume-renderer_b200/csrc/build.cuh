@@ -368,8 +368,6 @@ __global__ void ring_start_kernel(unsigned int* ctrl, int stride, int rings, int
     ctrl[(size_t)rings * 3 * stride + 1] = 0u; // march_rq.cuh: blocks published and not yet taken
     ctrl[(size_t)rings * 3 * stride + stride] = 0u;
   }
-  // march_rq.cuh: warps still marching per SM (RING_SM_SLOTS words after the two global lines)
-  for (int i = r; i < 512; i += gridDim.x * blockDim.x) ctrl[(size_t)rings * 3 * stride + 2 * stride + i] = 0u;
 }
 
 // ---- sort-first: dense slice <-> frame for the warp tiles owned by (rank, nranks) --------------------------------

@@ -105,7 +105,6 @@ struct LaunchParams {
   unsigned int* ring_seq;   // per slot sequence number
   float4* ring_data;        // ring_cap blocks of 64 float4 (32 tasks)
   int ring_cap, ring_high;  // slots (power of two); fill level above which a producer shades a block before publishing
-  int rq_yield;             // march_rq.cuh: helpers leave SMs with marching warps alone once fewer than this many warps march
   int rq_self;              // march_rq.cuh: blocks of a tile its warp shades itself while the ring is above ring_high
   unsigned long long* acc;  // per pixel 3 words of fixed-point sums: (r|g), (b|Gx), (Gy|Gz)
   float* ray_alpha;         // per pixel opacity of the sample being rendered

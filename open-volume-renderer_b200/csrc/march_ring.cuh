@@ -40,8 +40,7 @@ constexpr float ACC_SCALE = 1073741824.f;      // 2^30
 // control words, 128 bytes apart (separate L2 lines). Per ring r at ctrl + 96 r: [0] head (publish tickets), [32] tail (claim
 // tickets), [64] warps of this ring still marching. After the rings: [0] warps still marching in total, [32] error flag.
 constexpr int RING_CTRL_STRIDE = 32, RING_CTRL_PER_RING = 3 * RING_CTRL_STRIDE;
-constexpr int RING_SM_SLOTS = 512; // march_rq.cuh: warps still marching per SM, indexed by %smid, after the two global lines
-__host__ __device__ __forceinline__ size_t ring_ctrl_words(int rings) { return (size_t)rings * RING_CTRL_PER_RING + 2 * RING_CTRL_STRIDE + RING_SM_SLOTS; }
+__host__ __device__ __forceinline__ size_t ring_ctrl_words(int rings) { return (size_t)rings * RING_CTRL_PER_RING + 2 * RING_CTRL_STRIDE; }
 __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p)
 {
   unsigned int v;
